@@ -1,0 +1,147 @@
+/* ssl4p.h — C-ABI of libssl4p.so: the sm_100a (B200) kernels behind the MAE ViT hot path of irconde/SSL4POLYP.
+ *
+ * The reference has no native/FFI layer (pure Python): its boundary for this path is the
+ * nn.Module API of src/ssl4polyp/models/mae/models_mae.py and src/ssl4polyp/models/models.py.  Each entry point
+ * below replaces the stock ATen/cuBLAS/cuDNN call sequence behind the cited reference lines; the Python side
+ * (ssl4polyp_b200/ops.py) binds them with ctypes and ssl4polyp_b200/models_mae.py mirrors the module API.
+ *
+ * Conventions
+ *   - plain C types only; every pointer is a DEVICE pointer borrowed for the duration of the enqueue;
+ *     the library never allocates or frees device memory and never synchronises the device;
+ *   - every call is asynchronous on `stream` (a cudaStream_t passed as void*; NULL = legacy default stream);
+ *   - return 0 on success, non-zero on failure; ssl4p_last_error() returns a thread-local message;
+ *   - "bf16" = __nv_bfloat16, row-major, innermost dimension contiguous unless a leading dimension is given.
+ */
+#ifndef SSL4P_H_
+#define SSL4P_H_
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SSL4P_ABI_VERSION 1
+int ssl4p_abi_version(void);
+const char* ssl4p_last_error(void);
+/* number of kernels this library has launched in the calling process (for bench.py's gpu_launches) */
+unsigned long long ssl4p_launch_count(void);
+
+/* ------------------------------------------------------------------------------------------------
+ * GEMM on tcgen05 tensor cores (bf16 in, fp32 accumulate in TMEM), TMA-fed, fused epilogues.
+ * Replaces nn.Linear / Conv2d(k=s=16) forward+backward: timm 0.4.12 Attention.qkv/proj, Mlp.fc1/fc2 as
+ * instantiated at models_mae.py:39-41,53-55; decoder_embed :47,174; decoder_pred :58,191; PatchEmbed.proj :33,152.
+ *   layout NT: C[M,N] = A[M,K] . B[N,K]^T      (y = x W^T, forward)
+ *   layout NN: C[M,N] = A[M,K] . B[K,N]        (dx = dy W, dgrad)
+ *   layout TN: C[M,N] = A[K,M]^T . B[K,N]      (dW = dy^T x, wgrad; K = tokens; deterministic split-K)
+ * ------------------------------------------------------------------------------------------------ */
+enum { SSL4P_GEMM_NT = 0, SSL4P_GEMM_NN = 1, SSL4P_GEMM_TN = 2 };
+enum {
+    SSL4P_EPI_BIAS_BF16 = 0,         /* C(bf16)  = acc + bias (bias may be NULL)                          */
+    SSL4P_EPI_BIAS_GELU_BF16 = 1,    /* C(bf16)  = h = acc + bias ; C2(bf16) = gelu_erf(h)     (Mlp.fc1)  */
+    SSL4P_EPI_BIAS_RESIDUAL_F32 = 2, /* C(fp32)  = acc + bias + aux(fp32)     (attn.proj / Mlp.fc2 + skip) */
+    SSL4P_EPI_BIAS_F32 = 3,          /* C(fp32)  = acc + bias                                             */
+    SSL4P_EPI_DGELU_BF16 = 4,        /* C(bf16)  = acc * gelu_erf'(aux(bf16))       (dgrad through GELU)  */
+    SSL4P_EPI_PARTIAL_F32 = 5        /* C(fp32)[split] = acc  (split-K partial planes, M*ldc apart)       */
+};
+#define SSL4P_MAX_SPLITS 16
+int ssl4p_gemm_bf16(const void* A, const void* B, void* C, void* C2, const float* bias, const void* aux,
+                    int M, int N, int K, int lda, int ldb, int ldc, int ldc2, int ldaux,
+                    int layout, int epilogue, int splits, int force_bn, void* stream);
+int ssl4p_gemm_pick_splits(int M, int N, int K);
+size_t ssl4p_gemm_workspace_bytes(int M, int N, int K, int layout, int epilogue);
+/* out[i] (+)= sum_s parts[s*stride + i]   (fixed order: deterministic) */
+int ssl4p_splitk_reduce(const float* parts, int splits, long long stride, float* out, long long n, int accumulate, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * random_masking (models_mae.py:123-148) as a function of the noise the caller drew with torch.rand.
+ *   ids_restore[n,i] = rank of noise[n,i] in its row (stable ascending: ties -> lower index first)  int64
+ *   mask[n,i]        = ids_restore[n,i] >= len_keep ? 1 : 0                                          fp32
+ *   ids_keep[n,r]    = i such that ids_restore[n,i] == r, r < len_keep (= ids_shuffle[:, :len_keep]) int64
+ * ------------------------------------------------------------------------------------------------ */
+int ssl4p_mask_from_noise(const float* noise, int N, int L, int len_keep,
+                          int64_t* ids_restore, float* mask, int64_t* ids_keep, void* stream);
+/* x_masked[n,r,:] = x[n, ids_keep[n,r], :]   (models_mae.py:139-140), fp32 */
+int ssl4p_gather_tokens_f32(const float* x, const int64_t* ids_keep, float* out, int N, int L, int keep, int D, void* stream);
+
+/* patchify / unpatchify (models_mae.py:95-121): imgs[n,c,h*p+pi,w*p+qi] <-> x[n,h*W+w,(pi*p+qi)*C+c], fp32 */
+int ssl4p_patchify(const float* imgs, float* x, int N, int C, int H, int W, int p, void* stream);
+int ssl4p_unpatchify(const float* x, float* imgs, int N, int C, int H, int W, int p, void* stream);
+
+/* PatchEmbed operand (timm PatchEmbed = Conv2d(k=s=p), models_mae.py:33,152) restricted to the kept patches:
+ *   cols[n*keep+r, (c*p+pi)*p+qi] = bf16(imgs[n,c,h*p+pi,w*p+qi]),  (h,w) = divmod(ids_keep[n,r], W/p)
+ * ids_keep == NULL -> all patches in order (keep must equal (H/p)*(W/p)). */
+int ssl4p_im2col_patches(const float* imgs, const int64_t* ids_keep, void* cols_bf16,
+                         int N, int C, int H, int W, int p, int keep, void* stream);
+/* x[n,0,:] = cls + pos[0];  x[n,1+r,:] = tok[n*keep+r,:] + pos[1+ids_keep[n,r]]   (models_mae.py:155,161-163) */
+int ssl4p_assemble_tokens(const float* tok, const int64_t* ids_keep, const float* pos, const float* cls,
+                          float* x, int N, int keep, int D, void* stream);
+/* backward of the above: dtok(bf16)[n*keep+r,:] = dx[n,1+r,:];  dcls[:] (+)= sum_n dx[n,0,:] */
+int ssl4p_assemble_tokens_bwd(const float* dx, void* dtok_bf16, float* dcls, int N, int keep, int D, int accumulate, void* stream);
+
+/* LayerNorm over the last dim (nn.LayerNorm, eps per models_mae.py:227), fp32 in, bf16 out, fp32 statistics saved */
+int ssl4p_layernorm_fwd(const float* x, const float* gamma, const float* beta, float eps,
+                        void* y_bf16, float* mean, float* rstd, int M, int D, void* stream);
+/* dx_out(fp32) = (residual_grad ? residual_grad : 0) + LN'(dy);  dxb(bf16) = bf16(dx_out) if non-NULL;
+ * dgamma/dbeta (+)= column sums (two-stage, deterministic; workspace >= ssl4p_layernorm_bwd_workspace_bytes) */
+int ssl4p_layernorm_bwd(const void* dy_bf16, const float* x, const float* mean, const float* rstd, const float* gamma,
+                        const float* residual_grad, float* dx_out, void* dxb_bf16, float* dgamma, float* dbeta,
+                        int M, int D, int accumulate, void* workspace, size_t workspace_bytes, void* stream);
+size_t ssl4p_layernorm_bwd_workspace_bytes(int M, int D);
+
+/* Multi-head self-attention of timm 0.4.12 Attention.forward (softmax(q k^T * scale) v), fused, per (batch, head).
+ * qkv: bf16 [B, T, 3, H, hd] (the qkv Linear output as-is); out: bf16 [B, T, H*hd]; lse: fp32 [B, H, T]. */
+int ssl4p_attention_fwd(const void* qkv, void* out, float* lse, int B, int T, int H, int hd, float scale, void* stream);
+int ssl4p_attention_bwd(const void* qkv, const void* out, const void* dout, const float* lse, void* dqkv,
+                        int B, int T, int H, int hd, float scale, void* stream);
+
+/* Decoder input assembly (models_mae.py:177-183):
+ *   x[n,0,:]   = y[n,0,:] + dpos[0]
+ *   x[n,1+i,:] = (ids_restore[n,i] < Te-1 ? y[n,1+ids_restore[n,i],:] : mask_token) + dpos[1+i]
+ * y: bf16 [N,Te,Dd] (decoder_embed output), x: fp32 [N,1+L,Dd]. */
+int ssl4p_decoder_unshuffle_fwd(const void* y_bf16, const float* mask_token, const int64_t* ids_restore, const float* dpos,
+                                float* x, int N, int Te, int L, int Dd, void* stream);
+/* dy(bf16)[n,0,:] = dx[n,0,:]; dy[n,1+r,:] = dx[n,1+ids_keep[n,r],:]; dmask_token (+)= sum over masked positions */
+int ssl4p_decoder_unshuffle_bwd(const float* dx, const int64_t* ids_keep, const float* mask, void* dy_bf16, float* dmask_token,
+                                int N, int Te, int L, int Dd, int accumulate, void* workspace, size_t workspace_bytes, void* stream);
+size_t ssl4p_decoder_unshuffle_bwd_workspace_bytes(int N, int L, int Dd);
+
+/* forward_loss (models_mae.py:198-214) without materialising patchify(imgs):
+ *   target = patch pixels (optionally (t-mean)/sqrt(var_unbiased+1e-6)); loss = sum_masked mean_j (pred-target)^2 / sum(mask)
+ * pred: fp32, row (n,i) at pred + (n*pred_batch_stride + i*P) (lets pred live inside a [N,1+L,P] buffer). */
+int ssl4p_masked_mse_fwd(const float* imgs, const float* pred, long long pred_batch_stride, const float* mask, int norm_pix,
+                         float* loss, int N, int C, int H, int W, int p, void* workspace, size_t workspace_bytes, void* stream);
+/* dpred(bf16)[n,i,:] = grad_out * 2 * mask * (pred - target) / (P * sum(mask)); rows with mask 0 are written as 0.
+ * grad_out: device scalar (fp32).  dpred row (n,i) at dpred + n*dpred_batch_stride + i*P. */
+int ssl4p_masked_mse_bwd(const float* imgs, const float* pred, long long pred_batch_stride, const float* mask, int norm_pix,
+                         const float* grad_out, void* dpred_bf16, long long dpred_batch_stride,
+                         int N, int C, int H, int W, int p, void* workspace, size_t workspace_bytes, void* stream);
+size_t ssl4p_masked_mse_workspace_bytes(int N, int L);
+
+/* out[j] (+)= sum_m x[m,j]  (bias gradients), two-stage deterministic */
+int ssl4p_colsum_bf16(const void* x_bf16, int M, int N, int ld, float* out, int accumulate,
+                      void* workspace, size_t workspace_bytes, void* stream);
+size_t ssl4p_colsum_workspace_bytes(int M, int N);
+
+/* dst(bf16)[i] = src(fp32)[i] */
+int ssl4p_cast_f32_bf16(const float* src, void* dst_bf16, long long n, void* stream);
+
+/* Fused flat AdamW (torch.optim.AdamW semantics, main_pretrain.py:217-218) over a flat parameter arena:
+ *   g = grad*grad_scale; p *= 1 - lr*wd[chunk]; m,v update; p -= lr/bc1 * m / (sqrt(v)/sqrt(bc2) + eps)
+ * wd_flags: one byte per 256-element chunk (1 = apply weight decay).  Also refreshes the bf16 shadow weights and
+ * counts non-finite gradients into *nonfinite (models/mae/util/misc.py:387-400 detect_grad_anomalies). */
+int ssl4p_adamw_flat(float* p, const float* g, float* m, float* v, void* p_bf16, const uint8_t* wd_flags, long long n,
+                     float lr, float beta1, float beta2, float eps, float weight_decay, float bias_corr1, float bias_corr2,
+                     float grad_scale, int* nonfinite, void* stream);
+
+/* ViT_from_MAE head (models.py:211-222): logits[n,:] = W . pooled[n,:] + b with pooled = x[n,0,:] ("cls") or
+ * mean_i x[n,1+i,:] ("spatial"); x is the fp32 output of the final LayerNorm kept as bf16 [N,T,D]. */
+int ssl4p_pool_head_fwd(const void* xn_bf16, const float* W, const float* b, float* logits, int N, int T, int D, int ncls,
+                        int spatial, void* stream);
+int ssl4p_pool_head_bwd(const void* xn_bf16, const float* W, const float* dlogits, void* dxn_bf16, float* dW, float* db,
+                        int N, int T, int D, int ncls, int spatial, int accumulate, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SSL4P_H_ */

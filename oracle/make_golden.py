@@ -235,7 +235,7 @@ def main():
     tiny = O.MAEConfig(img_size=64, embed_dim=64, depth=2, num_heads=2, decoder_embed_dim=32, decoder_depth=1,
                        decoder_num_heads=2, norm_pix_loss=True)
     cases.append(run_case(ref_mod, "tiny", tiny, tiny_kwargs, B=3, seed=4, mask_ratio=0.75, hf_check=True))
-    out = {"cases": cases, "ties": crafted_ties_case(), "torch": torch.__version__,
+    out = {"cases": cases, "ties": crafted_ties_case(), "torch": str(torch.__version__),
            "generator": "oracle/make_golden.py", "reference": "irconde/SSL4POLYP models_mae.py (unmodified) + timm 0.4.12 shim"}
     path = os.path.join(GOLDEN_DIR, "mae_golden.pt")
     torch.save(out, path)

@@ -1,0 +1,481 @@
+// bf16 GEMM on the 5th-gen tensor cores: TMA (SWIZZLE_128B) -> shared memory -> tcgen05.mma (fp32
+// accumulators in TMEM, double buffered) -> tcgen05.ld epilogue with bias / GELU / residual fusion.
+//
+// Replaces the cuBLAS `addmm` calls behind every nn.Linear of timm 0.4.12's Block/Attention/Mlp as used by
+// /root/reference/src/ssl4polyp/models/mae/models_mae.py:39-41,53-55,47,58 (SURVEY §2d K1,K9,K11-K14,K16) and
+// their autograd backward (dgrad = NN layout, wgrad = TN layout with deterministic split-K).
+//
+// Persistent kernel, one CTA per SM, 192 threads:
+//   warp 0      : TMA producer (one elected lane)
+//   warp 1      : TMEM allocator + tcgen05.mma issuer (one elected lane)
+//   warps 2..5  : epilogue; warp w owns TMEM lanes 32*(w%4) .. 32*(w%4)+31  (= 32 rows of the 128-row tile)
+// Pipelines: smem full/empty ring (kStages), TMEM full/empty (2 accumulators).
+#include "common.cuh"
+#include "ssl4p.h"
+#include <mutex>
+#include <unordered_map>
+
+namespace ssl4p {
+
+constexpr int BM = 128;          // tile rows (UMMA M, cta_group::1)
+constexpr int BK = 64;           // K per stage: 64 bf16 = 128 B = one SWIZZLE_128B row
+constexpr int UMMA_K = 16;
+constexpr int kGemmThreads = 192;
+
+struct GemmParams {
+    int M, N, K;                 // C[M,N] = sum_k A[m,k] B[n,k]
+    int ldc, ldc2, ldaux;        // leading dimensions (elements) of C, C2 and aux
+    int k_per_split;             // K range per split (multiple of BK); split index = tile / (mt*nt)
+    int splits;
+    void* C;                     // primary output
+    void* C2;                    // secondary output (GELU: activated copy)
+    const float* bias;           // [N] or null
+    const void* aux;             // residual (fp32 [M,ldaux]) or pre-activation (bf16 [M,ldaux])
+    long long split_stride;      // elements between split-K partial planes of C
+};
+
+template <int BN, bool A_MN, bool B_MN>
+struct SmemLayout {
+    static constexpr int kABytes = BM * BK * 2;
+    static constexpr int kBBytes = BN * BK * 2;
+    static constexpr int kStageBytes = kABytes + kBBytes;
+    static constexpr int kBudget = 200 * 1024;
+    static constexpr int kStagesRaw = kBudget / kStageBytes;
+    static constexpr int kStages = kStagesRaw > 8 ? 8 : kStagesRaw;
+    static constexpr int kBarBytes = 1024;
+    static constexpr int kTotal = kStages * kStageBytes + kBarBytes + 1024 /*align slack*/;
+};
+
+// ---- epilogue math ------------------------------------------------------------------------------
+// Each epilogue thread owns one output row and receives 32 consecutive fp32 accumulator columns.
+template <int EPI>
+__device__ __forceinline__ void epilogue_chunk(const GemmParams& p, int row, int col0, int ncols, int split, uint32_t (&acc)[32]) {
+    float v[32];
+#pragma unroll
+    for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(acc[j]);
+
+    if constexpr (EPI == SSL4P_EPI_BIAS_BF16 || EPI == SSL4P_EPI_BIAS_GELU_BF16 || EPI == SSL4P_EPI_BIAS_RESIDUAL_F32 ||
+                  EPI == SSL4P_EPI_BIAS_F32) {
+        if (p.bias != nullptr) {
+            if (ncols == 32) {
+#pragma unroll
+                for (int j = 0; j < 32; j += 4) {
+                    const float4 b = __ldg(reinterpret_cast<const float4*>(p.bias + col0 + j));
+                    v[j] += b.x; v[j + 1] += b.y; v[j + 2] += b.z; v[j + 3] += b.w;
+                }
+            } else {
+#pragma unroll
+                for (int j = 0; j < 32; ++j) if (j < ncols) v[j] += __ldg(p.bias + col0 + j);
+            }
+        }
+    }
+
+    const size_t off = (size_t)row * p.ldc + col0;
+    if constexpr (EPI == SSL4P_EPI_BIAS_RESIDUAL_F32) {
+        const float* res = reinterpret_cast<const float*>(p.aux) + (size_t)row * p.ldaux + col0;
+        float* out = reinterpret_cast<float*>(p.C) + off;
+        if (ncols == 32) {
+#pragma unroll
+            for (int j = 0; j < 32; j += 4) {
+                const float4 r = *reinterpret_cast<const float4*>(res + j);
+                float4 o; o.x = v[j] + r.x; o.y = v[j + 1] + r.y; o.z = v[j + 2] + r.z; o.w = v[j + 3] + r.w;
+                *reinterpret_cast<float4*>(out + j) = o;
+            }
+        } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) if (j < ncols) out[j] = v[j] + res[j];
+        }
+    } else if constexpr (EPI == SSL4P_EPI_BIAS_F32 || EPI == SSL4P_EPI_PARTIAL_F32) {
+        float* out = reinterpret_cast<float*>(p.C) + off + (EPI == SSL4P_EPI_PARTIAL_F32 ? (size_t)split * p.split_stride : 0);
+        if (ncols == 32) {
+#pragma unroll
+            for (int j = 0; j < 32; j += 4) *reinterpret_cast<float4*>(out + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+        } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) if (j < ncols) out[j] = v[j];
+        }
+    } else {
+        // bf16 outputs
+        if constexpr (EPI == SSL4P_EPI_DGELU_BF16) {
+            const __nv_bfloat16* h = reinterpret_cast<const __nv_bfloat16*>(p.aux) + (size_t)row * p.ldaux + col0;
+            if (ncols == 32) {
+#pragma unroll
+                for (int j = 0; j < 32; j += 8) {
+                    const uint4 hv = *reinterpret_cast<const uint4*>(h + j);
+                    const uint32_t hw[4] = {hv.x, hv.y, hv.z, hv.w};
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        const float2 hf = unpack_bf16(hw[q]);
+                        v[j + 2 * q] *= gelu_grad_f(hf.x);
+                        v[j + 2 * q + 1] *= gelu_grad_f(hf.y);
+                    }
+                }
+            } else {
+#pragma unroll
+                for (int j = 0; j < 32; ++j) if (j < ncols) v[j] *= gelu_grad_f(__bfloat162float(h[j]));
+            }
+        }
+        __nv_bfloat16* out = reinterpret_cast<__nv_bfloat16*>(p.C) + off;
+        if (ncols == 32) {
+#pragma unroll
+            for (int j = 0; j < 32; j += 8) {
+                uint4 o;
+                o.x = pack_bf16(v[j], v[j + 1]); o.y = pack_bf16(v[j + 2], v[j + 3]);
+                o.z = pack_bf16(v[j + 4], v[j + 5]); o.w = pack_bf16(v[j + 6], v[j + 7]);
+                *reinterpret_cast<uint4*>(out + j) = o;
+            }
+        } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) if (j < ncols) out[j] = __float2bfloat16(v[j]);
+        }
+        if constexpr (EPI == SSL4P_EPI_BIAS_GELU_BF16) {
+            __nv_bfloat16* out2 = reinterpret_cast<__nv_bfloat16*>(p.C2) + (size_t)row * p.ldc2 + col0;
+            if (ncols == 32) {
+#pragma unroll
+                for (int j = 0; j < 32; j += 8) {
+                    uint4 o;
+                    o.x = pack_bf16(gelu_f(v[j]), gelu_f(v[j + 1])); o.y = pack_bf16(gelu_f(v[j + 2]), gelu_f(v[j + 3]));
+                    o.z = pack_bf16(gelu_f(v[j + 4]), gelu_f(v[j + 5])); o.w = pack_bf16(gelu_f(v[j + 6]), gelu_f(v[j + 7]));
+                    *reinterpret_cast<uint4*>(out2 + j) = o;
+                }
+            } else {
+#pragma unroll
+                for (int j = 0; j < 32; ++j) if (j < ncols) out2[j] = __float2bfloat16(gelu_f(v[j]));
+            }
+        }
+    }
+}
+
+// ---- the kernel ---------------------------------------------------------------------------------
+template <int BN, bool A_MN, bool B_MN, int EPI>
+__global__ void __launch_bounds__(kGemmThreads, 1)
+gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmParams p) {
+    using L = SmemLayout<BN, A_MN, B_MN>;
+    constexpr int kStages = L::kStages;
+    constexpr uint32_t kTmemCols = 512;                      // 2 accumulators x up to 256 columns
+    constexpr uint32_t kAccStride = 256;
+
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    uint8_t* smem_a = smem;                                  // kStages x 16 KB
+    uint8_t* smem_b = smem + kStages * L::kABytes;           // kStages x BN*128 B
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kStages * L::kStageBytes);
+    uint64_t* full_bar = bars;                               // [kStages]
+    uint64_t* empty_bar = bars + kStages;                    // [kStages]
+    uint64_t* tmem_full = bars + 2 * kStages;                // [2]
+    uint64_t* tmem_empty = bars + 2 * kStages + 2;           // [2]
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * kStages + 4);
+
+    const int warp = threadIdx.x >> 5;
+    const int mt = (p.M + BM - 1) / BM;
+    const int nt = (p.N + BN - 1) / BN;
+    const int tiles_mn = mt * nt;
+    const int total_tiles = tiles_mn * p.splits;
+
+    if (warp == 0 && lane_id() == 0) {
+        tma_prefetch_desc(&tmA);
+        tma_prefetch_desc(&tmB);
+    }
+    if (warp == 1) {
+        if (lane_id() == 0) {
+            for (int i = 0; i < kStages; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], 1); }
+            for (int i = 0; i < 2; ++i) { mbar_init(&tmem_full[i], 1); mbar_init(&tmem_empty[i], 4); }
+            mbar_fence_init();
+            fence_proxy_async();
+        }
+        __syncwarp();
+        tmem_alloc<kTmemCols>(tmem_slot);
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        // ===================== TMA producer =====================
+        if (lane_id() == 0) {
+            int stage = 0; uint32_t phase = 0;
+            for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+                const int split = tile / tiles_mn;
+                const int t = tile - split * tiles_mn;
+                const int m0 = (t / nt) * BM, n0 = (t % nt) * BN;
+                const int k_begin = split * p.k_per_split;
+                const int k_end = min(p.K, k_begin + p.k_per_split);
+                for (int k = k_begin; k < k_end; k += BK) {
+                    mbar_wait(&empty_bar[stage], phase ^ 1);
+                    mbar_expect_tx(&full_bar[stage], L::kStageBytes);
+                    uint8_t* sa = smem_a + stage * L::kABytes;
+                    uint8_t* sb = smem_b + stage * L::kBBytes;
+                    if constexpr (!A_MN) {
+                        tma_load_2d(sa, &tmA, &full_bar[stage], k, m0);             // box [64 k] x [128 rows]
+                    } else {
+#pragma unroll
+                        for (int c = 0; c < BM / 64; ++c)                            // box [64 m] x [64 k rows]
+                            tma_load_2d(sa + c * (BK * 128), &tmA, &full_bar[stage], m0 + c * 64, k);
+                    }
+                    if constexpr (!B_MN) {
+                        tma_load_2d(sb, &tmB, &full_bar[stage], k, n0);             // box [64 k] x [BN rows]
+                    } else {
+#pragma unroll
+                        for (int c = 0; c < BN / 64; ++c)
+                            tma_load_2d(sb + c * (BK * 128), &tmB, &full_bar[stage], n0 + c * 64, k);
+                    }
+                    if (++stage == kStages) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+        __syncwarp();
+    } else if (warp == 1) {
+        // ===================== MMA issuer =====================
+        constexpr uint32_t idesc = umma_idesc_bf16(BM, BN, A_MN, B_MN);
+        // K-major SW128: 8-row groups 1024 B apart (SBO), LBO unused.  MN-major SW128: 64-element MN chunks
+        // BK*128 B apart (LBO), 8-k-row groups 1024 B apart (SBO).
+        constexpr uint32_t a_lbo = A_MN ? BK * 128 : 16, a_sbo = 1024;
+        constexpr uint32_t b_lbo = B_MN ? BK * 128 : 16, b_sbo = 1024;
+        constexpr uint32_t a_kstep = A_MN ? (UMMA_K / 8) * 1024 : UMMA_K * 2;   // bytes per UMMA_K step
+        constexpr uint32_t b_kstep = B_MN ? (UMMA_K / 8) * 1024 : UMMA_K * 2;
+        const bool leader = lane_id() == 0;     // tcgen05.commit tracks the issuing thread: one fixed lane issues all
+        int stage = 0; uint32_t phase = 0;
+        int acc = 0; uint32_t acc_phase = 0;
+        for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+            const int split = tile / tiles_mn;
+            const int k_begin = split * p.k_per_split;
+            const int k_end = min(p.K, k_begin + p.k_per_split);
+            mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
+            tc_fence_after();
+            const uint32_t tmem_d = tmem_base + acc * kAccStride;
+            uint32_t accumulate = 0;
+            for (int k = k_begin; k < k_end; k += BK) {
+                mbar_wait(&full_bar[stage], phase);
+                tc_fence_after();
+                if (leader) {
+                    const uint32_t sa = smem_u32(smem_a + stage * L::kABytes);
+                    const uint32_t sb = smem_u32(smem_b + stage * L::kBBytes);
+#pragma unroll
+                    for (int kk = 0; kk < BK / UMMA_K; ++kk) {
+                        const uint64_t adesc = umma_smem_desc(sa + kk * a_kstep, a_lbo, a_sbo);
+                        const uint64_t bdesc = umma_smem_desc(sb + kk * b_kstep, b_lbo, b_sbo);
+                        umma_bf16(tmem_d, adesc, bdesc, idesc, accumulate);
+                        accumulate = 1;
+                    }
+                    umma_commit(&empty_bar[stage]);                  // frees the smem slot when the MMAs retire
+                }
+                __syncwarp();
+                if (++stage == kStages) { stage = 0; phase ^= 1; }
+            }
+            if (leader) umma_commit(&tmem_full[acc]);            // accumulator complete -> epilogue
+            __syncwarp();
+            if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+        }
+    } else {
+        // ===================== epilogue warps =====================
+        const int q = warp & 3;                                       // TMEM lane quarter this warp may access
+        int acc = 0; uint32_t acc_phase = 0;
+        for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+            const int split = tile / tiles_mn;
+            const int t = tile - split * tiles_mn;
+            const int m0 = (t / nt) * BM, n0 = (t % nt) * BN;
+            mbar_wait(&tmem_full[acc], acc_phase);
+            tc_fence_after();
+            const int row = m0 + q * 32 + (int)lane_id();
+            const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + acc * kAccStride;
+#pragma unroll 1
+            for (int c = 0; c < BN; c += 32) {
+                uint32_t r[32];
+                tmem_ld_32x32(taddr + c, r);
+                tmem_ld_wait();
+                if (split * p.k_per_split >= p.K) {              // empty split-K range: the accumulator was never written
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) r[j] = 0u;
+                }
+                const int col0 = n0 + c;
+                const int ncols = min(32, p.N - col0);
+                if (row < p.M && ncols > 0) epilogue_chunk<EPI>(p, row, col0, ncols, split, r);
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane_id() == 0) mbar_arrive(&tmem_empty[acc]);
+            if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc<kTmemCols>(tmem_base);
+    }
+}
+
+// ---- host side ----------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode_fn() {
+    static EncodeTiledFn fn = nullptr;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        void* f = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &qres) == cudaSuccess &&
+            qres == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeTiledFn>(f);
+    });
+    return fn;
+}
+
+// 2-D bf16 tensor map: `inner` contiguous elements per row, `rows` rows with pitch `ld` elements;
+// box = 64 x box_rows, SWIZZLE_128B, zero fill out of bounds.
+static int make_tmap(CUtensorMap* out, const void* ptr, long long inner, long long rows, long long ld, int box_rows) {
+    struct Key { const void* p; long long a, b, c; int r; bool operator==(const Key& o) const { return p == o.p && a == o.a && b == o.b && c == o.c && r == o.r; } };
+    struct Hash { size_t operator()(const Key& k) const { return std::hash<const void*>()(k.p) ^ (size_t)(k.a * 1315423911ull) ^ (size_t)(k.b * 2654435761ull) ^ (size_t)(k.c << 7) ^ (size_t)k.r; } };
+    static thread_local std::unordered_map<Key, CUtensorMap, Hash> cache;
+    Key key{ptr, inner, rows, ld, box_rows};
+    auto it = cache.find(key);
+    if (it != cache.end()) { *out = it->second; return SSL4P_OK; }
+
+    EncodeTiledFn enc = get_encode_fn();
+    if (!enc) { set_error("cuTensorMapEncodeTiled entry point unavailable (no CUDA driver?)"); return SSL4P_ERR_CUDA; }
+    SSL4P_REQUIRE((reinterpret_cast<uintptr_t>(ptr) & 15) == 0, "TMA operand pointer must be 16-byte aligned");
+    SSL4P_REQUIRE((ld * 2) % 16 == 0, "TMA operand row pitch must be a multiple of 16 bytes (ld=%lld)", ld);
+    cuuint64_t dims[2] = {(cuuint64_t)inner, (cuuint64_t)rows};
+    cuuint64_t strides[1] = {(cuuint64_t)ld * 2};
+    cuuint32_t box[2] = {64u, (cuuint32_t)box_rows};
+    cuuint32_t estr[2] = {1u, 1u};
+    CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled failed (CUresult %d) inner=%lld rows=%lld ld=%lld box_rows=%d", (int)r, inner, rows, ld, box_rows); return SSL4P_ERR_CUDA; }
+    if (cache.size() > 4096) cache.clear();
+    cache.emplace(key, *out);
+    return SSL4P_OK;
+}
+
+template <int BN, bool A_MN, bool B_MN, int EPI>
+static int launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p, cudaStream_t stream) {
+    using L = SmemLayout<BN, A_MN, B_MN>;
+    auto kern = gemm_tcgen05_kernel<BN, A_MN, B_MN, EPI>;
+    static bool attr_set = false;
+    if (!attr_set) {
+        SSL4P_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal));
+        attr_set = true;
+    }
+    const int mt = (p.M + BM - 1) / BM, nt = (p.N + BN - 1) / BN;
+    const int total = mt * nt * p.splits;
+    const int grid = total < num_sms() ? total : num_sms();
+    kern<<<grid, kGemmThreads, L::kTotal, stream>>>(tmA, tmB, p);
+    return check_launch("gemm_tcgen05_kernel");
+}
+
+// Only the (layout, epilogue) pairs the model uses are instantiated.
+template <int BN>
+static int dispatch(int layout, int epi, const CUtensorMap& a, const CUtensorMap& b, const GemmParams& p, cudaStream_t s) {
+    if (layout == SSL4P_GEMM_NT) {
+        switch (epi) {
+            case SSL4P_EPI_BIAS_BF16: return launch<BN, false, false, SSL4P_EPI_BIAS_BF16>(a, b, p, s);
+            case SSL4P_EPI_BIAS_GELU_BF16: return launch<BN, false, false, SSL4P_EPI_BIAS_GELU_BF16>(a, b, p, s);
+            case SSL4P_EPI_BIAS_RESIDUAL_F32: return launch<BN, false, false, SSL4P_EPI_BIAS_RESIDUAL_F32>(a, b, p, s);
+            case SSL4P_EPI_BIAS_F32: return launch<BN, false, false, SSL4P_EPI_BIAS_F32>(a, b, p, s);
+        }
+    } else if (layout == SSL4P_GEMM_NN) {
+        switch (epi) {
+            case SSL4P_EPI_BIAS_BF16: return launch<BN, false, true, SSL4P_EPI_BIAS_BF16>(a, b, p, s);
+            case SSL4P_EPI_DGELU_BF16: return launch<BN, false, true, SSL4P_EPI_DGELU_BF16>(a, b, p, s);
+        }
+    } else {
+        switch (epi) {
+            case SSL4P_EPI_PARTIAL_F32: return launch<BN, true, true, SSL4P_EPI_PARTIAL_F32>(a, b, p, s);
+        }
+    }
+    set_error("gemm: epilogue %d is not available for layout %d", epi, layout);
+    return SSL4P_ERR_UNSUPPORTED;
+}
+
+// wave-quantisation aware choice of the N tile: minimise ceil(tiles/SMs) * per-tile cost (~BN, plus a fixed term)
+static int pick_bn(int M, int N, int splits, bool need64) {
+    const int cands[4] = {256, 192, 128, 64};
+    const int sms = num_sms();
+    int best = 128; double best_cost = 1e30;
+    for (int i = 0; i < 4; ++i) {
+        const int bn = cands[i];
+        (void)need64;
+        const long long tiles = (long long)((M + BM - 1) / BM) * ((N + bn - 1) / bn) * splits;
+        const long long waves = (tiles + sms - 1) / sms;
+        // smaller N tiles run the tensor pipe below peak (A re-read from smem per MMA): mild penalty
+        const double eff = bn >= 256 ? 1.0 : bn >= 192 ? 0.95 : bn >= 128 ? 0.85 : 0.6;
+        const double cost = (double)waves * (bn / eff + 24.0);
+        if (cost < best_cost) { best_cost = cost; best = bn; }
+    }
+    return best;
+}
+
+}  // namespace ssl4p
+
+using namespace ssl4p;
+
+extern "C" size_t ssl4p_gemm_workspace_bytes(int M, int N, int K, int layout, int epilogue) {
+    (void)K; (void)layout;
+    if (epilogue != SSL4P_EPI_PARTIAL_F32) return 0;
+    return (size_t)SSL4P_MAX_SPLITS * (size_t)M * (size_t)N * sizeof(float);
+}
+
+extern "C" int ssl4p_gemm_pick_splits(int M, int N, int K) {
+    // split K so that the tile count reaches ~2 waves; each split keeps >= 8 K-blocks
+    const int sms = num_sms();
+    const int tiles = ((M + BM - 1) / BM) * ((N + 255) / 256);
+    int s = (2 * sms + tiles - 1) / tiles;
+    const int kb = (K + BK - 1) / BK;
+    if (s > kb / 8) s = kb / 8;
+    if (s > SSL4P_MAX_SPLITS) s = SSL4P_MAX_SPLITS;
+    if (s < 1) s = 1;
+    return s;
+}
+
+extern "C" int ssl4p_gemm_bf16(const void* A, const void* B, void* C, void* C2, const float* bias, const void* aux,
+                               int M, int N, int K, int lda, int ldb, int ldc, int ldc2, int ldaux,
+                               int layout, int epilogue, int splits, int force_bn, void* stream_) {
+    cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+    SSL4P_REQUIRE(A && B && C, "gemm: null operand");
+    SSL4P_REQUIRE(M > 0 && N > 0 && K > 0, "gemm: bad shape M=%d N=%d K=%d", M, N, K);
+    SSL4P_REQUIRE(layout >= 0 && layout <= 2, "gemm: bad layout %d", layout);
+    const bool a_mn = layout == SSL4P_GEMM_TN;
+    const bool b_mn = layout != SSL4P_GEMM_NT;
+    if (splits < 1) splits = 1;
+    SSL4P_REQUIRE(splits == 1 || epilogue == SSL4P_EPI_PARTIAL_F32, "gemm: split-K needs the PARTIAL_F32 epilogue");
+    SSL4P_REQUIRE(splits <= SSL4P_MAX_SPLITS, "gemm: too many splits");
+    if (epilogue == SSL4P_EPI_BIAS_GELU_BF16) SSL4P_REQUIRE(C2 != nullptr, "gemm: GELU epilogue needs C2");
+    if (epilogue == SSL4P_EPI_BIAS_RESIDUAL_F32 || epilogue == SSL4P_EPI_DGELU_BF16) SSL4P_REQUIRE(aux != nullptr, "gemm: epilogue needs aux");
+    // vectorised epilogue accesses
+    SSL4P_REQUIRE(ldc % 8 == 0 && (reinterpret_cast<uintptr_t>(C) & 15) == 0, "gemm: C must be 16B aligned with ldc %% 8 == 0");
+    if (C2) SSL4P_REQUIRE(ldc2 % 8 == 0 && (reinterpret_cast<uintptr_t>(C2) & 15) == 0, "gemm: C2 alignment");
+    if (aux) SSL4P_REQUIRE(ldaux % 8 == 0 && (reinterpret_cast<uintptr_t>(aux) & 15) == 0, "gemm: aux alignment");
+    if (bias) SSL4P_REQUIRE((reinterpret_cast<uintptr_t>(bias) & 15) == 0, "gemm: bias alignment");
+
+    int bn = force_bn > 0 ? force_bn : pick_bn(M, N, splits, b_mn);
+    SSL4P_REQUIRE(bn == 64 || bn == 128 || bn == 192 || bn == 256, "gemm: unsupported N tile %d", bn);
+
+    GemmParams p;
+    p.M = M; p.N = N; p.K = K; p.ldc = ldc; p.ldc2 = ldc2; p.ldaux = ldaux;
+    p.splits = splits;
+    const int kb = (K + BK - 1) / BK;
+    p.k_per_split = ((kb + splits - 1) / splits) * BK;
+    p.C = C; p.C2 = C2; p.bias = bias; p.aux = aux;
+    p.split_stride = (long long)M * ldc;
+
+    CUtensorMap tmA, tmB;
+    int rc;
+    if (!a_mn) rc = make_tmap(&tmA, A, K, M, lda, BM);            // A[M,K], K contiguous
+    else       rc = make_tmap(&tmA, A, M, K, lda, BK);            // A stored [K,M], M contiguous
+    if (rc) return rc;
+    if (!b_mn) rc = make_tmap(&tmB, B, K, N, ldb, bn);            // B[N,K], K contiguous
+    else       rc = make_tmap(&tmB, B, N, K, ldb, BK);            // B stored [K,N], N contiguous
+    if (rc) return rc;
+
+    if (bn == 256) return dispatch<256>(layout, epilogue, tmA, tmB, p, stream);
+    if (bn == 192) return dispatch<192>(layout, epilogue, tmA, tmB, p, stream);
+    if (bn == 128) return dispatch<128>(layout, epilogue, tmA, tmB, p, stream);
+    if (bn == 64) return dispatch<64>(layout, epilogue, tmA, tmB, p, stream);
+    set_error("gemm: dispatch fell through");
+    return SSL4P_ERR_ARG;
+}

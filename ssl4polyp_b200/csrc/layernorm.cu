@@ -1,0 +1,250 @@
+// LayerNorm forward/backward over the last dimension (nn.LayerNorm(eps=1e-6) as passed at
+// /root/reference/src/ssl4polyp/models/mae/models_mae.py:227,235; used as norm1/norm2 of every timm Block, `norm` :168
+// and `decoder_norm` :188).  fp32 residual stream in, bf16 GEMM operand out.  HBM-bound: one warp per row, the row
+// lives in registers (16-byte loads), statistics by warp shuffles; the backward fuses the residual-gradient add and
+// produces the bf16 shadow of the gradient stream; dgamma/dbeta are reduced in two deterministic stages.
+#include "common.cuh"
+#include "ssl4p.h"
+
+namespace ssl4p {
+
+constexpr int kLnWarps = 8;
+
+// NV = float4 per lane (D = 128*NV).  NV == 0: generic D (D % 4 == 0), re-reading the row from L1/L2.
+template <int NV>
+__global__ void __launch_bounds__(kLnWarps * 32)
+layernorm_fwd_kernel(const float* __restrict__ x, const float* __restrict__ gamma, const float* __restrict__ beta, float eps,
+                     __nv_bfloat16* __restrict__ y, float* __restrict__ mean_out, float* __restrict__ rstd_out, int M, int D) {
+    const int lane = lane_id();
+    const int row = blockIdx.x * kLnWarps + (threadIdx.x >> 5);
+    if (row >= M) return;
+    const float4* xr = reinterpret_cast<const float4*>(x + (size_t)row * D);
+    const float4* g4 = reinterpret_cast<const float4*>(gamma);
+    const float4* b4 = reinterpret_cast<const float4*>(beta);
+    uint2* yr = reinterpret_cast<uint2*>(y + (size_t)row * D);
+    const float inv_d = 1.0f / (float)D;
+    if constexpr (NV > 0) {
+        float4 v[NV];
+        float s = 0.f;
+#pragma unroll
+        for (int i = 0; i < NV; ++i) { v[i] = xr[lane + 32 * i]; s += (v[i].x + v[i].y) + (v[i].z + v[i].w); }
+        const float mean = warp_sum(s) * inv_d;
+        float q = 0.f;
+#pragma unroll
+        for (int i = 0; i < NV; ++i) {
+            const float a = v[i].x - mean, b = v[i].y - mean, c = v[i].z - mean, d = v[i].w - mean;
+            q += (a * a + b * b) + (c * c + d * d);
+        }
+        const float rstd = rsqrtf(warp_sum(q) * inv_d + eps);
+#pragma unroll
+        for (int i = 0; i < NV; ++i) {
+            const float4 g = g4[lane + 32 * i], b = b4[lane + 32 * i];
+            uint2 o;
+            o.x = pack_bf16((v[i].x - mean) * rstd * g.x + b.x, (v[i].y - mean) * rstd * g.y + b.y);
+            o.y = pack_bf16((v[i].z - mean) * rstd * g.z + b.z, (v[i].w - mean) * rstd * g.w + b.w);
+            yr[lane + 32 * i] = o;
+        }
+        if (lane == 0) { mean_out[row] = mean; rstd_out[row] = rstd; }
+    } else {
+        const int D4 = D / 4;
+        float s = 0.f;
+        for (int i = lane; i < D4; i += 32) { const float4 v = xr[i]; s += (v.x + v.y) + (v.z + v.w); }
+        const float mean = warp_sum(s) * inv_d;
+        float q = 0.f;
+        for (int i = lane; i < D4; i += 32) {
+            const float4 v = xr[i];
+            const float a = v.x - mean, b = v.y - mean, c = v.z - mean, d = v.w - mean;
+            q += (a * a + b * b) + (c * c + d * d);
+        }
+        const float rstd = rsqrtf(warp_sum(q) * inv_d + eps);
+        for (int i = lane; i < D4; i += 32) {
+            const float4 v = xr[i], g = g4[i], b = b4[i];
+            uint2 o;
+            o.x = pack_bf16((v.x - mean) * rstd * g.x + b.x, (v.y - mean) * rstd * g.y + b.y);
+            o.y = pack_bf16((v.z - mean) * rstd * g.z + b.z, (v.w - mean) * rstd * g.w + b.w);
+            yr[i] = o;
+        }
+        if (lane == 0) { mean_out[row] = mean; rstd_out[row] = rstd; }
+    }
+}
+
+// Backward.  Grid-stride over rows (persistent), each lane keeps its dgamma/dbeta partials in registers.
+// part layout: [gridDim.x][2][D]  (dgamma then dbeta).
+template <int NV>
+__global__ void __launch_bounds__(kLnWarps * 32)
+layernorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const float* __restrict__ x, const float* __restrict__ mean_in,
+                     const float* __restrict__ rstd_in, const float* __restrict__ gamma, const float* __restrict__ res_grad,
+                     float* __restrict__ dx_out, __nv_bfloat16* __restrict__ dxb, float* __restrict__ part, int M, int D) {
+    extern __shared__ float s_red[];                           // [kLnWarps][2*D]
+    const int lane = lane_id();
+    const int warp = threadIdx.x >> 5;
+    const float inv_d = 1.0f / (float)D;
+    const float4* g4 = reinterpret_cast<const float4*>(gamma);
+    static_assert(NV > 0, "register-resident variant only");
+    float4 dg[NV], db[NV], gam[NV];
+#pragma unroll
+    for (int i = 0; i < NV; ++i) { dg[i] = make_float4(0, 0, 0, 0); db[i] = make_float4(0, 0, 0, 0); gam[i] = g4[lane + 32 * i]; }
+
+    for (int row = blockIdx.x * kLnWarps + warp; row < M; row += gridDim.x * kLnWarps) {
+        const float4* xr = reinterpret_cast<const float4*>(x + (size_t)row * D);
+        const uint2* dyr = reinterpret_cast<const uint2*>(dy + (size_t)row * D);
+        const float mean = mean_in[row], rstd = rstd_in[row];
+        float4 xh[NV], gy[NV];
+        float c1 = 0.f, c2 = 0.f;
+#pragma unroll
+        for (int i = 0; i < NV; ++i) {
+            const float4 v = xr[lane + 32 * i];
+            const uint2 u = dyr[lane + 32 * i];
+            const float2 d01 = unpack_bf16(u.x), d23 = unpack_bf16(u.y);
+            xh[i] = make_float4((v.x - mean) * rstd, (v.y - mean) * rstd, (v.z - mean) * rstd, (v.w - mean) * rstd);
+            dg[i].x += d01.x * xh[i].x; dg[i].y += d01.y * xh[i].y; dg[i].z += d23.x * xh[i].z; dg[i].w += d23.y * xh[i].w;
+            db[i].x += d01.x; db[i].y += d01.y; db[i].z += d23.x; db[i].w += d23.y;
+            gy[i] = make_float4(d01.x * gam[i].x, d01.y * gam[i].y, d23.x * gam[i].z, d23.y * gam[i].w);
+            c1 += (gy[i].x + gy[i].y) + (gy[i].z + gy[i].w);
+            c2 += (gy[i].x * xh[i].x + gy[i].y * xh[i].y) + (gy[i].z * xh[i].z + gy[i].w * xh[i].w);
+        }
+        c1 = warp_sum(c1) * inv_d;
+        c2 = warp_sum(c2) * inv_d;
+        float4* dxr = reinterpret_cast<float4*>(dx_out + (size_t)row * D);
+        const float4* rr = res_grad ? reinterpret_cast<const float4*>(res_grad + (size_t)row * D) : nullptr;
+        uint2* dbr = dxb ? reinterpret_cast<uint2*>(dxb + (size_t)row * D) : nullptr;
+#pragma unroll
+        for (int i = 0; i < NV; ++i) {
+            float4 o;
+            o.x = rstd * (gy[i].x - c1 - xh[i].x * c2); o.y = rstd * (gy[i].y - c1 - xh[i].y * c2);
+            o.z = rstd * (gy[i].z - c1 - xh[i].z * c2); o.w = rstd * (gy[i].w - c1 - xh[i].w * c2);
+            if (rr) { const float4 r = rr[lane + 32 * i]; o.x += r.x; o.y += r.y; o.z += r.z; o.w += r.w; }
+            dxr[lane + 32 * i] = o;
+            if (dbr) { uint2 b; b.x = pack_bf16(o.x, o.y); b.y = pack_bf16(o.z, o.w); dbr[lane + 32 * i] = b; }
+        }
+    }
+    // block reduce of the per-warp partial sums (fixed order), then one partial row per block
+    float4* sw = reinterpret_cast<float4*>(s_red + (size_t)warp * 2 * D);
+#pragma unroll
+    for (int i = 0; i < NV; ++i) { sw[lane + 32 * i] = dg[i]; sw[D / 4 + lane + 32 * i] = db[i]; }
+    __syncthreads();
+    for (int j = threadIdx.x; j < 2 * D; j += blockDim.x) {
+        float acc = 0.f;
+#pragma unroll
+        for (int w = 0; w < kLnWarps; ++w) acc += s_red[(size_t)w * 2 * D + j];
+        part[(size_t)blockIdx.x * 2 * D + j] = acc;
+    }
+}
+
+// generic-D backward (small test configurations): one warp per row, partial sums through shared-memory atomics are
+// avoided by giving every block a private [2*D] accumulator updated by one warp at a time in fixed order.
+__global__ void __launch_bounds__(kLnWarps * 32)
+layernorm_bwd_generic_kernel(const __nv_bfloat16* __restrict__ dy, const float* __restrict__ x, const float* __restrict__ mean_in,
+                             const float* __restrict__ rstd_in, const float* __restrict__ gamma, const float* __restrict__ res_grad,
+                             float* __restrict__ dx_out, __nv_bfloat16* __restrict__ dxb, float* __restrict__ part, int M, int D) {
+    extern __shared__ float s_red[];                           // [kLnWarps][2*D]
+    const int lane = lane_id();
+    const int warp = threadIdx.x >> 5;
+    const float inv_d = 1.0f / (float)D;
+    float* my = s_red + (size_t)warp * 2 * D;
+    for (int j = lane; j < 2 * D; j += 32) my[j] = 0.f;
+    __syncwarp();
+    for (int row = blockIdx.x * kLnWarps + warp; row < M; row += gridDim.x * kLnWarps) {
+        const float* xr = x + (size_t)row * D;
+        const __nv_bfloat16* dyr = dy + (size_t)row * D;
+        const float mean = mean_in[row], rstd = rstd_in[row];
+        float c1 = 0.f, c2 = 0.f;
+        for (int j = lane; j < D; j += 32) {
+            const float xh = (xr[j] - mean) * rstd, d = __bfloat162float(dyr[j]);
+            const float gy = d * gamma[j];
+            c1 += gy; c2 += gy * xh;
+            my[j] += d * xh; my[D + j] += d;
+        }
+        c1 = warp_sum(c1) * inv_d; c2 = warp_sum(c2) * inv_d;
+        for (int j = lane; j < D; j += 32) {
+            const float xh = (xr[j] - mean) * rstd, gy = __bfloat162float(dyr[j]) * gamma[j];
+            float o = rstd * (gy - c1 - xh * c2);
+            if (res_grad) o += res_grad[(size_t)row * D + j];
+            dx_out[(size_t)row * D + j] = o;
+            if (dxb) dxb[(size_t)row * D + j] = __float2bfloat16(o);
+        }
+    }
+    __syncthreads();
+    for (int j = threadIdx.x; j < 2 * D; j += blockDim.x) {
+        float acc = 0.f;
+        for (int w = 0; w < kLnWarps; ++w) acc += s_red[(size_t)w * 2 * D + j];
+        part[(size_t)blockIdx.x * 2 * D + j] = acc;
+    }
+}
+
+// out[j] (+)= sum_g part[g][j]  over [G][2D] -> dgamma (j < D) and dbeta (j >= D)
+__global__ void ln_param_grad_reduce_kernel(const float* __restrict__ part, int G, int D, float* __restrict__ dgamma,
+                                            float* __restrict__ dbeta, int accumulate) {
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= 2 * D) return;
+    float* dst = j < D ? dgamma + j : dbeta + (j - D);
+    float acc = accumulate ? *dst : 0.f;
+    for (int g = 0; g < G; ++g) acc += part[(size_t)g * 2 * D + j];
+    *dst = acc;
+}
+
+static int ln_bwd_grid(int M) {
+    int g = 2 * num_sms();
+    const int need = (M + kLnWarps - 1) / kLnWarps;
+    return g < need ? g : need;
+}
+
+}  // namespace ssl4p
+
+using namespace ssl4p;
+#define STREAM ((cudaStream_t)stream)
+
+extern "C" int ssl4p_layernorm_fwd(const float* x, const float* gamma, const float* beta, float eps, void* y, float* mean, float* rstd,
+                                   int M, int D, void* stream) {
+    SSL4P_REQUIRE(x && gamma && beta && y && mean && rstd, "layernorm_fwd: null pointer");
+    SSL4P_REQUIRE(M >= 0 && D > 0 && D % 4 == 0, "layernorm_fwd: D must be a multiple of 4 (D=%d)", D);
+    if (M == 0) return SSL4P_OK;
+    const int grid = (M + kLnWarps - 1) / kLnWarps, threads = kLnWarps * 32;
+    __nv_bfloat16* yb = (__nv_bfloat16*)y;
+    switch (D) {
+        case 512: layernorm_fwd_kernel<4><<<grid, threads, 0, STREAM>>>(x, gamma, beta, eps, yb, mean, rstd, M, D); break;
+        case 768: layernorm_fwd_kernel<6><<<grid, threads, 0, STREAM>>>(x, gamma, beta, eps, yb, mean, rstd, M, D); break;
+        case 1024: layernorm_fwd_kernel<8><<<grid, threads, 0, STREAM>>>(x, gamma, beta, eps, yb, mean, rstd, M, D); break;
+        default: layernorm_fwd_kernel<0><<<grid, threads, 0, STREAM>>>(x, gamma, beta, eps, yb, mean, rstd, M, D); break;
+    }
+    return check_launch("layernorm_fwd_kernel");
+}
+
+extern "C" size_t ssl4p_layernorm_bwd_workspace_bytes(int M, int D) {
+    (void)M;
+    return (size_t)2 * 148 * 2 * 2 * (size_t)D * sizeof(float);     // up to 592 partial rows of [2*D]
+}
+
+extern "C" int ssl4p_layernorm_bwd(const void* dy, const float* x, const float* mean, const float* rstd, const float* gamma,
+                                   const float* residual_grad, float* dx_out, void* dxb, float* dgamma, float* dbeta,
+                                   int M, int D, int accumulate, void* workspace, size_t workspace_bytes, void* stream) {
+    SSL4P_REQUIRE(dy && x && mean && rstd && gamma && dx_out && dgamma && dbeta, "layernorm_bwd: null pointer");
+    SSL4P_REQUIRE(M > 0 && D > 0 && D % 4 == 0, "layernorm_bwd: bad shape");
+    const int grid = ln_bwd_grid(M);
+    SSL4P_REQUIRE(workspace && workspace_bytes >= (size_t)grid * 2 * D * sizeof(float), "layernorm_bwd: workspace too small");
+    const int threads = kLnWarps * 32;
+    const size_t smem = (size_t)kLnWarps * 2 * D * sizeof(float);
+    float* part = (float*)workspace;
+    const __nv_bfloat16* dyb = (const __nv_bfloat16*)dy;
+    __nv_bfloat16* dxbb = (__nv_bfloat16*)dxb;
+#define LN_BWD(NV_)                                                                                                        \
+    {                                                                                                                      \
+        static bool attr = false;                                                                                          \
+        if (!attr && smem > 48 * 1024) { SSL4P_CUDA(cudaFuncSetAttribute(layernorm_bwd_kernel<NV_>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); attr = true; } \
+        layernorm_bwd_kernel<NV_><<<grid, threads, smem, STREAM>>>(dyb, x, mean, rstd, gamma, residual_grad, dx_out, dxbb, part, M, D); \
+    }
+    switch (D) {
+        case 512: LN_BWD(4) break;
+        case 768: LN_BWD(6) break;
+        case 1024: LN_BWD(8) break;
+        default: {
+            SSL4P_REQUIRE(smem <= 48 * 1024, "layernorm_bwd: generic path supports D <= 768");
+            layernorm_bwd_generic_kernel<<<grid, threads, smem, STREAM>>>(dyb, x, mean, rstd, gamma, residual_grad, dx_out, dxbb, part, M, D);
+        }
+    }
+#undef LN_BWD
+    int rc = check_launch("layernorm_bwd_kernel");
+    if (rc) return rc;
+    ln_param_grad_reduce_kernel<<<(2 * D + 127) / 128, 128, 0, STREAM>>>(part, grid, D, dgamma, dbeta, accumulate);
+    return check_launch("ln_param_grad_reduce_kernel");
+}

@@ -1,0 +1,299 @@
+"""GPU parity tests of the individual C-ABI kernels against plain fp32 torch / the oracle (tests only)."""
+import math
+
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+from oracle import mae_oracle as O  # noqa: E402  (checker only)
+
+
+def dev():
+    return torch.device("cuda:0")
+
+
+def rel_err(a, b):
+    a, b = a.float(), b.float()
+    return ((a - b).norm() / b.norm().clamp_min(1e-20)).item()
+
+
+# ---------------------------------------------------------------------------------------------- GEMM
+@pytest.mark.parametrize("M,N,K", [(128, 256, 64), (256, 512, 512), (100, 768, 768), (394, 2304, 768), (1000, 192, 1024), (12800, 768, 3072)])
+@pytest.mark.parametrize("bn", [0, 64, 128, 192, 256])
+def test_gemm_nt_bias(M, N, K, bn):
+    from ssl4polyp_b200 import ops
+    g = torch.Generator(device="cpu").manual_seed(M + N + K)
+    a = torch.randn(M, K, generator=g).to(dev()).bfloat16()
+    w = (torch.randn(N, K, generator=g) / math.sqrt(K)).to(dev()).bfloat16()
+    bias = torch.randn(N, generator=g).to(dev())
+    ref = a.float() @ w.float().t() + bias
+    out = ops.gemm(a, w, ops.GEMM_NT, ops.EPI_BIAS_BF16, bias=bias, force_bn=bn)
+    assert rel_err(out, ref) < 1e-2, rel_err(out, ref)
+    out32 = ops.gemm(a, w, ops.GEMM_NT, ops.EPI_BIAS_F32, bias=bias, force_bn=bn)
+    assert rel_err(out32, ref) < 2e-3, rel_err(out32, ref)
+
+
+def test_gemm_nt_gelu_residual():
+    from ssl4polyp_b200 import ops
+    M, N, K = 394, 2048, 512
+    a = torch.randn(M, K, device=dev()).bfloat16()
+    w = (torch.randn(N, K, device=dev()) / math.sqrt(K)).bfloat16()
+    bias = torch.randn(N, device=dev())
+    h_ref = a.float() @ w.float().t() + bias
+    h, g = ops.gemm(a, w, ops.GEMM_NT, ops.EPI_BIAS_GELU_BF16, bias=bias)
+    assert rel_err(h, h_ref) < 1e-2
+    assert rel_err(g, F.gelu(h_ref)) < 1e-2
+    res = torch.randn(M, N, device=dev())
+    out = ops.gemm(a, w, ops.GEMM_NT, ops.EPI_BIAS_RESIDUAL_F32, bias=bias, aux=res)
+    assert rel_err(out, h_ref + res) < 2e-3
+
+
+@pytest.mark.parametrize("M,N,K", [(128, 64, 64), (394, 512, 2048), (100, 768, 2304), (12800, 768, 3072)])
+@pytest.mark.parametrize("bn", [0, 64, 128, 192, 256])
+def test_gemm_nn_dgrad(M, N, K, bn):
+    from ssl4polyp_b200 import ops
+    dy = torch.randn(M, K, device=dev()).bfloat16()
+    w = (torch.randn(K, N, device=dev()) / math.sqrt(K)).bfloat16()          # [K=out_features, N=in_features]
+    ref = dy.float() @ w.float()
+    out = ops.gemm(dy, w, ops.GEMM_NN, ops.EPI_BIAS_BF16, force_bn=bn)
+    assert rel_err(out, ref) < 1e-2, rel_err(out, ref)
+    h = torch.randn(M, N, device=dev()).bfloat16()
+    out2 = ops.gemm(dy, w, ops.GEMM_NN, ops.EPI_DGELU_BF16, aux=h, force_bn=bn)
+    x = h.float()
+    dgelu = 0.5 * (1 + torch.erf(x / math.sqrt(2))) + x * torch.exp(-0.5 * x * x) / math.sqrt(2 * math.pi)
+    assert rel_err(out2, ref * dgelu) < 1e-2
+
+
+@pytest.mark.parametrize("M,N,K", [(128, 64, 64), (768, 768, 100), (2304, 768, 394), (512, 2048, 12800), (768, 3072, 1000)])
+@pytest.mark.parametrize("splits", [1, 3, 0])
+@pytest.mark.parametrize("bn", [0, 64, 256])
+def test_gemm_tn_wgrad(M, N, K, splits, bn):
+    from ssl4polyp_b200 import ops
+    dy = torch.randn(K, M, device=dev()).bfloat16()       # [tokens, out_features]
+    x = torch.randn(K, N, device=dev()).bfloat16()        # [tokens, in_features]
+    ref = dy.float().t() @ x.float()
+    s = splits if splits > 0 else ops.pick_splits(M, N, K)
+    out = ops.gemm(dy, x, ops.GEMM_TN, ops.EPI_PARTIAL_F32, splits=s, force_bn=bn)
+    assert rel_err(out, ref) < 2e-3, (rel_err(out, ref), s)
+    acc = torch.ones(M, N, device=dev())
+    ops.gemm(dy, x, ops.GEMM_TN, ops.EPI_PARTIAL_F32, splits=s, accumulate_into=acc, force_bn=bn)
+    assert rel_err(acc, ref + 1) < 2e-3
+
+
+def test_gemm_strided_views():
+    """A operand as a row-strided view (qkv slices), C as a strided view."""
+    from ssl4polyp_b200 import ops
+    M, K, N = 300, 512, 256
+    big = torch.randn(M, 3 * K, device=dev()).bfloat16()
+    a = big[:, K:2 * K]
+    w = (torch.randn(N, K, device=dev()) / math.sqrt(K)).bfloat16()
+    outbig = torch.zeros(M, 2 * N, device=dev(), dtype=torch.bfloat16)
+    ops.gemm(a, w, ops.GEMM_NT, ops.EPI_BIAS_BF16, out=outbig[:, N:])
+    assert rel_err(outbig[:, N:], a.float() @ w.float().t()) < 1e-2
+    assert outbig[:, :N].abs().max().item() == 0
+
+
+# ---------------------------------------------------------------------------------------------- masking / tokens
+@pytest.mark.parametrize("N,L,ratio", [(4, 196, 0.75), (256, 196, 0.75), (3, 16, 0.75), (5, 196, 0.6), (2, 1024, 0.5)])
+def test_mask_from_noise_bit_exact(N, L, ratio):
+    from ssl4polyp_b200 import ops
+    noise = torch.rand(N, L, generator=torch.Generator().manual_seed(N * L))
+    keep = O.len_keep_of(L, ratio)
+    ids_keep_o, mask_o, ids_restore_o = O.masking_from_noise(noise, ratio)
+    ids_restore, mask, ids_keep = ops.mask_from_noise(noise.to(dev()), keep)
+    assert ids_restore.dtype == torch.int64 and mask.dtype == torch.float32
+    assert torch.equal(ids_restore.cpu(), ids_restore_o)
+    assert torch.equal(mask.cpu(), mask_o)
+    assert torch.equal(ids_keep.cpu(), ids_keep_o)
+
+
+def test_mask_from_noise_ties_golden():
+    from ssl4polyp_b200 import ops
+    import os
+    gold = torch.load(os.path.join(os.path.dirname(__file__), "golden", "mae_golden.pt"))["ties"]
+    ids_restore, mask, ids_keep = ops.mask_from_noise(gold["noise"].to(dev()), gold["ids_keep"].shape[1])
+    assert torch.equal(ids_restore.cpu(), gold["ids_restore"])
+    assert torch.equal(mask.cpu(), gold["mask"])
+    assert torch.equal(ids_keep.cpu(), gold["ids_keep"])
+
+
+@pytest.mark.parametrize("N,size", [(2, 224), (3, 64)])
+def test_patchify_roundtrip(N, size):
+    from ssl4polyp_b200 import ops
+    imgs = torch.randn(N, 3, size, size)
+    x = ops.patchify(imgs.to(dev()), 16)
+    assert torch.equal(x.cpu(), O.patchify(imgs, 16))
+    back = ops.unpatchify(x, 16)
+    assert torch.equal(back.cpu(), imgs)
+
+
+def test_im2col_assemble_gather():
+    from ssl4polyp_b200 import ops
+    N, L, D, keep = 3, 196, 768, 49
+    imgs = torch.randn(N, 3, 224, 224)
+    noise = torch.rand(N, L)
+    ids_keep, _, ids_restore = O.masking_from_noise(noise, 0.75)
+    cols = ops.im2col_patches(imgs.to(dev()), ids_keep.to(dev()), 16)
+    ref = imgs.reshape(N, 3, 14, 16, 14, 16).permute(0, 2, 4, 1, 3, 5).reshape(N, L, 768)   # (c, pi, qi) column order
+    ref = torch.gather(ref, 1, ids_keep.unsqueeze(-1).expand(-1, -1, 768)).reshape(N * keep, 768)
+    assert torch.equal(cols.float().cpu(), ref.bfloat16().float())
+    allcols = ops.im2col_patches(imgs.to(dev()), None, 16)
+    assert torch.equal(allcols.float().cpu(), imgs.reshape(N, 3, 14, 16, 14, 16).permute(0, 2, 4, 1, 3, 5).reshape(N * L, 768).bfloat16().float())
+    tok = torch.randn(N * keep, D); pos = torch.randn(1 + L, D); cls = torch.randn(D)
+    x = ops.assemble_tokens(tok.to(dev()), ids_keep.to(dev()), pos.to(dev()), cls.to(dev()), N, keep, D)
+    ref_x = torch.cat([(cls + pos[0]).expand(N, 1, D), tok.reshape(N, keep, D) + pos[1:][ids_keep]], dim=1)
+    assert torch.allclose(x.cpu(), ref_x, atol=1e-6)
+    xs = torch.randn(N, L, D)
+    got = ops.gather_tokens(xs.to(dev()), ids_keep.to(dev()))
+    assert torch.equal(got.cpu(), torch.gather(xs, 1, ids_keep.unsqueeze(-1).expand(-1, -1, D)))
+    dx = torch.randn(N, keep + 1, D)
+    dcls = torch.zeros(D, device=dev())
+    dtok = ops.assemble_tokens_bwd(dx.to(dev()), dcls)
+    assert torch.equal(dtok.float().cpu(), dx[:, 1:].reshape(N * keep, D).bfloat16().float())
+    assert torch.allclose(dcls.cpu(), dx[:, 0].sum(0), atol=1e-5)
+
+
+def test_decoder_unshuffle_fwd_bwd():
+    from ssl4polyp_b200 import ops
+    N, L, Dd, keep = 3, 196, 512, 49
+    noise = torch.rand(N, L)
+    ids_keep, mask, ids_restore = O.masking_from_noise(noise, 0.75)
+    y = torch.randn(N, keep + 1, Dd).bfloat16()
+    mt = torch.randn(Dd); dpos = torch.randn(1 + L, Dd)
+    x = ops.decoder_unshuffle_fwd(y.to(dev()), mt.to(dev()), ids_restore.to(dev()), dpos.to(dev()))
+    yf = y.float()
+    body = torch.cat([yf[:, 1:], mt.expand(N, L - keep, Dd)], dim=1)
+    body = torch.gather(body, 1, ids_restore.unsqueeze(-1).expand(-1, -1, Dd))
+    ref = torch.cat([yf[:, :1], body], dim=1) + dpos
+    assert torch.allclose(x.cpu(), ref, atol=1e-6)
+    dx = torch.randn(N, 1 + L, Dd)
+    dmt = torch.zeros(Dd, device=dev())
+    dy = ops.decoder_unshuffle_bwd(dx.to(dev()), ids_keep.to(dev()), mask.to(dev()), dmt)
+    ref_dy = torch.cat([dx[:, :1], torch.gather(dx[:, 1:], 1, ids_keep.unsqueeze(-1).expand(-1, -1, Dd))], dim=1)
+    assert torch.equal(dy.float().cpu(), ref_dy.bfloat16().float())
+    ref_dmt = (dx[:, 1:] * mask.unsqueeze(-1)).sum((0, 1))
+    assert torch.allclose(dmt.cpu(), ref_dmt, atol=1e-3, rtol=1e-4)
+
+
+# ---------------------------------------------------------------------------------------------- LayerNorm
+@pytest.mark.parametrize("M,D", [(100, 768), (394, 512), (50, 1024), (37, 64), (20, 32)])
+def test_layernorm_fwd_bwd(M, D):
+    from ssl4polyp_b200 import ops
+    x = (torch.randn(M, D) * 2 + 0.5).requires_grad_(True)
+    gamma = (1 + 0.1 * torch.randn(D)).requires_grad_(True)
+    beta = (0.1 * torch.randn(D)).requires_grad_(True)
+    y_ref = F.layer_norm(x, (D,), gamma, beta, 1e-6)
+    y, mean, rstd = ops.layernorm_fwd(x.detach().to(dev()), gamma.detach().to(dev()), beta.detach().to(dev()), 1e-6)
+    assert rel_err(y.cpu(), y_ref.detach()) < 5e-3
+    dy = torch.randn(M, D).bfloat16()
+    y_ref.backward(dy.float())
+    res = torch.randn(M, D)
+    dgamma = torch.zeros(D, device=dev()); dbeta = torch.zeros(D, device=dev())
+    dx, dxb = ops.layernorm_bwd(dy.to(dev()), x.detach().to(dev()), mean, rstd, gamma.detach().to(dev()), res.to(dev()).clone(), dgamma, dbeta)
+    assert rel_err(dx.cpu(), x.grad + res) < 1e-4
+    assert rel_err(dxb.cpu(), x.grad + res) < 5e-3
+    assert rel_err(dgamma.cpu(), gamma.grad) < 1e-4
+    assert rel_err(dbeta.cpu(), beta.grad) < 1e-4
+    dx2, none = ops.layernorm_bwd(dy.to(dev()), x.detach().to(dev()), mean, rstd, gamma.detach().to(dev()), None, dgamma, dbeta, want_bf16=False, accumulate=True)
+    assert none is None and rel_err(dx2.cpu(), x.grad) < 1e-4
+    assert rel_err(dgamma.cpu(), 2 * gamma.grad) < 1e-4
+
+
+# ---------------------------------------------------------------------------------------------- attention
+@pytest.mark.parametrize("B,T,H,hd", [(2, 50, 12, 64), (2, 197, 16, 32), (1, 197, 12, 64), (3, 5, 2, 32), (2, 17, 2, 32), (2, 64, 4, 64)])
+def test_attention_fwd_bwd(B, T, H, hd):
+    from ssl4polyp_b200 import ops
+    qkv = torch.randn(B, T, 3, H, hd).bfloat16()
+    scale = hd ** -0.5
+    q, k, v = [t.float().requires_grad_(True) for t in qkv.permute(2, 0, 3, 1, 4)]
+    a = ((q @ k.transpose(-2, -1)) * scale).softmax(-1)
+    o_ref = (a @ v).transpose(1, 2).reshape(B, T, H * hd)
+    qkv_d = qkv.reshape(B * T, 3 * H * hd).to(dev())
+    out, lse = ops.attention_fwd(qkv_d, B, T, H, hd, scale)
+    assert rel_err(out.cpu().reshape(B, T, H * hd), o_ref.detach()) < 1e-2
+    lse_ref = torch.logsumexp((q @ k.transpose(-2, -1)) * scale, dim=-1)
+    assert torch.allclose(lse.cpu(), lse_ref.detach(), atol=2e-3, rtol=1e-3)
+    do = torch.randn(B, T, H * hd).bfloat16()
+    o_ref.backward(do.float())
+    dqkv = ops.attention_bwd(qkv_d, out, do.reshape(B * T, H * hd).to(dev()), lse, B, T, H, hd, scale)
+    dqkv = dqkv.cpu().float().reshape(B, T, 3, H, hd).permute(2, 0, 3, 1, 4)
+    for i, (name, t) in enumerate((("dq", q), ("dk", k), ("dv", v))):
+        assert rel_err(dqkv[i], t.grad) < 2e-2, (name, rel_err(dqkv[i], t.grad))
+
+
+# ---------------------------------------------------------------------------------------------- loss
+@pytest.mark.parametrize("norm_pix", [True, False])
+@pytest.mark.parametrize("N,size,cls_row", [(2, 224, True), (3, 64, False)])
+def test_masked_mse(norm_pix, N, size, cls_row):
+    from ssl4polyp_b200 import ops
+    L = (size // 16) ** 2
+    imgs = torch.randn(N, 3, size, size)
+    _, mask, _ = O.masking_from_noise(torch.rand(N, L), 0.75)
+    pred_full = torch.randn(N, L + (1 if cls_row else 0), 768)
+    pred = (pred_full[:, 1:] if cls_row else pred_full).clone().requires_grad_(True)
+    loss_ref = O.masked_mse(imgs, pred, mask, norm_pix)
+    loss_ref.backward()
+    loss, ws = ops.masked_mse_fwd(imgs.to(dev()), pred_full.to(dev()), cls_row, mask.to(dev()), norm_pix, 16)
+    assert abs(loss.item() - loss_ref.item()) / abs(loss_ref.item()) < 1e-5
+    gout = torch.tensor(0.5, device=dev())
+    dpred = ops.masked_mse_bwd(imgs.to(dev()), pred_full.to(dev()), cls_row, mask.to(dev()), norm_pix, 16, gout, ws)
+    got = dpred.float().cpu()
+    if cls_row:
+        assert got[:, 0].abs().max().item() == 0
+        got = got[:, 1:]
+    assert rel_err(got, 0.5 * pred.grad) < 5e-3
+    assert got[mask == 0].abs().max().item() == 0
+
+
+# ---------------------------------------------------------------------------------------------- misc
+def test_colsum_cast_adamw():
+    from ssl4polyp_b200 import ops
+    x = torch.randn(1000, 768).bfloat16()
+    out = ops.colsum(x.to(dev()))
+    assert rel_err(out.cpu(), x.float().sum(0)) < 1e-4
+    src = torch.randn(100003)
+    assert torch.equal(ops.cast_bf16(src.to(dev())).float().cpu(), src.bfloat16().float())
+    n = 256 * 40
+    p = torch.randn(n); g = torch.randn(n)
+    flags = (torch.arange(n // 256) % 2).to(torch.uint8)
+    ref_p = torch.nn.Parameter(p.clone())
+    opt = torch.optim.AdamW([{"params": [ref_p]}], lr=1e-2, betas=(0.9, 0.95), weight_decay=0.0)
+    pd, md, vd = p.to(dev()), torch.zeros(n, device=dev()), torch.zeros(n, device=dev())
+    pb = torch.empty(n, dtype=torch.bfloat16, device=dev())
+    bad = torch.zeros(1, dtype=torch.int32, device=dev())
+    wd = 0.05
+    for step in (1, 2, 3):
+        ref_p.grad = g.clone()
+        # reference with per-chunk weight decay: decoupled decay applied manually
+        with torch.no_grad():
+            decay = flags.repeat_interleave(256).float()
+            ref_p.mul_(1 - 1e-2 * wd * decay)
+        opt.step()
+        ops.adamw_flat(pd, g.to(dev()), md, vd, pb, flags.to(dev()), 1e-2, 0.9, 0.95, 1e-8, wd, step, nonfinite=bad)
+    assert rel_err(pd.cpu(), ref_p.detach()) < 1e-5
+    assert torch.equal(pb.float().cpu(), pd.cpu().bfloat16().float())
+    assert bad.item() == 0
+    gbad = g.clone(); gbad[5] = float("nan")
+    ops.adamw_flat(pd, gbad.to(dev()), md, vd, pb, flags.to(dev()), 1e-2, 0.9, 0.95, 1e-8, wd, 4, nonfinite=bad)
+    assert bad.item() >= 1
+
+
+def test_pool_head():
+    from ssl4polyp_b200 import ops
+    N, T, D, ncls = 4, 197, 768, 2
+    xn = torch.randn(N, T, D).bfloat16()
+    W = torch.randn(ncls, D) * 0.05; b = torch.randn(ncls)
+    for spatial in (False, True):
+        xf = xn.float().requires_grad_(True); Wr = W.clone().requires_grad_(True); br = b.clone().requires_grad_(True)
+        pooled = xf[:, 1:].mean(1) if spatial else xf[:, 0]
+        ref = F.linear(pooled, Wr, br)
+        logits = ops.pool_head_fwd(xn.to(dev()), W.to(dev()), b.to(dev()), N, T, D, spatial)
+        assert torch.allclose(logits.cpu(), ref.detach(), atol=1e-3, rtol=1e-3)
+        dl = torch.randn(N, ncls)
+        ref.backward(dl)
+        dW = torch.zeros(ncls, D, device=dev()); db = torch.zeros(ncls, device=dev())
+        dxn = ops.pool_head_bwd(xn.to(dev()), W.to(dev()), dl.to(dev()), dW, db, N, T, D, spatial)
+        assert rel_err(dxn.cpu().reshape(N, T, D), xf.grad) < 1e-2
+        assert rel_err(dW.cpu(), Wr.grad) < 1e-4 and rel_err(db.cpu(), br.grad) < 1e-5
