@@ -1,0 +1,325 @@
+#!/usr/bin/env python
+"""bench.py — MAE ViT-B/16 pretraining step throughput (images/s) on N B200s, one process per GPU.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--batch B] [--impl b200|reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P \
+        bench.py --gpus N --steps K --warmup W
+
+Workload (BASELINE.json configs[1]; [2] at N=8): MAE ViT-B/16, mask_ratio 0.75, norm_pix_loss, batch 256 per GPU,
+synthetic 224x224 fp32 images, AdamW (blr 1.5e-4, wd 0.05, betas 0.9/0.95).  One step = forward + loss + backward +
+bucketed gradient all-reduce (N>1) + fused AdamW.  Prints ONE JSON line (rank 0):
+  value    images/s with the batch already resident in HBM (CUDA events, max over ranks)
+  e2e      images/s through PretrainEngine.step with the batch copied from pinned host memory every step and the
+           loss read back to the host every step (copies inside the timed region)
+  roofline tcgen05 GEMM kernel: algorithmic FLOPs of every GEMM launch of one step / their CUDA-event durations,
+           against MEASURED_PEAKS.json (bf16 sustained: the kernel is timed inside a long step)
+  cpu_baseline  the CPU oracle (fp32 port of the reference step; the reference itself needs timm==0.4.12 which is
+           not installable here) timed on this box's host cores on a bounded sample (N=1 only)
+`--impl reference` times that CPU port alone with all host threads (rank 0 only) and prints the same line shape.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+F_STEP_GFLOP_PER_IMG = {"base": 58.164, "large": 123.839}     # 3 x forward matmul FLOPs
+METRIC = "MAE ViT-B/16 pretrain img/s @1/2/4/8 B200; % bf16 tensor-core peak"
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--batch", type=int, default=256, help="images per GPU per step")
+    ap.add_argument("--model", default="base", choices=["base", "large"])
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--cpu-batch", type=int, default=8, help="batch of the CPU baseline sample (BASELINE configs[0])")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+def peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            p = json.load(f)
+        return {"tflops_burst": p.get("bf16_tflops", 1590.0), "tflops_sustained": p.get("bf16_tflops_sustained", 1400.0),
+                "hbm_gbs": p.get("hbm_gbs", 6650.0), "source": "measured"}
+    return {"tflops_burst": 1590.0, "tflops_sustained": 1400.0, "hbm_gbs": 6650.0, "source": "fallback"}
+
+
+# ------------------------------------------------------------------------------------------------------------
+# clocks: nvidia-smi sampled during the timed region
+# ------------------------------------------------------------------------------------------------------------
+class ClockSampler:
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.idx = gpu_index
+        self.proc = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.idx), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except OSError:
+            self.proc = None
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            out, _ = self.proc.communicate(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+            out, _ = self.proc.communicate()
+        sm, mx, reasons, power = [], [], set(), []
+        for line in out.strip().splitlines():
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2])); power.append(float(f[3]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        return {"sm_mhz": statistics.median(sm), "sm_max_mhz": max(mx), "reasons": sorted(reasons),
+                "power_w_max": max(power), "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------------------------------------
+# CPU port of the reference step (oracle) — the baseline arm
+# ------------------------------------------------------------------------------------------------------------
+def cpu_step_fn(model_name: str, batch: int):
+    import torch
+    from oracle import mae_oracle as O            # bench.py's cpu_baseline / --impl reference legs only
+    cfg = O.MAEConfig(norm_pix_loss=True) if model_name == "base" else O.MAEConfig(embed_dim=1024, depth=24, num_heads=16, norm_pix_loss=True)
+    sd = O.init_state_dict(cfg, seed=0)
+    params = {k: v.clone().requires_grad_(k not in ("pos_embed", "decoder_pos_embed")) for k, v in sd.items()}
+    groups = O.weight_decay_groups(params.items(), 0.05)
+    opt = torch.optim.AdamW(groups, lr=1.5e-4 * batch / 256, betas=(0.9, 0.95))
+    imgs = torch.randn(batch, 3, 224, 224, generator=torch.Generator().manual_seed(1000))
+
+    def step():
+        noise = torch.rand(batch, cfg.num_patches)
+        loss, _, _ = O.mae_forward(params, imgs, noise, 0.75, cfg)
+        opt.zero_grad(set_to_none=True)
+        loss.backward()
+        opt.step()
+        return float(loss.detach())
+    return step
+
+
+def run_cpu(model_name, batch, steps, warmup, budget_s=None):
+    import torch
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    step = cpu_step_fn(model_name, batch)
+    for _ in range(warmup):
+        step()
+    times = []
+    t_begin = time.perf_counter()
+    for _ in range(steps):
+        t0 = time.perf_counter()
+        step()
+        times.append(time.perf_counter() - t0)
+        if budget_s is not None and time.perf_counter() - t_begin > budget_s:
+            break
+    total = sum(times)
+    return {"img_s": batch * len(times) / total, "ms_per_step": 1e3 * total / len(times), "steps": len(times), "cores": cores}
+
+
+def reference_arm(args):
+    """`--impl reference`: the reference's CPU fp32 path for the same step (its own code needs timm==0.4.12, absent and
+    not installable offline, so this is the oracle port of it — cpu_baseline.kind == "port"), all host threads."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    r = run_cpu(args.model, args.cpu_batch, args.steps, args.warmup)
+    sample = (f"{r['steps']} steps of MAE ViT-{'B' if args.model == 'base' else 'L'}/16 fwd+loss+bwd+AdamW, batch {args.cpu_batch}, "
+              f"fp32, torch CPU, {r['cores']} threads")
+    line = {
+        "impl": "reference", "metric": METRIC, "value": r["img_s"], "unit": "images/s", "n_gpus": args.gpus,
+        "steps": r["steps"], "warmup": args.warmup, "ms_per_step": r["ms_per_step"], "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"MAE ViT-{'B' if args.model == 'base' else 'L'}/16 pretraining step, mask_ratio 0.75, norm_pix_loss, "
+                               f"CPU sample batch {args.cpu_batch} (BASELINE configs[0] shape; the B200 arm runs batch {args.batch}/GPU)"},
+        "cpu_baseline": {"value": r["img_s"], "unit": "images/s", "cores": r["cores"], "kind": "port", "sample": sample},
+        "e2e": {"value": r["img_s"], "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def b200_arm(args):
+    import torch
+    import torch.distributed as dist
+    from ssl4polyp_b200 import _lib, models_mae, ops
+    from ssl4polyp_b200.engine import PretrainEngine
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (the B200 arm has no CPU fallback; use --impl reference for the CPU port)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    assert world == args.gpus or world == 1, f"--gpus {args.gpus} but WORLD_SIZE={world}"
+
+    B = args.batch
+    torch.manual_seed(0)                                              # same init on every rank (DDP would broadcast)
+    ctor = models_mae.mae_vit_base_patch16 if args.model == "base" else models_mae.mae_vit_large_patch16
+    model = ctor(norm_pix_loss=True).to(dev).train()
+    lr = 1.5e-4 * (B * world) / 256                                   # main_pretrain.py:201-204
+    eng = PretrainEngine(model, lr=lr, weight_decay=0.05, betas=(0.9, 0.95), mask_ratio=0.75)
+    torch.manual_seed(0 + rank)                                       # masking noise stream: seed + rank (main_pretrain.py:147)
+
+    g = torch.Generator().manual_seed(1000 + rank)
+    host = [torch.randn(B, 3, 224, 224, generator=g).pin_memory() for _ in range(2)]
+    resident = [h.to(dev) for h in host]                              # 2 x 154 MB at B=256: each larger than the 126 MB L2
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(ms: float) -> float:
+        if world == 1:
+            return ms
+        t = torch.tensor([ms], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    # ---- leg 1: inputs resident in HBM -------------------------------------------------------------------
+    for i in range(args.warmup):
+        eng.step(resident[i % 2])
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    l0 = _lib.launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(args.steps):
+        loss = eng.step(resident[i % 2])
+    e1.record()
+    barrier()
+    launches = _lib.launch_count() - l0
+    clocks = sampler.stop() if rank == 0 else None
+    ms = max_over_ranks(e0.elapsed_time(e1))
+    ms_per_step = ms / args.steps
+    value = B * world * args.steps / (ms / 1e3)
+    loss_val = float(loss.item())
+    nonfinite = eng.nonfinite_count()
+
+    # ---- leg 2: end to end — pinned host batch -> H2D every step, loss -> host every step --------------------
+    e2e = None
+    if not args.no_e2e:
+        copy_stream = torch.cuda.Stream(device=dev)
+        bufs = [torch.empty_like(resident[0]) for _ in range(2)]
+        ready = [torch.cuda.Event(), torch.cuda.Event()]
+        consumed = [torch.cuda.Event(), torch.cuda.Event()]
+
+        def prefetch(i):
+            with torch.cuda.stream(copy_stream):
+                copy_stream.wait_event(consumed[i % 2])
+                bufs[i % 2].copy_(host[i % 2], non_blocking=True)
+                ready[i % 2].record(copy_stream)
+
+        def e2e_loop(n):
+            for b in consumed:
+                b.record(torch.cuda.current_stream())
+            prefetch(0)
+            out = 0.0
+            for i in range(n):
+                if i + 1 < n:
+                    prefetch(i + 1)
+                torch.cuda.current_stream().wait_event(ready[i % 2])
+                l = eng.step(bufs[i % 2])
+                consumed[i % 2].record(torch.cuda.current_stream())
+                out = float(l.item())                                  # D2H read of the step's result, every step
+            return out
+
+        e2e_loop(max(2, min(args.warmup, 3)))
+        barrier()
+        e0.record()
+        e2e_loop(args.steps)
+        e1.record()
+        barrier()
+        ms2 = max_over_ranks(e0.elapsed_time(e1))
+        e2e = {"value": B * world * args.steps / (ms2 / 1e3), "unit": "images/s",
+               "h2d_bytes_per_step": int(host[0].numel() * 4 * world), "d2h_bytes_per_step": 4 * world,
+               "ms_per_step": ms2 / args.steps}
+
+    # ---- roofline leg: every GEMM launch of one step timed with CUDA events on the launching stream ---------
+    pk = peaks()
+    ops.GEMM_PROFILE = []
+    eng.step(resident[0])
+    torch.cuda.synchronize()
+    prof, ops.GEMM_PROFILE = ops.GEMM_PROFILE, None
+    g_ms = sum(a.elapsed_time(b) for a, b, _, _ in prof)
+    g_flops = sum(f for _, _, f, _ in prof)
+    achieved = g_flops / (g_ms / 1e3) / 1e12 if g_ms > 0 else 0.0
+    step_tflops = F_STEP_GFLOP_PER_IMG[args.model] * 1e9 * B / (ms_per_step / 1e3) / 1e12
+    roofline = {"bound": "tensor", "kernel": "gemm_tcgen05_kernel", "achieved": achieved, "peak": pk["tflops_sustained"],
+                "unit": "TFLOP/s", "frac": achieved / pk["tflops_sustained"], "traffic": None,
+                "peak_source": f"{pk['source']} (bf16 sustained; burst {pk['tflops_burst']})",
+                "gemm_launches_per_step": len(prof), "gemm_ms_per_step": g_ms, "gemm_share_of_step": g_ms / ms_per_step,
+                "step_tflops_per_gpu": step_tflops, "step_frac_of_peak": step_tflops / pk["tflops_sustained"]}
+
+    # ---- CPU baseline (rank 0, N=1 only): bounded sample of the same step on the host cores -----------------
+    cpu = None
+    if world == 1 and not args.no_cpu_baseline:
+        r = run_cpu(args.model, args.cpu_batch, steps=4, warmup=1, budget_s=25.0)
+        cpu = {"value": r["img_s"], "unit": "images/s", "cores": r["cores"], "kind": "port",
+               "sample": f"{r['steps']} steps, batch {args.cpu_batch}, fp32 fwd+loss+bwd+AdamW of the same model (oracle/mae_oracle.py), "
+                         f"{r['ms_per_step']:.0f} ms/step"}
+
+    if rank == 0:
+        name = "B" if args.model == "base" else "L"
+        line = {
+            "metric": METRIC, "value": value, "unit": "images/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "bf16", "data": "synthetic",
+            "config": {"workload": f"MAE ViT-{name}/16 pretraining step (fwd+loss+bwd+allreduce+AdamW), mask_ratio 0.75, norm_pix_loss, "
+                                   f"batch {B}/GPU, 224x224 fp32 images",
+                       "global_batch": B * world, "parallelism": f"dp{world}",
+                       "l2_policy": "two alternating 154 MB input batches (> 126 MB L2); per-step activations ~14 GB"},
+            "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu,
+            "loss": loss_val, "nonfinite_grad_blocks": nonfinite,
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse()
+    if args.impl == "reference":
+        reference_arm(args)
+    else:
+        b200_arm(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,232 @@
+"""Fused data-parallel training step for the MAE / classifier hot path.
+
+What `engine_pretrain.train_one_epoch` does per iteration in the reference
+(/root/reference/src/ssl4polyp/models/mae/engine_pretrain.py:47-81: lr schedule, autocast forward, backward through DDP,
+~600 `.any()` host syncs of `detect_grad_anomalies`, GradScaler step, `cuda.synchronize`, scalar all-reduce) is done here as:
+
+  forward  : vit_core.mae_fwd on our kernels (bf16 tensor-core operands, fp32 residual/statistics/loss)
+  backward : vit_core.mae_bwd writing weight gradients straight into ONE flat fp32 arena laid out like the
+             parameter arena (param_store.ParamStore)
+  DP       : the arena is cut into buckets in reverse-forward order; the moment the last gradient of a bucket has been
+             enqueued an event is recorded and NCCL all-reduces that bucket on a side stream while backward continues
+             (one process per GPU; the SUM is turned into the mean by `grad_scale = 1/world` inside the optimiser)
+  update   : ops.adamw_flat — one pass over p/g/m/v for all ~250 tensors, decoupled weight decay by timm's rule
+             (ndim == 1 or name.endswith('.bias') -> no decay; main_pretrain.py:217, timm optim_factory.add_weight_decay),
+             bf16 shadow weights refreshed in the same pass, non-finite gradients counted on the device
+             (util/misc.py:387-400) — no host sync anywhere in the step.
+"""
+from __future__ import annotations
+
+import math
+
+import torch
+import torch.distributed as dist
+
+from . import ops, vit_core
+from .param_store import ALIGN
+
+
+class ArenaSink(vit_core.GradSink):
+    def __init__(self, engine: "TrainEngine"):
+        self.e = engine
+        self.accumulate = False
+
+    def buf(self, name, like):
+        return self.e.grad_views[name], self.accumulate
+
+    def ready(self, name):
+        self.e._on_ready(name)
+
+
+class TrainEngine:
+    def __init__(self, model, lr: float, weight_decay: float = 0.05, betas=(0.9, 0.95), eps: float = 1e-8,
+                 process_group=None, bucket_mb: float = 64.0, no_decay_rule=None):
+        self.model = model
+        store = model._store
+        store.sync()
+        self.store = store
+        self.lr, self.wd, self.betas, self.eps = lr, weight_decay, betas, eps
+        dev = store.flat.device
+        self.device = dev
+        n = store.total
+        self.grads = torch.zeros(n, dtype=torch.float32, device=dev)
+        self.exp_avg = torch.zeros(n, dtype=torch.float32, device=dev)
+        self.exp_avg_sq = torch.zeros(n, dtype=torch.float32, device=dev)
+        self.nonfinite = torch.zeros(1, dtype=torch.int32, device=dev)
+        self.t = 0
+        self.grad_views = {}
+        flags = torch.zeros(n // ALIGN, dtype=torch.uint8)
+        rule = no_decay_rule or (lambda name, p: p.ndim == 1 or name.endswith(".bias"))
+        for name, (a, cnt) in store.offsets.items():
+            p = store.params[name]
+            self.grad_views[name] = self.grads[a:a + cnt].view(p.shape)
+            if p.requires_grad and not rule(name, p):
+                flags[a // ALIGN:(a + cnt + ALIGN - 1) // ALIGN] = 1
+        self.wd_flags = flags.to(dev)
+        # ---- data parallel
+        self.pg = process_group
+        self.world = dist.get_world_size(process_group) if (dist.is_available() and dist.is_initialized()) else 1
+        self.comm_stream = torch.cuda.Stream(device=dev) if self.world > 1 else None
+        self._build_buckets(bucket_mb)
+        self.sink = ArenaSink(self)
+        self._pending = []
+
+    # ---- buckets: contiguous arena ranges, filled from the END of the arena (= first gradients of backward) ----
+    def _build_buckets(self, bucket_mb):
+        names = [n for n in self.store.offsets if self.store.params[n].requires_grad]
+        names.sort(key=lambda n: self.store.offsets[n][0], reverse=True)
+        limit = int(bucket_mb * (1 << 20) / 4)
+        self.buckets = []        # [start, end, {names}]
+        cur_names, cur_end, cur_start = [], None, None
+        for nme in names:
+            a, cnt = self.store.offsets[nme]
+            if cur_end is None:
+                cur_end = (a + cnt + ALIGN - 1) // ALIGN * ALIGN
+            cur_start = a
+            cur_names.append(nme)
+            if cur_end - cur_start >= limit:
+                self.buckets.append([cur_start, cur_end, set(cur_names)])
+                cur_names, cur_end = [], None
+        if cur_names:
+            self.buckets.append([cur_start, cur_end, set(cur_names)])
+        # close the gaps (frozen tensors in between): bucket i ends where bucket i-1 starts
+        for i in range(1, len(self.buckets)):
+            self.buckets[i][1] = self.buckets[i - 1][0]
+        self.bucket_of = {}
+        for i, (_, _, ns) in enumerate(self.buckets):
+            for nme in ns:
+                self.bucket_of[nme] = i
+        self._remaining = [len(b[2]) for b in self.buckets]
+        self._seen = set()
+
+    def _reset_ready(self):
+        self._remaining = [len(b[2]) for b in self.buckets]
+        self._seen.clear()
+        self._pending = []
+
+    def _on_ready(self, name):
+        if self.world == 1 or not self._reduce_now or name in self._seen:
+            return
+        i = self.bucket_of.get(name)
+        if i is None:
+            return
+        self._seen.add(name)
+        self._remaining[i] -= 1
+        if self._remaining[i] == 0:
+            self._launch_bucket(i)
+
+    def _launch_bucket(self, i):
+        a, b, _ = self.buckets[i]
+        ev = torch.cuda.Event()
+        ev.record(torch.cuda.current_stream())
+        self.comm_stream.wait_event(ev)
+        with torch.cuda.stream(self.comm_stream):
+            dist.all_reduce(self.grads[a:b], op=dist.ReduceOp.SUM, group=self.pg)
+        self._pending.append(i)
+
+    def _finish_reduce(self):
+        if self.world == 1:
+            return
+        for i, rem in enumerate(self._remaining):       # tensors whose gradient never appeared (unused parameters)
+            if rem > 0 and i not in self._pending:
+                self._launch_bucket(i)
+        torch.cuda.current_stream().wait_stream(self.comm_stream)
+
+    # ---- one optimisation step -------------------------------------------------------------------------------
+    def backward_and_step(self, run_backward, lr=None, accumulate: bool = False, do_step: bool = True):
+        """run_backward(sink) enqueues the backward; gradients are reduced across ranks as buckets complete when
+        `do_step` (the reference all-reduces on every micro-step, engine_pretrain.py:64-72; summing locally and
+        reducing once on the boundary gives the same mean with 1/accum of the traffic)."""
+        self.sink.accumulate = accumulate
+        self._reduce_now = do_step
+        self._reset_ready()
+        run_backward(self.sink)
+        if not do_step:
+            return
+        self._finish_reduce()
+        self.t += 1
+        b1, b2 = self.betas
+        ops.adamw_flat(self.store.flat, self.grads, self.exp_avg, self.exp_avg_sq, self.store.shadow, self.wd_flags,
+                       self.lr if lr is None else lr, b1, b2, self.eps, self.wd, self.t,
+                       grad_scale=1.0 / self.world, nonfinite=self.nonfinite)
+        self.store.mark_shadow_fresh()
+
+    def nonfinite_count(self) -> int:
+        """Number of optimiser blocks that saw a non-finite gradient so far (host sync: call off the hot path)."""
+        return int(self.nonfinite.item())
+
+    # ---- optimiser state in torch.optim.AdamW's layout (checkpoint hand-off, util/misc.py:306-352) -----------
+    def optimizer_state_dict(self):
+        state = {}
+        names = [n for n in self.store.offsets if self.store.params[n].requires_grad]
+        for i, nme in enumerate(names):
+            a, cnt = self.store.offsets[nme]
+            shape = self.store.params[nme].shape
+            state[i] = {"step": torch.tensor(float(self.t)),
+                        "exp_avg": self.exp_avg[a:a + cnt].view(shape).clone(),
+                        "exp_avg_sq": self.exp_avg_sq[a:a + cnt].view(shape).clone()}
+        return {"state": state, "param_names": names, "t": self.t,
+                "param_groups": [{"lr": self.lr, "betas": self.betas, "eps": self.eps, "weight_decay": self.wd}]}
+
+    def load_optimizer_state_dict(self, sd):
+        names = sd.get("param_names") or [n for n in self.store.offsets if self.store.params[n].requires_grad]
+        self.t = int(sd.get("t", 0))
+        for i, nme in enumerate(names):
+            st = sd["state"].get(i)
+            if st is None or nme not in self.store.offsets:
+                continue
+            a, cnt = self.store.offsets[nme]
+            self.exp_avg[a:a + cnt].copy_(st["exp_avg"].reshape(-1))
+            self.exp_avg_sq[a:a + cnt].copy_(st["exp_avg_sq"].reshape(-1))
+            if not sd.get("t"):
+                self.t = int(float(st["step"]))
+
+
+class PretrainEngine(TrainEngine):
+    """MAE pretraining step: `step(imgs) -> loss` (device scalar, this rank's masked-patch mean: models_mae.py:213)."""
+
+    def __init__(self, model, lr, weight_decay=0.05, betas=(0.9, 0.95), mask_ratio=0.75, **kw):
+        super().__init__(model, lr, weight_decay, betas, **kw)
+        self.mask_ratio = mask_ratio
+        self._one = torch.ones((), dtype=torch.float32, device=self.device)
+
+    def step(self, imgs, lr=None, noise=None, accum_iter: int = 1, micro_index: int = 0):
+        m = self.model
+        if noise is None:
+            noise = torch.rand(imgs.shape[0], m.patch_embed.num_patches, device=imgs.device)   # models_mae.py:132
+        loss, pred_full, mask, ids_restore, sv = vit_core.mae_fwd(
+            self.store, m._dims, imgs, noise, m._len_keep(self.mask_ratio), m.norm_pix_loss, True)
+        dloss = self._one if accum_iter == 1 else self._one / accum_iter
+        last = micro_index == accum_iter - 1
+        self.backward_and_step(lambda sink: vit_core.mae_bwd(self.store, sink, m._dims, sv, dloss), lr=lr,
+                               accumulate=micro_index > 0, do_step=last)
+        return loss
+
+
+class ClassifierEngine(TrainEngine):
+    """Fine-tune step (train_classification.py:4525-4546): logits -> BCE-with-logits on logit1-logit0 (2 classes,
+    :3347-3374) or cross-entropy -> backward -> AdamW.  The loss over B x ncls scalars stays in torch."""
+
+    def __init__(self, model, lr, weight_decay=0.05, betas=(0.9, 0.999), pos_weight=None, **kw):
+        super().__init__(model, lr, weight_decay, betas, **kw)
+        self.pos_weight = pos_weight
+
+    def step(self, imgs, target, lr=None):
+        m = self.model
+        logits, sv = vit_core.classifier_fwd(self.store, m._dims, imgs, m.out_token == "spatial", True)
+        lg = logits.detach().requires_grad_(True)
+        if logits.shape[1] == 2:
+            z = lg[:, 1] - lg[:, 0]
+            loss = torch.nn.functional.binary_cross_entropy_with_logits(z, target.float(), pos_weight=self.pos_weight)
+        else:
+            loss = torch.nn.functional.cross_entropy(lg, target)
+        (dlogits,) = torch.autograd.grad(loss, lg)
+        self.backward_and_step(lambda sink: vit_core.classifier_bwd(self.store, sink, m._dims, sv, dlogits.contiguous()), lr=lr)
+        return loss.detach()
+
+
+def cosine_lr(it_epoch: float, lr: float, min_lr: float, warmup_epochs: float, epochs: float) -> float:
+    """Per-iteration half-cosine with linear warm-up (reference util/lr_sched.py:9-21)."""
+    if it_epoch < warmup_epochs:
+        return lr * it_epoch / warmup_epochs
+    return min_lr + (lr - min_lr) * 0.5 * (1. + math.cos(math.pi * (it_epoch - warmup_epochs) / (epochs - warmup_epochs)))

@@ -49,6 +49,20 @@ def workspace(nbytes: int, device, tag: str = "ws") -> torch.Tensor:
 # ------------------------------------------------------------------------------------------------------------
 # GEMM
 # ------------------------------------------------------------------------------------------------------------
+GEMM_PROFILE = None      # bench.py sets this to a list to time every GEMM launch with CUDA events (roofline leg)
+
+
+def _gemm_launch(lib, M, N, K, layout, epilogue, *args):
+    if GEMM_PROFILE is None:
+        return lib.ssl4p_gemm_bf16(*args)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    rc = lib.ssl4p_gemm_bf16(*args)
+    e1.record()
+    GEMM_PROFILE.append((e0, e1, 2.0 * M * N * K, (M, N, K, layout, epilogue)))
+    return rc
+
+
 def gemm(a, b, layout, epilogue, *, bias=None, aux=None, out=None, out2=None, splits=1, force_bn=0,
          accumulate_into=None):
     """C = op(A) . op(B) with a fused epilogue; see include/ssl4p.h.  a, b: bf16 2-D (last dim contiguous).
@@ -73,11 +87,11 @@ def gemm(a, b, layout, epilogue, *, bias=None, aux=None, out=None, out2=None, sp
         _req(final, f32, "gemm out")
         assert final.shape == (M, N)
         if splits == 1 and accumulate_into is None:
-            _lib.check(lib.ssl4p_gemm_bf16(a.data_ptr(), b.data_ptr(), final.data_ptr(), None, None, None, M, N, K,
+            _lib.check(_gemm_launch(lib, M, N, K, layout, epilogue, a.data_ptr(), b.data_ptr(), final.data_ptr(), None, None, None, M, N, K,
                                            a.stride(0), b.stride(0), N, 0, 0, layout, epilogue, 1, force_bn, _stream()), "gemm")
             return final
         ws = workspace(splits * M * N * 4, dev, "splitk")
-        _lib.check(lib.ssl4p_gemm_bf16(a.data_ptr(), b.data_ptr(), ws.data_ptr(), None, None, None, M, N, K,
+        _lib.check(_gemm_launch(lib, M, N, K, layout, epilogue, a.data_ptr(), b.data_ptr(), ws.data_ptr(), None, None, None, M, N, K,
                                        a.stride(0), b.stride(0), N, 0, 0, layout, epilogue, splits, force_bn, _stream()), "gemm")
         _lib.check(lib.ssl4p_splitk_reduce(ws.data_ptr(), splits, M * N, final.data_ptr(), M * N,
                                            1 if accumulate_into is not None else 0, _stream()), "splitk_reduce")
@@ -98,7 +112,7 @@ def gemm(a, b, layout, epilogue, *, bias=None, aux=None, out=None, out2=None, sp
         _req(aux, f32 if epilogue == EPI_BIAS_RESIDUAL_F32 else bf16, "gemm aux", contiguous=False)
         assert aux.shape == (M, N) and aux.stride(1) == 1
         ldaux = aux.stride(0)
-    _lib.check(lib.ssl4p_gemm_bf16(a.data_ptr(), b.data_ptr(), out.data_ptr(), _ptr(out2), _ptr(bias), _ptr(aux), M, N, K,
+    _lib.check(_gemm_launch(lib, M, N, K, layout, epilogue, a.data_ptr(), b.data_ptr(), out.data_ptr(), _ptr(out2), _ptr(bias), _ptr(aux), M, N, K,
                                    a.stride(0), b.stride(0), out.stride(0), out2.stride(0) if out2 is not None else 0, ldaux,
                                    layout, epilogue, 1, force_bn, _stream()), "gemm")
     return (out, out2) if epilogue == EPI_BIAS_GELU_BF16 else out
@@ -306,6 +320,44 @@ def masked_mse_bwd(imgs, pred_buf, has_cls_row, mask, norm_pix, p, grad_out, ws)
     pptr = pred_buf.data_ptr() + (P * 4 if has_cls_row else 0)
     _lib.check(lib.ssl4p_masked_mse_bwd(imgs.data_ptr(), pptr, rows * P, mask.data_ptr(), int(norm_pix), grad_out.data_ptr(), dpred.data_ptr(),
                                         rows * P, N, C, H, W, p, ws.data_ptr(), ws.numel(), _stream()), "masked_mse_bwd")
+    return dpred
+
+
+
+def _pred_layout(pred, L, P):
+    """pred: fp32 [N, L, P] whose rows are contiguous and whose batch stride may exceed L*P (a [:, 1:, :] view)."""
+    _req(pred, f32, "pred", contiguous=False)
+    if pred.dim() != 3 or pred.shape[1] != L or pred.shape[2] != P or pred.stride(2) != 1 or pred.stride(1) != P:
+        raise RuntimeError("pred must be [N, L, P] with contiguous rows (stride(1) == P, stride(2) == 1)")
+    return pred.data_ptr(), pred.stride(0)
+
+
+def masked_mse_fwd_strided(imgs, pred, mask, norm_pix, p):
+    """forward_loss on a pred that is either contiguous [N,L,P] or the [:,1:,:] view of a [N,1+L,P] buffer."""
+    lib = _lib.load()
+    _req(imgs, f32, "imgs"); _req(mask, f32, "mask")
+    N, C, H, W = imgs.shape
+    L = (H // p) * (W // p)
+    P = p * p * C
+    pptr, bstride = _pred_layout(pred, L, P)
+    ws = torch.empty(lib.ssl4p_masked_mse_workspace_bytes(N, L), dtype=torch.uint8, device=imgs.device)
+    loss = torch.empty((), dtype=f32, device=imgs.device)
+    _lib.check(lib.ssl4p_masked_mse_fwd(imgs.data_ptr(), pptr, bstride, mask.data_ptr(), int(norm_pix), loss.data_ptr(), N, C, H, W, p,
+                                        ws.data_ptr(), ws.numel(), _stream()), "masked_mse_fwd")
+    return loss, ws
+
+
+def masked_mse_bwd_strided(imgs, pred, mask, norm_pix, p, grad_out, ws):
+    """-> dpred bf16 contiguous [N, L, P]."""
+    lib = _lib.load()
+    N, C, H, W = imgs.shape
+    L = (H // p) * (W // p)
+    P = p * p * C
+    pptr, bstride = _pred_layout(pred, L, P)
+    _req(grad_out, f32, "grad_out")
+    dpred = torch.empty(N, L, P, dtype=bf16, device=imgs.device)
+    _lib.check(lib.ssl4p_masked_mse_bwd(imgs.data_ptr(), pptr, bstride, mask.data_ptr(), int(norm_pix), grad_out.data_ptr(), dpred.data_ptr(),
+                                        L * P, N, C, H, W, p, ws.data_ptr(), ws.numel(), _stream()), "masked_mse_bwd")
     return dpred
 
 

@@ -1,0 +1,231 @@
+"""GPU parity of the drop-in model (ssl4polyp_b200.models_mae / models) against
+  (1) the committed golden vectors produced by the UNMODIFIED reference (tests/golden/mae_golden.pt), and
+  (2) the CPU oracle (oracle/mae_oracle.py) run on the same weights, images and noise.
+Tolerances are BASELINE.json's: masking indices / ids_restore / mask bit-exact; loss rel 1e-2; gradient cosine > 0.999.
+"""
+import os
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+from oracle import mae_oracle as O  # noqa: E402  (checker only)
+
+GOLDEN = os.path.join(os.path.dirname(__file__), "golden", "mae_golden.pt")
+LOSS_RTOL = 1e-2
+GRAD_COS = 0.999
+
+
+def dev():
+    return torch.device("cuda:0")
+
+
+def synth_imgs(B, seed, size=224):
+    g = torch.Generator().manual_seed(1000 + seed)
+    return torch.randn(B, 3, size, size, generator=g)
+
+
+def subsample(t, n=64):
+    f = t.detach().reshape(-1)
+    step = max(1, f.numel() // n)
+    return f[::step][:n].clone()
+
+
+def cos(a, b):
+    a, b = a.double().flatten(), b.double().flatten()
+    return (a @ b / (a.norm() * b.norm()).clamp_min(1e-300)).item()
+
+
+def build_base(seed, norm_pix):
+    from ssl4polyp_b200 import models_mae
+    torch.manual_seed(seed)
+    m = models_mae.mae_vit_base_patch16(norm_pix_loss=norm_pix)
+    return m.to(dev()).train()
+
+
+@pytest.fixture(scope="module")
+def golden():
+    return torch.load(GOLDEN)
+
+
+@pytest.mark.parametrize("idx", [0, 1, 2, 3])
+def test_mae_base_against_reference_golden(golden, idx):
+    c = golden["cases"][idx]
+    assert c["cfg_name"] == "base"
+    B, seed, mr = c["B"], c["seed"], c["mask_ratio"]
+    m = build_base(seed, c["cfg"]["norm_pix_loss"])
+    # same init as the reference constructor under the same seed (bit-exact on CPU, checked in test_host.py)
+    assert torch.equal(subsample(m.state_dict()["blocks.0.attn.qkv.weight"].cpu(), 16), c["w_sample"])
+    imgs = synth_imgs(B, seed)
+    assert torch.equal(subsample(imgs, 16), c["imgs_sample"])
+    loss, pred, mask, ids_restore = m.forward_with_noise(imgs.to(dev()), c["noise"].to(dev()), mr)
+    assert ids_restore.dtype == torch.int64 and mask.dtype == torch.float32
+    assert torch.equal(ids_restore.cpu(), c["ids_restore"]), "ids_restore must be bit-exact"
+    assert torch.equal(mask.cpu(), c["mask"]), "mask must be bit-exact"
+    assert pred.shape == (B, 196, 768)
+    rel = abs(loss.item() - c["loss"].item()) / abs(c["loss"].item())
+    assert rel < LOSS_RTOL, (loss.item(), c["loss"].item())
+    ps = subsample(pred.cpu(), 256)
+    assert cos(ps, c["pred_sample"]) > 0.995
+    assert abs(pred.float().norm().item() - c["pred_norm"].item()) / c["pred_norm"].item() < 2e-2
+    loss.backward()
+    grads = {k: p.grad for k, p in m.named_parameters() if p.grad is not None}
+    assert set(grads) == set(c["grad_norm"]), set(grads) ^ set(c["grad_norm"])
+    for k, gs in c["grad_sample"].items():
+        assert cos(subsample(grads[k].cpu(), 64), gs) > 0.99, k
+    bad = []
+    for k, gn in c["grad_norm"].items():
+        r = abs(grads[k].norm().item() - gn.item()) / max(gn.item(), 1e-12)
+        if r > 5e-2:
+            bad.append((k, r))
+    assert not bad, bad[:8]
+
+
+def _oracle_run(cfg, sd, imgs, noise, mr):
+    sd_g = {k: v.clone().requires_grad_(k not in ("pos_embed", "decoder_pos_embed")) for k, v in sd.items()}
+    loss, pred, mask = O.mae_forward(sd_g, imgs, noise, mr, cfg)
+    loss.backward()
+    _, _, ids_restore = O.masking_from_noise(noise, mr)
+    return loss.detach(), pred.detach(), mask, ids_restore, {k: v.grad for k, v in sd_g.items() if v.grad is not None}
+
+
+def _check_against_oracle(m, cfg, B, seed, mr, size):
+    m.zero_grad(set_to_none=True)
+    sd = {k: v.detach().cpu().clone() for k, v in m.state_dict().items()}
+    imgs = synth_imgs(B, seed, size)
+    with torch.random.fork_rng(devices=[]):
+        torch.manual_seed(seed)
+        noise = torch.rand(B, cfg.num_patches)
+    loss_o, pred_o, mask_o, ids_o, grads_o = _oracle_run(cfg, sd, imgs, noise, mr)
+    loss, pred, mask, ids_restore = m.forward_with_noise(imgs.to(dev()), noise.to(dev()), mr)
+    assert torch.equal(ids_restore.cpu(), ids_o) and torch.equal(mask.cpu(), mask_o)
+    assert abs(loss.item() - loss_o.item()) / abs(loss_o.item()) < LOSS_RTOL
+    assert cos(pred.cpu(), pred_o) > 0.999
+    loss.backward()
+    worst = 1.0
+    for k, g in grads_o.items():
+        p = dict(m.named_parameters())[k]
+        assert p.grad is not None, k
+        c = cos(p.grad.cpu(), g)
+        worst = min(worst, c)
+        assert c > GRAD_COS, (k, c)
+    return worst
+
+
+def test_mae_base_all_grads_against_oracle():
+    m = build_base(5, True)
+    _check_against_oracle(m, O.MAEConfig(norm_pix_loss=True), B=2, seed=5, mr=0.75, size=224)
+
+
+def test_mae_small_config_against_oracle():
+    """64x64 images, 16 patches, D=64 (2 heads of 32), decoder D=64: ragged tiles everywhere (M = 15, 51 rows)."""
+    from functools import partial
+    from ssl4polyp_b200 import models_mae
+    torch.manual_seed(11)
+    kw = dict(img_size=64, patch_size=16, in_chans=3, embed_dim=64, depth=2, num_heads=2, decoder_embed_dim=64,
+              decoder_depth=2, decoder_num_heads=2, mlp_ratio=4.)
+    m = models_mae.MaskedAutoencoderViT(norm_layer=partial(torch.nn.LayerNorm, eps=1e-6), norm_pix_loss=True, **kw).to(dev())
+    with torch.no_grad():                      # non-trivial LayerNorm / bias / token values
+        for p in m.parameters():
+            if p.requires_grad and p.ndim == 1:
+                p.add_(0.1 * torch.randn_like(p))
+    cfg = O.MAEConfig(img_size=64, embed_dim=64, depth=2, num_heads=2, decoder_embed_dim=64, decoder_depth=2,
+                      decoder_num_heads=2, norm_pix_loss=True)
+    _check_against_oracle(m, cfg, B=3, seed=4, mr=0.75, size=64)
+    _check_against_oracle(m, cfg, B=5, seed=6, mr=0.5, size=64)
+
+
+def test_forward_draws_the_reference_noise():
+    """`forward` must consume exactly one torch.rand(N, L) from the device generator (models_mae.py:132)."""
+    m = build_base(0, True)
+    imgs = synth_imgs(2, 0).to(dev())
+    torch.manual_seed(123)
+    noise = torch.rand(2, 196, device=dev())
+    after = torch.rand(4, device=dev())
+    torch.manual_seed(123)
+    with torch.no_grad():
+        loss, pred, mask = m(imgs, mask_ratio=0.75)
+    assert torch.equal(torch.rand(4, device=dev()), after)
+    ids_keep, mask_o, _ = O.masking_from_noise(noise.cpu(), 0.75)
+    assert torch.equal(mask.cpu(), mask_o)
+    assert mask.sum().item() == 2 * 147 and loss.dim() == 0 and not loss.requires_grad
+
+
+def test_piecewise_api_matches_fused_forward():
+    m = build_base(1, True)
+    imgs = synth_imgs(2, 1).to(dev())
+    torch.manual_seed(7)
+    loss, pred, mask = m(imgs, 0.75)
+    loss.backward()
+    g_fused = {k: p.grad.clone() for k, p in m.named_parameters() if p.grad is not None}
+    m.zero_grad(set_to_none=True)
+    torch.manual_seed(7)
+    latent, mask2, ids_restore = m.forward_encoder(imgs, 0.75)
+    assert latent.shape == (2, 50, 768) and latent.dtype == torch.float32
+    pred2 = m.forward_decoder(latent, ids_restore)
+    loss2 = m.forward_loss(imgs, pred2, mask2)
+    assert torch.equal(mask, mask2)
+    assert abs(loss.item() - loss2.item()) / abs(loss.item()) < 1e-3
+    assert cos(pred, pred2) > 0.9999
+    loss2.backward()
+    for k, g in g_fused.items():
+        g2 = dict(m.named_parameters())[k].grad
+        assert g2 is not None and cos(g, g2) > 0.999, k
+    # patchify / unpatchify / random_masking
+    x = m.patchify(imgs)
+    assert torch.equal(x.cpu(), O.patchify(imgs.cpu()))
+    assert torch.equal(m.unpatchify(x), imgs)
+    torch.manual_seed(3)
+    xm, mk, ir = m.random_masking(x, 0.75)
+    torch.manual_seed(3)
+    nz = torch.rand(2, 196, device=dev())
+    ik, mk_o, ir_o = O.masking_from_noise(nz.cpu(), 0.75)
+    assert torch.equal(ir.cpu(), ir_o) and torch.equal(mk.cpu(), mk_o)
+    assert torch.equal(xm.cpu(), torch.gather(x.cpu(), 1, ik.unsqueeze(-1).expand(-1, -1, 768)))
+
+
+def test_classifier_against_oracle():
+    from ssl4polyp_b200 import models
+    torch.manual_seed(2)
+    m = models.ViT_from_MAE(None, True, 2, False, None, embed_dim=768, depth=12, num_heads=12, out_token="cls").to(dev()).train()
+    sd = {k: v.detach().cpu().clone() for k, v in m.state_dict().items()}
+    B = 4
+    imgs = synth_imgs(B, 9)
+    target = torch.tensor([0, 1, 1, 0])
+    sd_g = {k: v.clone().requires_grad_(k not in ("pos_embed", "decoder_pos_embed")) for k, v in sd.items()}
+    logits_o = O.classifier_forward(sd_g, imgs, O.MAE_BASE, "cls", True)
+    loss_o = O.binary_polyp_loss(logits_o, target)
+    loss_o.backward()
+    logits = m(imgs.to(dev()))
+    assert logits.shape == (B, 2) and logits.dtype == torch.float32
+    assert (logits.cpu() - logits_o.detach()).abs().max().item() < 3e-2 * max(1.0, logits_o.abs().max().item())
+    loss = O.binary_polyp_loss(logits, target.to(dev()))          # 4 scalars of glue, stays in torch
+    assert abs(loss.item() - loss_o.item()) / abs(loss_o.item()) < LOSS_RTOL
+    loss.backward()
+    for k, v in sd_g.items():
+        if v.grad is None:
+            continue
+        g = dict(m.named_parameters())[k].grad
+        assert g is not None, k
+        assert cos(g.cpu(), v.grad) > 0.995, (k, cos(g.cpu(), v.grad))
+
+
+def test_classifier_finetune_modes_prune_backward():
+    from ssl4polyp_b200 import models
+    torch.manual_seed(3)
+    m = models.ViT_from_MAE(None, True, 2, False, None, embed_dim=768, depth=12, num_heads=12, out_token="spatial").to(dev()).train()
+    for p in m.parameters():
+        p.requires_grad_(False)
+    for p in m.lin_head.parameters():
+        p.requires_grad_(True)
+    for p in m.blocks[-1].parameters():
+        p.requires_grad_(True)
+    imgs = synth_imgs(2, 3).to(dev())
+    m(imgs).sum().backward()
+    with_grad = {k for k, p in m.named_parameters() if p.grad is not None}
+    assert with_grad == {k for k, p in m.named_parameters() if p.requires_grad}
+    assert all(k.startswith(("lin_head.", "blocks.11.")) for k in with_grad)
+    with torch.no_grad():
+        out = m.eval()(imgs)
+    assert not out.requires_grad
