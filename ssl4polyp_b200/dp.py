@@ -1,0 +1,108 @@
+"""Data-parallel gradient exchange for the flat gradient arena: bucket plan + overlapped all-reduce.
+
+The reference wraps the model in `torch.nn.parallel.DistributedDataParallel`
+(/root/reference/src/ssl4polyp/models/mae/main_pretrain.py:212-214, classification/train_classification.py:5743-5750):
+bucketed SUM all-reduce fired from autograd hooks, averaged by world size.  Here the backward is our own schedule, so
+the exchange is driven by it directly: the arena is cut into contiguous buckets starting from its END (the arena is in
+forward order, so its end is what backward produces first); when the last gradient of a bucket has been enqueued, an
+event is recorded on the compute stream and NCCL all-reduces that slice on a side stream while backward carries on.
+The division by world size is folded into the optimiser (`grad_scale`).  One process per GPU; no other collective is
+on the data path.  The same class runs over gloo on CPU tensors (tests: world_size 2) with async work handles.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass, field
+
+import torch
+import torch.distributed as dist
+
+
+@dataclass
+class Bucket:
+    start: int
+    end: int
+    names: set = field(default_factory=set)
+
+
+def plan_buckets(offsets: dict, trainable: list, limit_elems: int, align: int = 256) -> list:
+    """offsets: name -> (start, numel) in the arena; trainable: names that get a gradient.
+    Returns buckets ordered as backward completes them (highest arena offsets first).  Buckets are contiguous and
+    tile [first trainable start, last trainable end): frozen tensors in between ride along (their gradient is zero)."""
+    names = sorted(trainable, key=lambda n: offsets[n][0], reverse=True)
+    buckets: list[Bucket] = []
+    cur = None
+    for nme in names:
+        a, cnt = offsets[nme]
+        if cur is None:
+            cur = Bucket(start=a, end=(a + cnt + align - 1) // align * align)
+        cur.start = a
+        cur.names.add(nme)
+        if cur.end - cur.start >= limit_elems:
+            buckets.append(cur)
+            cur = None
+    if cur is not None:
+        buckets.append(cur)
+    for i in range(1, len(buckets)):
+        buckets[i].end = buckets[i - 1].start
+    return buckets
+
+
+class BucketReducer:
+    def __init__(self, flat: torch.Tensor, buckets: list, group=None):
+        self.flat = flat
+        self.buckets = buckets
+        self.group = group
+        self.world = dist.get_world_size(group) if (dist.is_available() and dist.is_initialized()) else 1
+        self.cuda = flat.is_cuda
+        self.comm_stream = torch.cuda.Stream(device=flat.device) if (self.cuda and self.world > 1) else None
+        self.bucket_of = {n: i for i, b in enumerate(buckets) for n in b.names}
+        self.launch_order: list[int] = []
+        self.reset()
+
+    def reset(self):
+        self._remaining = [len(b.names) for b in self.buckets]
+        self._seen = set()
+        self._launched = set()
+        self._handles = []
+        self.launch_order = []
+
+    def ready(self, name: str) -> None:
+        """The kernels producing gradient `name` have been enqueued on the current stream."""
+        if self.world == 1 or name in self._seen:
+            return
+        i = self.bucket_of.get(name)
+        if i is None:
+            return
+        self._seen.add(name)
+        self._remaining[i] -= 1
+        if self._remaining[i] == 0:
+            self._launch(i)
+
+    def _launch(self, i: int) -> None:
+        b = self.buckets[i]
+        view = self.flat[b.start:b.end]
+        self._launched.add(i)
+        self.launch_order.append(i)
+        if self.cuda:
+            ev = torch.cuda.Event()
+            ev.record(torch.cuda.current_stream())
+            self.comm_stream.wait_event(ev)
+            with torch.cuda.stream(self.comm_stream):
+                dist.all_reduce(view, op=dist.ReduceOp.SUM, group=self.group)
+        else:
+            self._handles.append(dist.all_reduce(view, op=dist.ReduceOp.SUM, group=self.group, async_op=True))
+
+    def finish(self) -> None:
+        """Reduce whatever has not been launched (parameters that received no gradient this step), then make the
+        current stream wait for all bucket reductions."""
+        if self.world == 1:
+            return
+        for i in range(len(self.buckets)):
+            if i not in self._launched:
+                self._launch(i)
+        if self.cuda:
+            torch.cuda.current_stream().wait_stream(self.comm_stream)
+        else:
+            for h in self._handles:
+                h.wait()
+            self._handles = []

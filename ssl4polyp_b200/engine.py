@@ -23,6 +23,7 @@ import torch
 import torch.distributed as dist
 
 from . import ops, vit_core
+from .dp import BucketReducer, plan_buckets
 from .param_store import ALIGN
 
 
@@ -63,74 +64,17 @@ class TrainEngine:
             if p.requires_grad and not rule(name, p):
                 flags[a // ALIGN:(a + cnt + ALIGN - 1) // ALIGN] = 1
         self.wd_flags = flags.to(dev)
-        # ---- data parallel
-        self.pg = process_group
-        self.world = dist.get_world_size(process_group) if (dist.is_available() and dist.is_initialized()) else 1
-        self.comm_stream = torch.cuda.Stream(device=dev) if self.world > 1 else None
-        self._build_buckets(bucket_mb)
+        # ---- data parallel (dp.py): bucket plan over the gradient arena + overlapped all-reduce
+        trainable = [n for n in store.offsets if store.params[n].requires_grad]
+        self.buckets = plan_buckets(store.offsets, trainable, int(bucket_mb * (1 << 20) / 4), ALIGN)
+        self.reducer = BucketReducer(self.grads, self.buckets, process_group)
+        self.world = self.reducer.world
         self.sink = ArenaSink(self)
-        self._pending = []
-
-    # ---- buckets: contiguous arena ranges, filled from the END of the arena (= first gradients of backward) ----
-    def _build_buckets(self, bucket_mb):
-        names = [n for n in self.store.offsets if self.store.params[n].requires_grad]
-        names.sort(key=lambda n: self.store.offsets[n][0], reverse=True)
-        limit = int(bucket_mb * (1 << 20) / 4)
-        self.buckets = []        # [start, end, {names}]
-        cur_names, cur_end, cur_start = [], None, None
-        for nme in names:
-            a, cnt = self.store.offsets[nme]
-            if cur_end is None:
-                cur_end = (a + cnt + ALIGN - 1) // ALIGN * ALIGN
-            cur_start = a
-            cur_names.append(nme)
-            if cur_end - cur_start >= limit:
-                self.buckets.append([cur_start, cur_end, set(cur_names)])
-                cur_names, cur_end = [], None
-        if cur_names:
-            self.buckets.append([cur_start, cur_end, set(cur_names)])
-        # close the gaps (frozen tensors in between): bucket i ends where bucket i-1 starts
-        for i in range(1, len(self.buckets)):
-            self.buckets[i][1] = self.buckets[i - 1][0]
-        self.bucket_of = {}
-        for i, (_, _, ns) in enumerate(self.buckets):
-            for nme in ns:
-                self.bucket_of[nme] = i
-        self._remaining = [len(b[2]) for b in self.buckets]
-        self._seen = set()
-
-    def _reset_ready(self):
-        self._remaining = [len(b[2]) for b in self.buckets]
-        self._seen.clear()
-        self._pending = []
+        self._reduce_now = True
 
     def _on_ready(self, name):
-        if self.world == 1 or not self._reduce_now or name in self._seen:
-            return
-        i = self.bucket_of.get(name)
-        if i is None:
-            return
-        self._seen.add(name)
-        self._remaining[i] -= 1
-        if self._remaining[i] == 0:
-            self._launch_bucket(i)
-
-    def _launch_bucket(self, i):
-        a, b, _ = self.buckets[i]
-        ev = torch.cuda.Event()
-        ev.record(torch.cuda.current_stream())
-        self.comm_stream.wait_event(ev)
-        with torch.cuda.stream(self.comm_stream):
-            dist.all_reduce(self.grads[a:b], op=dist.ReduceOp.SUM, group=self.pg)
-        self._pending.append(i)
-
-    def _finish_reduce(self):
-        if self.world == 1:
-            return
-        for i, rem in enumerate(self._remaining):       # tensors whose gradient never appeared (unused parameters)
-            if rem > 0 and i not in self._pending:
-                self._launch_bucket(i)
-        torch.cuda.current_stream().wait_stream(self.comm_stream)
+        if self._reduce_now:
+            self.reducer.ready(name)
 
     # ---- one optimisation step -------------------------------------------------------------------------------
     def backward_and_step(self, run_backward, lr=None, accumulate: bool = False, do_step: bool = True):
@@ -139,11 +83,11 @@ class TrainEngine:
         reducing once on the boundary gives the same mean with 1/accum of the traffic)."""
         self.sink.accumulate = accumulate
         self._reduce_now = do_step
-        self._reset_ready()
+        self.reducer.reset()
         run_backward(self.sink)
         if not do_step:
             return
-        self._finish_reduce()
+        self.reducer.finish()
         self.t += 1
         b1, b2 = self.betas
         ops.adamw_flat(self.store.flat, self.grads, self.exp_avg, self.exp_avg_sq, self.store.shadow, self.wd_flags,

@@ -1,0 +1,242 @@
+"""CPU-only tests (`-m "not gpu"`): the oracle against the reference-generated golden vectors, the C-ABI surface,
+the host-side mirror of the reference interface, and the data-parallel bucket logic over gloo (world_size 2).
+No CUDA compute is called here."""
+import ctypes
+import os
+import re
+import subprocess
+import sys
+
+import pytest
+import torch
+
+from oracle import mae_oracle as O
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+GOLDEN = os.path.join(ROOT, "tests", "golden", "mae_golden.pt")
+
+
+@pytest.fixture(scope="module")
+def golden():
+    return torch.load(GOLDEN)
+
+
+def subsample(t, n=64):
+    f = t.detach().reshape(-1)
+    step = max(1, f.numel() // n)
+    return f[::step][:n].clone()
+
+
+def synth_imgs(B, seed, size=224):
+    return torch.randn(B, 3, size, size, generator=torch.Generator().manual_seed(1000 + seed))
+
+
+# ------------------------------------------------------------------------------------------------ oracle vs golden
+def test_oracle_masking_matches_reference_golden(golden):
+    for c in golden["cases"]:
+        ids_keep, mask, ids_restore = O.masking_from_noise(c["noise"], c["mask_ratio"])
+        assert torch.equal(ids_restore, c["ids_restore"])
+        assert torch.equal(mask, c["mask"])
+        assert ids_restore.dtype == torch.int64 and mask.dtype == torch.float32
+        L = c["noise"].shape[1]
+        assert ids_keep.shape[1] == int(L * (1 - c["mask_ratio"]))
+    t = golden["ties"]
+    ids_keep, mask, ids_restore = O.masking_from_noise(t["noise"], t["mask_ratio"])
+    assert torch.equal(ids_keep, t["ids_keep"]) and torch.equal(mask, t["mask"]) and torch.equal(ids_restore, t["ids_restore"])
+
+
+def test_oracle_tiny_case_full_forward_backward_matches_reference_golden(golden):
+    c = golden["cases"][4]
+    cfg = O.MAEConfig(**c["cfg"])
+    sd = O.init_state_dict(cfg, seed=c["seed"])
+    assert torch.equal(subsample(sd["blocks.0.attn.qkv.weight"], 16), c["w_sample"])
+    imgs = synth_imgs(c["B"], c["seed"], cfg.img_size)
+    assert torch.equal(subsample(imgs, 16), c["imgs_sample"])
+    sd_g = {k: v.clone().requires_grad_(k not in ("pos_embed", "decoder_pos_embed")) for k, v in sd.items()}
+    loss, pred, mask = O.mae_forward(sd_g, imgs, c["noise"], c["mask_ratio"], cfg)
+    loss.backward()
+    assert abs(loss.item() - c["loss"].item()) < 1e-5 * abs(c["loss"].item())
+    assert torch.allclose(subsample(pred, 256), c["pred_sample"], rtol=1e-4, atol=1e-5)
+    for k, gn in c["grad_norm"].items():
+        assert abs(sd_g[k].grad.norm().item() - gn.item()) <= 1e-3 * gn.item() + 1e-8, k
+    for k, gs in c["grad_sample"].items():
+        assert torch.allclose(subsample(sd_g[k].grad, 64), gs, rtol=1e-3, atol=1e-6), k
+
+
+def test_oracle_base_forward_matches_reference_golden(golden):
+    c = golden["cases"][0]
+    cfg = O.MAEConfig(**c["cfg"])
+    sd = O.init_state_dict(cfg, seed=c["seed"])
+    imgs = synth_imgs(c["B"], c["seed"])
+    with torch.no_grad():
+        loss, pred, mask = O.mae_forward(sd, imgs, c["noise"], c["mask_ratio"], cfg)
+    assert abs(loss.item() - c["loss"].item()) < 1e-5 * abs(c["loss"].item())
+    assert torch.allclose(subsample(pred, 256), c["pred_sample"], rtol=1e-4, atol=1e-5)
+    assert torch.equal(mask, c["mask"])
+
+
+def test_oracle_patchify_roundtrip_and_len_keep():
+    x = torch.randn(2, 3, 64, 64)
+    assert torch.equal(O.unpatchify(O.patchify(x)), x)
+    assert O.len_keep_of(196, 0.75) == 49 and O.len_keep_of(196, 0.6) == 78      # int(196*0.4) = int(78.4)
+
+
+# ------------------------------------------------------------------------------------------------ C-ABI surface
+def test_abi_header_symbols_exported_and_bound():
+    from ssl4polyp_b200 import _lib
+    with open(os.path.join(ROOT, "include", "ssl4p.h")) as f:
+        header = f.read()
+    declared = set(re.findall(r"\b(ssl4p_[a-z0-9_]+)\s*\(", header))
+    assert len(declared) >= 30
+    assert declared == set(_lib.SIGNATURES), declared ^ set(_lib.SIGNATURES)
+    assert os.path.exists(_lib.LIB_PATH), "run __graft_entry__.build() first"
+    lib = ctypes.CDLL(_lib.LIB_PATH)
+    for name in declared:
+        assert hasattr(lib, name), f"{name} not exported by libssl4p.so"
+    loaded = _lib.load()
+    assert loaded.ssl4p_abi_version() == 1
+    assert loaded.ssl4p_last_error() is not None
+
+
+def test_library_is_sm100a_tcgen05_and_tma():
+    """SASS evidence (B200_PROFILING.md): UTC*MMA = tcgen05.mma, UTMALDG = TMA loads, LDTM = tcgen05.ld."""
+    from ssl4polyp_b200 import _lib
+    out = subprocess.run(["cuobjdump", "-sass", _lib.LIB_PATH], capture_output=True, text=True)
+    if out.returncode != 0:
+        pytest.skip("cuobjdump unavailable")
+    sass = out.stdout
+    assert "sm_100a" in sass
+    assert re.search(r"UTC\w*MMA", sass), "no tcgen05.mma in the library"
+    assert "UTMALDG" in sass and "LDTM" in sass
+
+
+def test_product_never_imports_the_oracle_and_has_no_cpu_path():
+    pkg = os.path.join(ROOT, "ssl4polyp_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for fn in files:
+            if fn.endswith(".py"):
+                src = open(os.path.join(dirpath, fn)).read()
+                assert not re.search(r"^\s*(from|import)\s+oracle", src, re.M), f"{fn} imports the oracle"
+    from ssl4polyp_b200 import models_mae, ops
+    m = models_mae.MaskedAutoencoderViT(img_size=32, embed_dim=64, depth=1, num_heads=2, decoder_embed_dim=64,
+                                        decoder_depth=1, decoder_num_heads=2)
+    with pytest.raises(RuntimeError, match="CUDA"):
+        m(torch.zeros(1, 3, 32, 32))
+    with pytest.raises(RuntimeError, match="CUDA"):
+        ops.mask_from_noise(torch.rand(2, 16), 4)
+
+
+# ------------------------------------------------------------------------------------------------ host-side mirror
+def test_constructor_init_is_bit_identical_to_reference_init():
+    from ssl4polyp_b200 import models_mae
+    torch.manual_seed(0)
+    m = models_mae.mae_vit_base_patch16(norm_pix_loss=True)
+    sd = O.init_state_dict(O.MAE_BASE, seed=0)      # pinned bit-for-bit to the reference constructor by make_golden.py
+    msd = m.state_dict()
+    assert set(sd) == set(msd)
+    for k in sd:
+        assert msd[k].shape == sd[k].shape and torch.equal(msd[k], sd[k]), k
+    assert not m.pos_embed.requires_grad and not m.decoder_pos_embed.requires_grad
+    assert m.norm.eps == 1e-6 and m.norm_pix_loss is True
+    assert m.patch_embed.patch_size == (16, 16) and m.patch_embed.num_patches == 196
+    assert isinstance(m.blocks, torch.nn.ModuleList) and len(m.blocks) == 12 and len(m.decoder_blocks) == 8
+
+
+def test_reference_factories_and_classifier_surface():
+    from ssl4polyp_b200 import models, models_mae, utils
+    assert models_mae.mae_vit_large_patch16 is models_mae.mae_vit_large_patch16_dec512d8b
+    assert callable(models_mae.mae_vit_huge_patch14)
+    m = utils.get_MAE_backbone(None, True, 2, False, None, out_token="cls")
+    assert isinstance(m, models.ViT_from_MAE)
+    keys = set(m.state_dict())
+    assert {"lin_head.weight", "lin_head.bias", "cls_token", "pos_embed", "decoder_pos_embed", "norm.weight"} <= keys
+    assert not any(k.startswith(("decoder_blocks", "decoder_embed", "decoder_pred", "decoder_norm", "mask_token")) for k in keys)
+    assert m.lin_head.weight.shape == (2, 768) and m.head is True and m.frozen is False and m.out_token == "cls"
+    # finetune.py:49-91 contract: blocks is a ModuleList, head module is `lin_head`
+    for p in m.parameters():
+        p.requires_grad_(False)
+    for p in list(m.blocks)[-1].parameters():
+        p.requires_grad_(True)
+    assert sum(p.requires_grad for p in m.parameters()) == 12
+
+
+def test_mae_to_classifier_checkpoint_handoff(tmp_path):
+    from ssl4polyp_b200 import models, models_mae
+    torch.manual_seed(1)
+    mae = models_mae.mae_vit_base_patch16()
+    path = tmp_path / "checkpoint-0.pth"
+    torch.save({"model": mae.state_dict()}, path)                      # util/misc.py:312-318 layout
+    clf = models.ViT_from_MAE(str(path), True, 2, False, None, 768, 12, 12, "cls")
+    for k, v in clf.state_dict().items():
+        if k in mae.state_dict():
+            assert torch.equal(v, mae.state_dict()[k]), k
+
+
+def test_sincos_table_matches_oracle():
+    from ssl4polyp_b200.util.pos_embed import get_2d_sincos_pos_embed
+    for dim in (768, 512, 1024):
+        t = torch.from_numpy(get_2d_sincos_pos_embed(dim, 14, cls_token=True)).float()
+        assert torch.equal(t, O.sincos_pos_embed(dim, 14))
+
+
+# ------------------------------------------------------------------------------------------------ DP bucket logic
+def test_bucket_plan_covers_trainable_range_in_backward_order():
+    from ssl4polyp_b200.dp import plan_buckets
+    offsets, off = {}, 0
+    sizes = {"cls": 768, "pos": 197 * 768, "pe.w": 768 * 768, "b0.w": 3 * 768 * 768, "b0.b": 2304, "b1.w": 4 * 768 * 768, "head": 512 * 768}
+    for k, n in sizes.items():
+        offsets[k] = (off, n)
+        off += (n + 255) // 256 * 256
+    trainable = [k for k in sizes if k != "pos"]
+    buckets = plan_buckets(offsets, trainable, limit_elems=2_000_000)
+    assert buckets[0].end == off and "head" in buckets[0].names
+    assert buckets[-1].start == offsets["cls"][0]
+    for a, b in zip(buckets, buckets[1:]):
+        assert b.end == a.start                       # contiguous, no gaps
+    assert set().union(*[b.names for b in buckets]) == set(trainable)
+
+
+_DP_WORKER = r"""
+import os, sys, torch, torch.distributed as dist
+sys.path.insert(0, sys.argv[3])
+from ssl4polyp_b200.dp import plan_buckets, BucketReducer
+rank, world = int(sys.argv[1]), 2
+dist.init_process_group("gloo", init_method=f"tcp://127.0.0.1:{sys.argv[2]}", rank=rank, world_size=world)
+offsets, off = {}, 0
+for i in range(12):
+    n = 1000 + 37 * i
+    offsets[f"p{i}"] = (off, n); off += (n + 255) // 256 * 256
+trainable = [f"p{i}" for i in range(12) if i != 3]           # p3 frozen
+flat = torch.zeros(off)
+for i in range(12):
+    a, n = offsets[f"p{i}"]
+    if i != 3:
+        flat[a:a + n] = (rank + 1) * (i + 1)
+buckets = plan_buckets(offsets, trainable, limit_elems=3000)
+red = BucketReducer(flat, buckets)
+assert red.world == 2
+for i in reversed(range(12)):                                 # backward order; p5 never reports (unused parameter)
+    if i not in (3, 5):
+        red.ready(f"p{i}")
+red.finish()
+for i in range(12):
+    a, n = offsets[f"p{i}"]
+    want = 0.0 if i == 3 else 3.0 * (i + 1)
+    assert torch.all(flat[a:a + n] == want), (i, flat[a].item(), want)
+assert red.launch_order[0] == 0 and sorted(red.launch_order) == list(range(len(buckets)))
+dist.destroy_process_group()
+print("ok", rank)
+"""
+
+
+def test_bucket_reducer_world_size_2_gloo(tmp_path):
+    import socket
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
+    script = tmp_path / "dp_worker.py"
+    script.write_text(_DP_WORKER)
+    procs = [subprocess.Popen([sys.executable, str(script), str(r), str(port), ROOT], stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True)
+             for r in range(2)]
+    for p in procs:
+        out, err = p.communicate(timeout=180)
+        assert p.returncode == 0, err[-2000:]
+        assert "ok" in out
