@@ -133,6 +133,13 @@ int ssl4p_cast_f32_bf16(const float* src, void* dst_bf16, long long n, void* str
 int ssl4p_adamw_flat(float* p, const float* g, float* m, float* v, void* p_bf16, const uint8_t* wd_flags, long long n,
                      float lr, float beta1, float beta2, float eps, float weight_decay, float bias_corr1, float bias_corr2,
                      float grad_scale, int* nonfinite, void* stream);
+/* Same update with the per-step scalars resident on the device, so that the whole training step can be replayed
+ * from a CUDA graph: hyper[0] = lr (util/lr_sched.py:9-21 writes it before each replay), hyper[1] = number of
+ * optimiser steps completed so far (the kernel uses t = hyper[1]+1 for the bias corrections and a trailing
+ * one-thread kernel stores t back). */
+int ssl4p_adamw_flat_dev(float* p, const float* g, float* m, float* v, void* p_bf16, const uint8_t* wd_flags, long long n,
+                         float* hyper, float beta1, float beta2, float eps, float weight_decay,
+                         float grad_scale, int* nonfinite, void* stream);
 
 /* ViT_from_MAE head (models.py:211-222): logits[n,:] = W . pooled[n,:] + b with pooled = x[n,0,:] ("cls") or
  * mean_i x[n,1+i,:] ("spatial"); x is the fp32 output of the final LayerNorm kept as bf16 [N,T,D]. */

@@ -45,6 +45,7 @@ SIGNATURES = {
     "ssl4p_colsum_workspace_bytes": (sz, [i32, i32]),
     "ssl4p_cast_f32_bf16": (i32, [vp, vp, i64, vp]),
     "ssl4p_adamw_flat": (i32, [vp, vp, vp, vp, vp, vp, i64, f32, f32, f32, f32, f32, f32, f32, f32, vp, vp]),
+    "ssl4p_adamw_flat_dev": (i32, [vp, vp, vp, vp, vp, vp, i64, vp, f32, f32, f32, f32, f32, vp, vp]),
     "ssl4p_pool_head_fwd": (i32, [vp, vp, vp, vp, i32, i32, i32, i32, i32, vp]),
     "ssl4p_pool_head_bwd": (i32, [vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, vp]),
 }

@@ -7,11 +7,19 @@
 
 namespace ssl4p {
 
+// hyper == nullptr: lr / inv_bc1 / inv_sqrt_bc2 are the host-computed scalars.  hyper != nullptr: lr = hyper[0] and the
+// bias corrections follow from t = hyper[1] + 1 (device-resident step counter: CUDA-graph replay).
 __global__ void __launch_bounds__(256)
 adamw_flat_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m, float* __restrict__ v,
                   __nv_bfloat16* __restrict__ pb, const uint8_t* __restrict__ wd_flags, long long n4,
                   float lr, float beta1, float beta2, float eps, float wd, float inv_bc1, float inv_sqrt_bc2, float grad_scale,
-                  int* __restrict__ nonfinite) {
+                  int* __restrict__ nonfinite, const float* __restrict__ hyper) {
+    if (hyper != nullptr) {
+        lr = hyper[0];
+        const float t = hyper[1] + 1.0f;
+        inv_bc1 = 1.0f / (1.0f - powf(beta1, t));
+        inv_sqrt_bc2 = rsqrtf(1.0f - powf(beta2, t));
+    }
     int bad = 0;
     const long long step = (long long)gridDim.x * blockDim.x;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += step) {
@@ -44,6 +52,8 @@ adamw_flat_kernel(float* __restrict__ p, const float* __restrict__ g, float* __r
     if (nonfinite && __syncthreads_or(bad) && threadIdx.x == 0) atomicAdd(nonfinite, 1);
 }
 
+__global__ void adamw_step_inc_kernel(float* hyper) { hyper[1] += 1.0f; }
+
 }  // namespace ssl4p
 
 using namespace ssl4p;
@@ -60,6 +70,25 @@ extern "C" int ssl4p_adamw_flat(float* p, const float* g, float* m, float* v, vo
     const long long cap = (long long)num_sms() * 8;
     if (blocks > cap) blocks = cap;
     adamw_flat_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(p, g, m, v, (__nv_bfloat16*)p_bf16, wd_flags, n4, lr, beta1, beta2, eps,
-                                                                          weight_decay, 1.0f / bias_corr1, 1.0f / sqrtf(bias_corr2), grad_scale, nonfinite);
+                                                                          weight_decay, 1.0f / bias_corr1, 1.0f / sqrtf(bias_corr2), grad_scale, nonfinite, nullptr);
     return check_launch("adamw_flat_kernel");
+}
+
+extern "C" int ssl4p_adamw_flat_dev(float* p, const float* g, float* m, float* v, void* p_bf16, const uint8_t* wd_flags, long long n,
+                                    float* hyper, float beta1, float beta2, float eps, float weight_decay,
+                                    float grad_scale, int* nonfinite, void* stream) {
+    SSL4P_REQUIRE(p && g && m && v && hyper, "adamw_dev: null pointer");
+    SSL4P_REQUIRE(n >= 0 && n % 4 == 0, "adamw_dev: n must be a multiple of 4 (arena chunks are 256 elements)");
+    if (n > 0) {
+        const long long n4 = n / 4;
+        long long blocks = (n4 + 255) / 256;
+        const long long cap = (long long)num_sms() * 8;
+        if (blocks > cap) blocks = cap;
+        adamw_flat_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(p, g, m, v, (__nv_bfloat16*)p_bf16, wd_flags, n4, 0.f, beta1, beta2, eps,
+                                                                              weight_decay, 1.f, 1.f, grad_scale, nonfinite, hyper);
+        int rc = check_launch("adamw_flat_kernel");
+        if (rc) return rc;
+    }
+    adamw_step_inc_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(hyper);
+    return check_launch("adamw_step_inc_kernel");
 }

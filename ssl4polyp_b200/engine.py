@@ -55,6 +55,14 @@ class TrainEngine:
         self.exp_avg_sq = torch.zeros(n, dtype=torch.float32, device=dev)
         self.nonfinite = torch.zeros(1, dtype=torch.int32, device=dev)
         self.t = 0
+        # per-step scalars live on the device so a captured step can be replayed: hyper = [lr, optimiser steps done]
+        self.hyper = torch.tensor([float(lr), 0.0], dtype=torch.float32, device=dev)
+        self._lr_on_device = float(lr)
+        self._graph = None
+        self._graph_warm = 0
+        self._graph_key = None
+        self._static_in = None
+        self._static_out = None
         self.grad_views = {}
         flags = torch.zeros(n // ALIGN, dtype=torch.uint8)
         rule = no_decay_rule or (lambda name, p: p.ndim == 1 or name.endswith(".bias"))
@@ -88,12 +96,49 @@ class TrainEngine:
         if not do_step:
             return
         self.reducer.finish()
-        self.t += 1
         b1, b2 = self.betas
-        ops.adamw_flat(self.store.flat, self.grads, self.exp_avg, self.exp_avg_sq, self.store.shadow, self.wd_flags,
-                       self.lr if lr is None else lr, b1, b2, self.eps, self.wd, self.t,
-                       grad_scale=1.0 / self.world, nonfinite=self.nonfinite)
+        if not torch.cuda.is_current_stream_capturing():
+            self._set_lr(self.lr if lr is None else lr)
+            self.t += 1
+        ops.adamw_flat_dev(self.store.flat, self.grads, self.exp_avg, self.exp_avg_sq, self.store.shadow, self.wd_flags,
+                           self.hyper, b1, b2, self.eps, self.wd, grad_scale=1.0 / self.world, nonfinite=self.nonfinite)
         self.store.mark_shadow_fresh()
+
+    def _set_lr(self, lr: float) -> None:
+        if lr != self._lr_on_device:
+            self.hyper[0:1].fill_(float(lr))
+            self._lr_on_device = float(lr)
+
+    # ---- CUDA-graph replay of a whole step ---------------------------------------------------------------------
+    def input_buffer(self, *shapes_dtypes):
+        """Static device tensors the captured step reads its batch from; write the batch here (e.g. the H2D copy)
+        to skip the staging copy in `step`."""
+        key = tuple((tuple(s), d) for s, d in shapes_dtypes)
+        if self._static_in is None or self._graph_key != key:
+            self._static_in = [torch.empty(s, dtype=d, device=self.device) for s, d in shapes_dtypes]
+            self._graph_key, self._graph, self._graph_warm = key, None, 0
+        return self._static_in
+
+    def _replay(self, eager_step, inputs, lr):
+        """Run `eager_step(*static_inputs)` from a CUDA graph (the first two calls run eagerly, the third
+        captures).  One cudaGraphLaunch replaces the ~500 kernel launches of the step."""
+        static = self.input_buffer(*[(t.shape, t.dtype) for t in inputs])
+        for dst, src in zip(static, inputs):
+            if dst.data_ptr() != src.data_ptr():
+                dst.copy_(src, non_blocking=True)
+        self._set_lr(self.lr if lr is None else lr)
+        if self._graph is None:
+            if self._graph_warm < 2:                          # lazy attribute / NCCL / workspace initialisation happens
+                self._graph_warm += 1                         # in ordinary eager steps on the caller's own batches
+                return eager_step(*static)
+            torch.cuda.synchronize()
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                self._static_out = eager_step(*static)
+            self._graph = g
+        self._graph.replay()
+        self.t += 1
+        return self._static_out
 
     def nonfinite_count(self) -> int:
         """Number of optimiser blocks that saw a non-finite gradient so far (host sync: call off the hot path)."""
@@ -124,6 +169,7 @@ class TrainEngine:
             self.exp_avg_sq[a:a + cnt].copy_(st["exp_avg_sq"].reshape(-1))
             if not sd.get("t"):
                 self.t = int(float(st["step"]))
+        self.hyper[1:2].fill_(float(self.t))
 
 
 class PretrainEngine(TrainEngine):
@@ -134,7 +180,15 @@ class PretrainEngine(TrainEngine):
         self.mask_ratio = mask_ratio
         self._one = torch.ones((), dtype=torch.float32, device=self.device)
 
-    def step(self, imgs, lr=None, noise=None, accum_iter: int = 1, micro_index: int = 0):
+    def step(self, imgs, lr=None, noise=None, accum_iter: int = 1, micro_index: int = 0, graph: bool = False):
+        """graph=True replays the whole step (noise draw, forward, backward, bucket all-reduces, AdamW) from a CUDA
+        graph; the returned loss tensor is then a static buffer overwritten by the next call."""
+        if graph:
+            if accum_iter != 1:
+                raise RuntimeError("graph replay does not accumulate gradients")
+            if noise is not None:                             # caller-supplied noise becomes a second static input
+                return self._replay(lambda x, z: self.step(x, noise=z), [imgs, noise], lr)
+            return self._replay(lambda x: self.step(x), [imgs], lr)
         m = self.model
         if noise is None:
             noise = torch.rand(imgs.shape[0], m.patch_embed.num_patches, device=imgs.device)   # models_mae.py:132
@@ -155,7 +209,9 @@ class ClassifierEngine(TrainEngine):
         super().__init__(model, lr, weight_decay, betas, **kw)
         self.pos_weight = pos_weight
 
-    def step(self, imgs, target, lr=None):
+    def step(self, imgs, target, lr=None, graph: bool = False):
+        if graph:
+            return self._replay(lambda x, y: self.step(x, y), [imgs, target], lr)
         m = self.model
         logits, sv = vit_core.classifier_fwd(self.store, m._dims, imgs, m.out_token == "spatial", True)
         lg = logits.detach().requires_grad_(True)

@@ -370,6 +370,15 @@ def adamw_flat(p, g, m, v, p_bf16, wd_flags, lr, beta1, beta2, eps, weight_decay
                                     float(grad_scale), _ptr(nonfinite), _stream()), "adamw_flat")
 
 
+def adamw_flat_dev(p, g, m, v, p_bf16, wd_flags, hyper, beta1, beta2, eps, weight_decay, grad_scale=1.0, nonfinite=None):
+    """AdamW with lr = hyper[0] and the step counter hyper[1] on the device (CUDA-graph replayable)."""
+    lib = _lib.load()
+    _req(hyper, f32, "hyper")
+    _lib.check(lib.ssl4p_adamw_flat_dev(p.data_ptr(), g.data_ptr(), m.data_ptr(), v.data_ptr(), _ptr(p_bf16), _ptr(wd_flags), p.numel(),
+                                        hyper.data_ptr(), float(beta1), float(beta2), float(eps), float(weight_decay),
+                                        float(grad_scale), _ptr(nonfinite), _stream()), "adamw_flat_dev")
+
+
 def pool_head_fwd(xn, W, b, N, T, D, spatial):
     lib = _lib.load()
     ncls = W.shape[0]

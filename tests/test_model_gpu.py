@@ -229,3 +229,70 @@ def test_classifier_finetune_modes_prune_backward():
     with torch.no_grad():
         out = m.eval()(imgs)
     assert not out.requires_grad
+
+
+def _small_mae(seed=0):
+    from functools import partial
+    from ssl4polyp_b200 import models_mae
+    torch.manual_seed(seed)
+    kw = dict(img_size=64, patch_size=16, in_chans=3, embed_dim=64, depth=2, num_heads=2, decoder_embed_dim=64,
+              decoder_depth=1, decoder_num_heads=2, mlp_ratio=4.)
+    return models_mae.MaskedAutoencoderViT(norm_layer=partial(torch.nn.LayerNorm, eps=1e-6), norm_pix_loss=True, **kw).to(dev()).train()
+
+
+def test_engine_graph_replay_matches_eager_steps():
+    """The captured step (noise draw, fwd, bwd, AdamW with device-resident lr/step) must walk the same trajectory as
+    the eager step on the same images and noise: losses and weights agree to fp32 round-off.  (With self-drawn noise
+    the captured torch.rand consumes the Philox stream at a different offset, so only the loss trend is checked.)"""
+    from ssl4polyp_b200.engine import PretrainEngine
+    imgs = [synth_imgs(4, s, 64).to(dev()) for s in range(2)]
+    out = {}
+    for mode in (False, True):
+        m = _small_mae(0)
+        eng = PretrainEngine(m, lr=1e-3, weight_decay=0.05)
+        gen = torch.Generator().manual_seed(123)
+        losses = []
+        for i in range(6):
+            lr = 1e-3 * (1.0 - 0.1 * i)                      # the schedule writes a new lr every iteration
+            noise = torch.rand(4, 16, generator=gen).to(dev())
+            losses.append(float(eng.step(imgs[i % 2], lr=lr, noise=noise, graph=mode).item()))
+        out[mode] = (losses, eng.store.flat.detach().clone(), eng.t)
+        assert eng.nonfinite_count() == 0
+    (le, we, te), (lg, wg, tg) = out[False], out[True]
+    assert te == tg == 6
+    assert lg[-1] < lg[0]
+    for a, b in zip(le, lg):
+        assert abs(a - b) <= 1e-5 * max(1.0, abs(a)), (le, lg)
+    assert torch.allclose(we, wg, rtol=1e-5, atol=1e-6)
+    m = _small_mae(0)
+    eng = PretrainEngine(m, lr=1e-3, weight_decay=0.05)
+    own = [float(eng.step(imgs[0], graph=True).item()) for _ in range(8)]     # noise drawn inside the captured step
+    assert own[-1] < own[0] and all(x == x for x in own)
+    assert len({round(x, 6) for x in own[3:]}) > 1           # replays do advance the noise stream
+
+
+def test_engine_step_matches_oracle_adamw_step():
+    """One engine step == the reference's step restated on the CPU oracle (engine_pretrain.py:50-72 with fp32,
+    torch.optim.AdamW over timm's weight-decay groups): updated weights agree (bf16 operand noise only)."""
+    from ssl4polyp_b200.engine import PretrainEngine
+    m = _small_mae(1)
+    cfg = O.MAEConfig(img_size=64, embed_dim=64, depth=2, num_heads=2, decoder_embed_dim=64, decoder_depth=1,
+                      decoder_num_heads=2, norm_pix_loss=True)
+    sd = {k: v.detach().cpu().clone() for k, v in m.state_dict().items()}
+    params = {k: v.clone().requires_grad_(k not in ("pos_embed", "decoder_pos_embed")) for k, v in sd.items()}
+    opt = torch.optim.AdamW(O.weight_decay_groups(params.items(), 0.05), lr=1e-3, betas=(0.9, 0.95))
+    imgs = synth_imgs(4, 7, 64)
+    noise = torch.rand(4, 16, generator=torch.Generator().manual_seed(5))
+    eng = PretrainEngine(m, lr=1e-3, weight_decay=0.05, betas=(0.9, 0.95))
+    for _ in range(3):
+        loss_o, _, _ = O.mae_forward(params, imgs, noise, 0.75, cfg)
+        opt.zero_grad(set_to_none=True)
+        loss_o.backward()
+        opt.step()
+        loss = eng.step(imgs.to(dev()), noise=noise.to(dev()))
+        assert abs(loss.item() - loss_o.item()) <= LOSS_RTOL * abs(loss_o.item())
+    for k, p in m.named_parameters():
+        delta_o = params[k].detach() - sd[k]
+        delta = p.detach().cpu() - sd[k]
+        if delta_o.abs().max() > 0:
+            assert cos(delta, delta_o) > 0.98, k
