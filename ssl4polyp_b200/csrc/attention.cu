@@ -403,7 +403,7 @@ static int attn_check(int B, int T, int H, int hd) {
     return SSL4P_OK;
 }
 
-extern "C" int ssl4p_attention_fwd(const void* qkv, void* out, float* lse, int B, int T, int H, int hd, float scale, void* stream) {
+extern "C" int ssl4p_attention_fwd_mma(const void* qkv, void* out, float* lse, int B, int T, int H, int hd, float scale, void* stream) {
     SSL4P_REQUIRE(qkv && out && lse, "attention_fwd: null pointer");
     int rc = attn_check(B, T, H, hd);
     if (rc) return rc;
@@ -416,7 +416,7 @@ extern "C" int ssl4p_attention_fwd(const void* qkv, void* out, float* lse, int B
     return launch_fwd<32, 26, 4>(qkv, out, lse, B, T, H, scale, s);
 }
 
-extern "C" int ssl4p_attention_bwd(const void* qkv, const void* out, const void* dout, const float* lse, void* dqkv,
+extern "C" int ssl4p_attention_bwd_mma(const void* qkv, const void* out, const void* dout, const float* lse, void* dqkv,
                                    int B, int T, int H, int hd, float scale, void* stream) {
     SSL4P_REQUIRE(qkv && out && dout && lse && dqkv, "attention_bwd: null pointer");
     int rc = attn_check(B, T, H, hd);

@@ -1,0 +1,708 @@
+// Fused multi-head self-attention forward/backward on the 5th-gen tensor cores (tcgen05 + TMEM), TMA-fed.
+//
+// Replaces timm 0.4.12 Attention.forward as used by /root/reference/src/ssl4polyp/models/mae/models_mae.py:166,186 and
+// models.py:205-207:  softmax(q k^T * hd^-0.5) v  on qkv [B, T, 3, H, hd]  (T = 50 encoder, 197 decoder/classifier;
+// hd = 64 / 32), and its autograd backward.  Nothing of size [B,H,T,T] ever touches HBM.
+//
+// Work item = (image b, 64-column slice of the head dimension) = one head (hd 64) or a PAIR of heads (hd 32): every
+// operand tile is then a [rows x 64 bf16] TMA box in the SWIZZLE_128B layout the GEMM kernel already uses, and a head
+// inside a pair is selected by the K offset of the UMMA descriptor (K-major operands) or by the half of the 64
+// accumulator columns that is kept (MN-major operands).  Rows t >= T are zero-filled by TMA (3-D tensor map
+// {column, token, image}), so padding needs no HBM traffic and no masking of the operands.
+//
+// Forward  (persistent, 1 CTA / SM, 320 threads):
+//   warps 0-3 / 4-7 : two softmax warpgroups; thread r owns row r of a 128-query tile (TMEM lane r)
+//   warp 8          : TMA producer (Q, K, V tiles of the next item)
+//   warp 9          : tcgen05.mma issuer, event driven: per warpgroup a chain  S = Q K^T -> [softmax] -> O = P V
+//   S (fp32, <= 256 columns) lives in TMEM; P (bf16) goes through shared memory in the K-major SW128 layout; O is
+//   accumulated in the TMEM columns S occupied (S is dead once P has been written).
+// Backward (persistent, 1 CTA / SM, 320 threads): per head, blocks of 128 keys x 128 queries:
+//   S^T = K Q^T and dP^T = V dO^T into TMEM; 8 warps turn them into P^T and dS^T (bf16, shared memory) using the saved
+//   log-sum-exp and D = rowsum(dO * O); then dV += P^T dO, dK += dS^T Q, dQ += dS K accumulate in TMEM.
+//   Deterministic (no atomics).
+#include "common.cuh"
+#include "ssl4p.h"
+#include <mutex>
+#include <unordered_map>
+
+namespace ssl4p {
+
+constexpr int kAttnThreads = 320;
+constexpr float kLog2eF = 1.4426950408889634f;
+
+__device__ __forceinline__ float fast_exp2(float x) {
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+
+// 3-D tiled load: coordinates {c0 = column, c1 = token, c2 = image}
+__device__ __forceinline__ void tma_load_3d(void* smem_dst, const CUtensorMap* m, uint64_t* bar, int c0, int c1, int c2) {
+    asm volatile(
+        "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+        ::"r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2)
+        : "memory");
+}
+
+__device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
+    asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+
+// runtime-N instruction descriptor (same fields as umma_idesc_bf16)
+__device__ __forceinline__ uint32_t idesc_rt(int M, int N, bool a_mn, bool b_mn) {
+    return (1u << 4) | (1u << 7) | (1u << 10) | ((a_mn ? 1u : 0u) << 15) | ((b_mn ? 1u : 0u) << 16) |
+           ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+
+// byte offset of the 16-byte chunk `chunk16` (0..7) of row `row` inside a [rows x 128 B] SWIZZLE_128B tile
+__device__ __forceinline__ uint32_t sw128_off(int row, int chunk16) {
+    return (uint32_t)row * 128u + (uint32_t)((chunk16 ^ (row & 7)) << 4);
+}
+
+constexpr int kTileBytes = 128 * 128;          // one [128 rows x 64 bf16] SW128 tile
+
+struct AttnFwdParams {
+    int T, H, items, slices_per_img;           // slices_per_img = H*hd/64
+    int Npad, NB, NKB;                         // keys padded to 16; query tiles of 128; key boxes of 128 rows
+    float scale;
+    __nv_bfloat16* out;                        // [B*T, H*hd]
+    float* lse;                                // [B, H, T]
+};
+
+// =========================================================================================================
+// forward
+// =========================================================================================================
+template <int HD>
+__global__ void __launch_bounds__(kAttnThreads, 1)
+attention_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnFwdParams p) {
+    constexpr int HP = 64 / HD;                                  // heads per work item
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    uint8_t* sQ = smem;                                          // 2 tiles
+    uint8_t* sK = smem + 2 * kTileBytes;                         // 2 tiles
+    uint8_t* sV = smem + 4 * kTileBytes;                         // 2 tiles
+    uint8_t* sP = smem + 6 * kTileBytes;                         // 2 warpgroups x 4 key chunks x 16 KB
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 14 * kTileBytes);
+    uint64_t* qkv_full = bars;                                   // [1]
+    uint64_t* qkv_empty = bars + 1;                              // [1]
+    uint64_t* s_full = bars + 2;                                 // [2]
+    uint64_t* p_full = bars + 4;                                 // [2]
+    uint64_t* o_full = bars + 6;                                 // [2]
+    uint64_t* s_empty = bars + 8;                                // [2]
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 10);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = lane_id();
+    const int NT = HP * p.NB;                                    // tiles per item
+    const int my_items = p.items > (int)blockIdx.x ? (p.items - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
+
+    if (warp == 8 && lane == 0) tma_prefetch_desc(&tmQKV);
+    if (warp == 9) {
+        if (lane == 0) {
+            mbar_init(qkv_full, 1);
+            mbar_init(qkv_empty, NT);
+            for (int i = 0; i < 2; ++i) {
+                mbar_init(&s_full[i], 1); mbar_init(&p_full[i], 128); mbar_init(&o_full[i], 1); mbar_init(&s_empty[i], 128);
+            }
+            mbar_fence_init();
+            fence_proxy_async();
+        }
+        __syncwarp();
+        tmem_alloc<512>(tmem_slot);
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 8) {
+        // ===================== TMA producer =====================
+        if (lane == 0) {
+            const int HHD = p.H * HD;
+            for (int il = 0; il < my_items; ++il) {
+                const int item = blockIdx.x + il * gridDim.x;
+                const int b = item / p.slices_per_img, sl = item % p.slices_per_img;
+                mbar_wait(qkv_empty, (il & 1) ^ 1);
+                mbar_expect_tx(qkv_full, (uint32_t)(p.NB + 2 * p.NKB) * kTileBytes);
+                for (int i = 0; i < p.NB; ++i) tma_load_3d(sQ + i * kTileBytes, &tmQKV, qkv_full, sl * 64, i * 128, b);
+                for (int i = 0; i < p.NKB; ++i) {
+                    tma_load_3d(sK + i * kTileBytes, &tmQKV, qkv_full, HHD + sl * 64, i * 128, b);
+                    tma_load_3d(sV + i * kTileBytes, &tmQKV, qkv_full, 2 * HHD + sl * 64, i * 128, b);
+                }
+            }
+        }
+        __syncwarp();
+    } else if (warp == 9) {
+        // ===================== MMA issuer (one thread, two chains) =====================
+        if (lane == 0) {
+            const uint32_t idesc_s = idesc_rt(128, p.Npad, false, false);
+            const uint32_t idesc_o = idesc_rt(128, 64, false, true);
+            const int total = my_items * NT;
+            int nxt[2] = {0, 1};
+            int stage[2] = {0, 0};
+            int loaded = 0;                                       // completions of qkv_full observed so far (in order)
+            const uint32_t sQa = smem_u32(sQ), sKa = smem_u32(sK), sVa = smem_u32(sV), sPa = smem_u32(sP);
+            while (nxt[0] < total || nxt[1] < total) {
+#pragma unroll
+                for (int w = 0; w < 2; ++w) {
+                    const int g = nxt[w];
+                    if (g >= total) continue;
+                    const int u = g >> 1, il = g / NT, t = g - il * NT;
+                    const uint32_t tmem_d = tmem_base + (uint32_t)w * 256u;
+                    if (stage[w] == 0) {
+                        if (loaded <= il && mbar_try_wait(qkv_full, loaded & 1)) ++loaded;   // the barrier is at most one phase ahead
+                        if (loaded <= il) continue;
+                        if (!mbar_try_wait(&s_empty[w], (u & 1) ^ 1)) continue;
+                        tc_fence_after();
+                        const int hh = t / p.NB, mb = t - hh * p.NB;
+                        const uint32_t a0 = sQa + mb * kTileBytes + hh * (HD * 2);
+                        const uint32_t b0 = sKa + hh * (HD * 2);
+#pragma unroll
+                        for (int kk = 0; kk < HD / 16; ++kk)
+                            umma_bf16(tmem_d, umma_smem_desc(a0 + kk * 32, 16, 1024), umma_smem_desc(b0 + kk * 32, 16, 1024), idesc_s, kk > 0);
+                        umma_commit(&s_full[w]);
+                        stage[w] = 1;
+                    } else {
+                        if (!mbar_try_wait(&p_full[w], u & 1)) continue;
+                        tc_fence_after();
+                        const uint32_t pa = sPa + (uint32_t)w * 4u * kTileBytes;
+                        const int ksteps = p.Npad >> 4;
+                        for (int ks = 0; ks < ksteps; ++ks)
+                            umma_bf16(tmem_d, umma_smem_desc(pa + (ks >> 2) * kTileBytes + (ks & 3) * 32, 16, 1024),
+                                      umma_smem_desc(sVa + ks * 2048, kTileBytes, 1024), idesc_o, ks > 0);
+                        umma_commit(&o_full[w]);
+                        umma_commit(qkv_empty);
+                        stage[w] = 0;
+                        nxt[w] = g + 2;
+                    }
+                }
+            }
+        }
+        __syncwarp();
+    } else {
+        // ===================== softmax warpgroups =====================
+        const int wg = warp >> 2, q4 = warp & 3;
+        const int row = q4 * 32 + lane;
+        const uint32_t taddr = tmem_base + ((uint32_t)(q4 * 32) << 16) + (uint32_t)wg * 256u;
+        uint8_t* pw = sP + wg * 4 * kTileBytes;
+        const float sl2 = p.scale * kLog2eF;
+        for (int il = 0; il < my_items; ++il) {
+            const int item = blockIdx.x + il * gridDim.x;
+            const int b = item / p.slices_per_img, sl = item % p.slices_per_img;
+            for (int t = 0; t < NT; ++t) {
+                const int g = il * NT + t;
+                if ((g & 1) != wg) continue;
+                const int u = g >> 1;
+                const int hh = t / p.NB, mb = t - hh * p.NB;
+                const int head = sl * HP + hh;
+                const int qrow = mb * 128 + row;
+                mbar_wait(&s_full[wg], u & 1);
+                tc_fence_after();
+                // ---- pass 1: row maximum over the valid keys
+                float mx = -INFINITY;
+                for (int c = 0; c < p.Npad; c += 32) {
+                    uint32_t r[32];
+                    tmem_ld_32x32(taddr + c, r);
+                    tmem_ld_wait();
+                    if (c + 32 <= p.T) {
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) mx = fmaxf(mx, __uint_as_float(r[j]));
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) if (c + j < p.T) mx = fmaxf(mx, __uint_as_float(r[j]));
+                    }
+                }
+                // ---- pass 2: p = exp2((s - max) * scale * log2e), row sum, bf16 P into the SW128 K-major tile
+                const float msl = mx * sl2;
+                float sum = 0.f;
+                for (int c = 0; c < p.Npad; c += 32) {
+                    uint32_t r[32];
+                    tmem_ld_32x32(taddr + c, r);
+                    tmem_ld_wait();
+                    float e[32];
+                    if (c + 32 <= p.T) {
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) e[j] = fast_exp2(fmaf(__uint_as_float(r[j]), sl2, -msl));
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) e[j] = (c + j < p.T) ? fast_exp2(fmaf(__uint_as_float(r[j]), sl2, -msl)) : 0.f;
+                    }
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) sum += e[j];
+                    uint8_t* tile = pw + (c >> 6) * kTileBytes;
+                    const int sub = (c & 63) >> 3;
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        uint4 o;
+                        o.x = pack_bf16(e[8 * i + 0], e[8 * i + 1]); o.y = pack_bf16(e[8 * i + 2], e[8 * i + 3]);
+                        o.z = pack_bf16(e[8 * i + 4], e[8 * i + 5]); o.w = pack_bf16(e[8 * i + 6], e[8 * i + 7]);
+                        *reinterpret_cast<uint4*>(tile + sw128_off(row, sub + i)) = o;
+                    }
+                }
+                fence_proxy_async();                              // generic-proxy smem writes -> visible to the tensor core
+                tc_fence_before();
+                mbar_arrive(&p_full[wg]);
+                // ---- epilogue: O / rowsum -> bf16
+                mbar_wait(&o_full[wg], u & 1);
+                tc_fence_after();
+                const float inv = 1.0f / sum;
+                if constexpr (HD == 64) {
+#pragma unroll
+                    for (int half = 0; half < 2; ++half) {
+                        uint32_t r[32];
+                        tmem_ld_32x32(taddr + half * 32, r);
+                        tmem_ld_wait();
+                        if (qrow < p.T) {
+                            __nv_bfloat16* dst = p.out + ((size_t)(b * p.T + qrow) * p.H + head) * HD + half * 32;
+#pragma unroll
+                            for (int i = 0; i < 4; ++i) {
+                                uint4 o;
+                                o.x = pack_bf16(__uint_as_float(r[8 * i + 0]) * inv, __uint_as_float(r[8 * i + 1]) * inv);
+                                o.y = pack_bf16(__uint_as_float(r[8 * i + 2]) * inv, __uint_as_float(r[8 * i + 3]) * inv);
+                                o.z = pack_bf16(__uint_as_float(r[8 * i + 4]) * inv, __uint_as_float(r[8 * i + 5]) * inv);
+                                o.w = pack_bf16(__uint_as_float(r[8 * i + 6]) * inv, __uint_as_float(r[8 * i + 7]) * inv);
+                                *reinterpret_cast<uint4*>(dst + 8 * i) = o;
+                            }
+                        }
+                    }
+                } else {
+                    uint32_t r[32];
+                    tmem_ld_32x32(taddr + hh * 32, r);
+                    tmem_ld_wait();
+                    if (qrow < p.T) {
+                        __nv_bfloat16* dst = p.out + ((size_t)(b * p.T + qrow) * p.H + head) * HD;
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) {
+                            uint4 o;
+                            o.x = pack_bf16(__uint_as_float(r[8 * i + 0]) * inv, __uint_as_float(r[8 * i + 1]) * inv);
+                            o.y = pack_bf16(__uint_as_float(r[8 * i + 2]) * inv, __uint_as_float(r[8 * i + 3]) * inv);
+                            o.z = pack_bf16(__uint_as_float(r[8 * i + 4]) * inv, __uint_as_float(r[8 * i + 5]) * inv);
+                            o.w = pack_bf16(__uint_as_float(r[8 * i + 6]) * inv, __uint_as_float(r[8 * i + 7]) * inv);
+                            *reinterpret_cast<uint4*>(dst + 8 * i) = o;
+                        }
+                    }
+                }
+                if (qrow < p.T) p.lse[((size_t)b * p.H + head) * p.T + qrow] = mx * p.scale + __logf(sum);
+                tc_fence_before();
+                mbar_arrive(&s_empty[wg]);
+            }
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 9) {
+        tc_fence_after();
+        tmem_dealloc<512>(tmem_base);
+    }
+}
+
+// =========================================================================================================
+// backward
+// =========================================================================================================
+struct AttnBwdParams {
+    int T, H, items, slices_per_img;
+    int Npad, NB;
+    float scale;
+    const __nv_bfloat16* out;                  // [B*T, H*hd]
+    const __nv_bfloat16* dout;                 // [B*T, H*hd]
+    const float* lse;                          // [B, H, T]
+    __nv_bfloat16* dqkv;                       // [B*T, 3*H*hd]
+};
+
+// 32 fp32 TMEM columns of this thread's row -> 32 bf16 at dst (16-byte stores)
+__device__ __forceinline__ void store_row32_bf16(__nv_bfloat16* dst, const uint32_t (&r)[32]) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        uint4 o;
+        o.x = pack_bf16(__uint_as_float(r[8 * i + 0]), __uint_as_float(r[8 * i + 1]));
+        o.y = pack_bf16(__uint_as_float(r[8 * i + 2]), __uint_as_float(r[8 * i + 3]));
+        o.z = pack_bf16(__uint_as_float(r[8 * i + 4]), __uint_as_float(r[8 * i + 5]));
+        o.w = pack_bf16(__uint_as_float(r[8 * i + 6]), __uint_as_float(r[8 * i + 7]));
+        *reinterpret_cast<uint4*>(dst + 8 * i) = o;
+    }
+}
+
+// TMEM column map (512 columns): S^T [0,128)  dP^T [128,256)  dV [256,320)  dK [320,384)  dQ[qt] [384 + 64 qt, +64)
+constexpr uint32_t kColST = 0, kColDP = 128, kColDV = 256, kColDK = 320, kColDQ = 384;
+
+template <int HD>
+__global__ void __launch_bounds__(kAttnThreads, 1)
+attention_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CUtensorMap tmDO, const AttnBwdParams p) {
+    constexpr int HP = 64 / HD;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    uint8_t* sQ = smem;                                          // 2 tiles each
+    uint8_t* sK = smem + 2 * kTileBytes;
+    uint8_t* sV = smem + 4 * kTileBytes;
+    uint8_t* sDO = smem + 6 * kTileBytes;
+    uint8_t* sPT = smem + 8 * kTileBytes;                        // [128 keys] x 2 chunks of 64 queries
+    uint8_t* sDS = smem + 10 * kTileBytes;
+    float* sL = reinterpret_cast<float*>(smem + 12 * kTileBytes);   // [HP][256] lse * log2e (+inf for q >= T)
+    float* sD = sL + HP * 256;                                      // [HP][256] D * scale
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 12 * kTileBytes + 4096);
+    uint64_t* in_full = bars;
+    uint64_t* in_empty = bars + 1;
+    uint64_t* st_full = bars + 2;
+    uint64_t* pt_full = bars + 3;
+    uint64_t* blk_done = bars + 4;
+    uint64_t* dvk_full = bars + 5;
+    uint64_t* dvk_empty = bars + 6;
+    uint64_t* dq_full = bars + 7;
+    uint64_t* dq_empty = bars + 8;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 9);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = lane_id();
+    const int my_items = p.items > (int)blockIdx.x ? (p.items - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
+    const int HHD = p.H * HD;
+
+    if (warp == 8 && lane == 0) { tma_prefetch_desc(&tmQKV); tma_prefetch_desc(&tmDO); }
+    if (warp == 9) {
+        if (lane == 0) {
+            mbar_init(in_full, 1); mbar_init(in_empty, 1);
+            mbar_init(st_full, 1); mbar_init(pt_full, 256); mbar_init(blk_done, 1);
+            mbar_init(dvk_full, 1); mbar_init(dvk_empty, 256);
+            mbar_init(dq_full, 1); mbar_init(dq_empty, 256);
+            mbar_fence_init();
+            fence_proxy_async();
+        }
+        __syncwarp();
+        tmem_alloc<512>(tmem_slot);
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 8) {
+        // ===================== TMA producer =====================
+        if (lane == 0) {
+            for (int il = 0; il < my_items; ++il) {
+                const int item = blockIdx.x + il * gridDim.x;
+                const int b = item / p.slices_per_img, sl = item % p.slices_per_img;
+                mbar_wait(in_empty, (il & 1) ^ 1);
+                mbar_expect_tx(in_full, (uint32_t)(4 * p.NB) * kTileBytes);
+                for (int i = 0; i < p.NB; ++i) {
+                    tma_load_3d(sQ + i * kTileBytes, &tmQKV, in_full, sl * 64, i * 128, b);
+                    tma_load_3d(sK + i * kTileBytes, &tmQKV, in_full, HHD + sl * 64, i * 128, b);
+                    tma_load_3d(sV + i * kTileBytes, &tmQKV, in_full, 2 * HHD + sl * 64, i * 128, b);
+                    tma_load_3d(sDO + i * kTileBytes, &tmDO, in_full, sl * 64, i * 128, b);
+                }
+            }
+        }
+        __syncwarp();
+    } else if (warp == 9) {
+        // ===================== MMA issuer =====================
+        if (lane == 0) {
+            const uint32_t sQa = smem_u32(sQ), sKa = smem_u32(sK), sVa = smem_u32(sV), sDOa = smem_u32(sDO);
+            const uint32_t sPTa = smem_u32(sPT), sDSa = smem_u32(sDS);
+            const uint32_t idesc_acc = idesc_rt(128, 64, false, true);     // A K-major (P^T / dS^T rows = keys), B MN-major
+            const uint32_t idesc_dq = idesc_rt(128, 64, true, true);       // A MN-major (dS^T read as [keys][queries]), B MN-major
+            int nblk = 0, nkt = 0, nhead = 0;
+            for (int il = 0; il < my_items; ++il) {
+                mbar_wait(in_full, il & 1);
+                tc_fence_after();
+                for (int hh = 0; hh < HP; ++hh, ++nhead) {
+                    const uint32_t koff = hh * (HD * 2);
+                    mbar_wait(dq_empty, (nhead & 1) ^ 1);                 // previous head's dQ has been read out
+                    tc_fence_after();
+                    for (int kt = 0; kt < p.NB; ++kt, ++nkt) {
+                        mbar_wait(dvk_empty, (nkt & 1) ^ 1);              // previous key tile's dV/dK have been read out
+                        tc_fence_after();
+                        for (int qt = 0; qt < p.NB; ++qt, ++nblk) {
+                            const int nq = min(128, p.Npad - qt * 128);
+                            const uint32_t idesc_s = idesc_rt(128, nq, false, false);
+                            // S^T = K[kt] Q[qt]^T ; dP^T = V[kt] dO[qt]^T   (TMEM columns were drained before pt_full of the previous block)
+#pragma unroll
+                            for (int kk = 0; kk < HD / 16; ++kk)
+                                umma_bf16(tmem_base + kColST, umma_smem_desc(sKa + kt * kTileBytes + koff + kk * 32, 16, 1024),
+                                          umma_smem_desc(sQa + qt * kTileBytes + koff + kk * 32, 16, 1024), idesc_s, kk > 0);
+#pragma unroll
+                            for (int kk = 0; kk < HD / 16; ++kk)
+                                umma_bf16(tmem_base + kColDP, umma_smem_desc(sVa + kt * kTileBytes + koff + kk * 32, 16, 1024),
+                                          umma_smem_desc(sDOa + qt * kTileBytes + koff + kk * 32, 16, 1024), idesc_s, kk > 0);
+                            umma_commit(st_full);
+                            mbar_wait(pt_full, nblk & 1);
+                            tc_fence_after();
+                            const int ksteps = nq >> 4;
+                            for (int ks = 0; ks < ksteps; ++ks) {
+                                const uint32_t aoff = (ks >> 2) * kTileBytes + (ks & 3) * 32;
+                                // dV[kt] += P^T dO[qt]
+                                umma_bf16(tmem_base + kColDV, umma_smem_desc(sPTa + aoff, 16, 1024),
+                                          umma_smem_desc(sDOa + qt * kTileBytes + ks * 2048, kTileBytes, 1024), idesc_acc, (qt > 0) || (ks > 0));
+                                // dK[kt] += dS^T Q[qt]
+                                umma_bf16(tmem_base + kColDK, umma_smem_desc(sDSa + aoff, 16, 1024),
+                                          umma_smem_desc(sQa + qt * kTileBytes + ks * 2048, kTileBytes, 1024), idesc_acc, (qt > 0) || (ks > 0));
+                            }
+                            // dQ[qt] += dS K[kt] : A = dS^T tile read MN-major (M = queries: 2 chunks of 64, 16 KB apart; K = keys)
+#pragma unroll
+                            for (int ks = 0; ks < 8; ++ks)
+                                umma_bf16(tmem_base + kColDQ + qt * 64, umma_smem_desc(sDSa + ks * 2048, kTileBytes, 1024),
+                                          umma_smem_desc(sKa + kt * kTileBytes + ks * 2048, kTileBytes, 1024), idesc_dq, (kt > 0) || (ks > 0));
+                            umma_commit(blk_done);
+                        }
+                        umma_commit(dvk_full);
+                    }
+                    umma_commit(dq_full);
+                }
+                umma_commit(in_empty);
+            }
+        }
+        __syncwarp();
+    } else {
+        // ===================== element-wise warps (256 threads) =====================
+        const int q4 = warp & 3, half = warp >> 2;
+        const int row = q4 * 32 + lane;                          // key row inside the 128-key tile (TMEM lane)
+        const uint32_t tlane = tmem_base + ((uint32_t)(q4 * 32) << 16);
+        const float sl2 = p.scale * kLog2eF;
+        const int tid = threadIdx.x;                             // 0..255
+        int nblk = 0, nkt = 0, nhead = 0;
+        for (int il = 0; il < my_items; ++il) {
+            const int item = blockIdx.x + il * gridDim.x;
+            const int b = item / p.slices_per_img, sl = item % p.slices_per_img;
+            // ---- per-query statistics of both heads: lse*log2e and D*scale, D = sum_d dO*O
+            named_bar_sync(1, 256);
+            for (int hh = 0; hh < HP; ++hh) {
+                const int head = sl * HP + hh;
+                const int q = tid;
+                float lv = INFINITY, dv = 0.f;
+                if (q < p.T) {
+                    const size_t off = ((size_t)(b * p.T + q) * p.H + head) * HD;
+                    float acc = 0.f;
+#pragma unroll
+                    for (int c = 0; c < HD / 8; ++c) {
+                        const uint4 a = *reinterpret_cast<const uint4*>(p.out + off + c * 8);
+                        const uint4 d = *reinterpret_cast<const uint4*>(p.dout + off + c * 8);
+                        const uint32_t aw[4] = {a.x, a.y, a.z, a.w}, dw[4] = {d.x, d.y, d.z, d.w};
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) { const float2 x = unpack_bf16(aw[j]), y = unpack_bf16(dw[j]); acc += x.x * y.x + x.y * y.y; }
+                    }
+                    dv = acc * p.scale;
+                    lv = p.lse[((size_t)b * p.H + head) * p.T + q] * kLog2eF;
+                }
+                sL[hh * 256 + q] = lv;
+                sD[hh * 256 + q] = dv;
+            }
+            named_bar_sync(1, 256);
+
+            for (int hh = 0; hh < HP; ++hh, ++nhead) {
+                const int head = sl * HP + hh;
+                const float* L = sL + hh * 256;
+                const float* Dq = sD + hh * 256;
+                for (int kt = 0; kt < p.NB; ++kt, ++nkt) {
+                    const int key = kt * 128 + row;
+                    const bool key_ok = key < p.T;
+                    for (int qt = 0; qt < p.NB; ++qt, ++nblk) {
+                        const int nq = min(128, p.Npad - qt * 128);
+                        mbar_wait(st_full, nblk & 1);
+                        tc_fence_after();
+                        if (nblk > 0) mbar_wait(blk_done, (nblk - 1) & 1);     // P^T / dS^T tiles of the previous block consumed
+#pragma unroll 1
+                        for (int cc = 0; cc < 2; ++cc) {
+                            const int c = half * 64 + cc * 32;                  // column (query) offset inside the block
+                            if (c >= nq) break;
+                            uint32_t rs[32], rd[32];
+                            tmem_ld_32x32(tlane + kColST + c, rs);
+                            tmem_ld_32x32(tlane + kColDP + c, rd);
+                            tmem_ld_wait();
+                            const int q0 = qt * 128 + c;
+                            uint32_t pw[16], dw[16];
+#pragma unroll
+                            for (int j = 0; j < 32; j += 2) {
+                                const float2 l2 = *reinterpret_cast<const float2*>(L + q0 + j);
+                                const float2 d2 = *reinterpret_cast<const float2*>(Dq + q0 + j);
+                                float p0 = fast_exp2(fmaf(__uint_as_float(rs[j]), sl2, -l2.x));
+                                float p1 = fast_exp2(fmaf(__uint_as_float(rs[j + 1]), sl2, -l2.y));
+                                float e0 = p0 * fmaf(__uint_as_float(rd[j]), p.scale, -d2.x);
+                                float e1 = p1 * fmaf(__uint_as_float(rd[j + 1]), p.scale, -d2.y);
+                                if (!key_ok || q0 + j >= p.T) { p0 = 0.f; e0 = 0.f; }
+                                if (!key_ok || q0 + j + 1 >= p.T) { p1 = 0.f; e1 = 0.f; }
+                                pw[j >> 1] = pack_bf16(p0, p1);
+                                dw[j >> 1] = pack_bf16(e0, e1);
+                            }
+                            const uint32_t tile = (uint32_t)(c >> 6) * kTileBytes;
+                            const int sub = (c & 63) >> 3;
+#pragma unroll
+                            for (int i = 0; i < 4; ++i) {
+                                const uint32_t off = tile + sw128_off(row, sub + i);
+                                *reinterpret_cast<uint4*>(sPT + off) = make_uint4(pw[4 * i], pw[4 * i + 1], pw[4 * i + 2], pw[4 * i + 3]);
+                                *reinterpret_cast<uint4*>(sDS + off) = make_uint4(dw[4 * i], dw[4 * i + 1], dw[4 * i + 2], dw[4 * i + 3]);
+                            }
+                        }
+                        fence_proxy_async();
+                        tc_fence_before();
+                        mbar_arrive(pt_full);
+                    }
+                    // ---- dV / dK of this key tile: warps 0-3 write dV, warps 4-7 write dK
+                    mbar_wait(dvk_full, nkt & 1);
+                    tc_fence_after();
+                    {
+                        const uint32_t col = half == 0 ? kColDV : kColDK;
+                        __nv_bfloat16* dst = p.dqkv + (size_t)(b * p.T + key) * (3 * HHD) + (half == 0 ? 2 * HHD : HHD) + head * HD;
+                        if constexpr (HD == 64) {
+#pragma unroll
+                            for (int h2 = 0; h2 < 2; ++h2) {
+                                uint32_t r[32];
+                                tmem_ld_32x32(tlane + col + h2 * 32, r);
+                                tmem_ld_wait();
+                                if (key_ok) store_row32_bf16(dst + h2 * 32, r);
+                            }
+                        } else {
+                            uint32_t r[32];
+                            tmem_ld_32x32(tlane + col + hh * 32, r);
+                            tmem_ld_wait();
+                            if (key_ok) store_row32_bf16(dst, r);
+                        }
+                    }
+                    tc_fence_before();
+                    mbar_arrive(dvk_empty);
+                }
+                // ---- dQ of this head: warps 0-3 take query tile 0, warps 4-7 query tile 1
+                mbar_wait(dq_full, nhead & 1);
+                tc_fence_after();
+                if (half < p.NB) {
+                    const int q = half * 128 + row;
+                    __nv_bfloat16* dst = p.dqkv + (size_t)(b * p.T + q) * (3 * HHD) + head * HD;
+                    if constexpr (HD == 64) {
+#pragma unroll
+                        for (int h2 = 0; h2 < 2; ++h2) {
+                            uint32_t r[32];
+                            tmem_ld_32x32(tlane + kColDQ + half * 64 + h2 * 32, r);
+                            tmem_ld_wait();
+                            if (q < p.T) store_row32_bf16(dst + h2 * 32, r);
+                        }
+                    } else {
+                        uint32_t r[32];
+                        tmem_ld_32x32(tlane + kColDQ + half * 64 + hh * 32, r);
+                        tmem_ld_wait();
+                        if (q < p.T) store_row32_bf16(dst, r);
+                    }
+                }
+                tc_fence_before();
+                mbar_arrive(dq_empty);
+            }
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 9) {
+        tc_fence_after();
+        tmem_dealloc<512>(tmem_base);
+    }
+}
+
+// ---- host side ----------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn3)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                   const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn3 attn_encode_fn() {
+    static EncodeTiledFn3 fn = nullptr;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        void* f = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &qres) == cudaSuccess &&
+            qres == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeTiledFn3>(f);
+    });
+    return fn;
+}
+
+// bf16 [B, T, cols] (cols contiguous): box = 64 columns x 128 tokens x 1 image, SWIZZLE_128B, zero fill for t >= T.
+static int make_tmap_tokens(CUtensorMap* out, const void* ptr, long long cols, long long T, long long B) {
+    struct Key { const void* p; long long c, t, b; bool operator==(const Key& o) const { return p == o.p && c == o.c && t == o.t && b == o.b; } };
+    struct Hash { size_t operator()(const Key& k) const { return std::hash<const void*>()(k.p) ^ (size_t)(k.c * 1315423911ull) ^ (size_t)(k.t * 2654435761ull) ^ (size_t)(k.b << 9); } };
+    static thread_local std::unordered_map<Key, CUtensorMap, Hash> cache;
+    Key key{ptr, cols, T, B};
+    auto it = cache.find(key);
+    if (it != cache.end()) { *out = it->second; return SSL4P_OK; }
+    EncodeTiledFn3 enc = attn_encode_fn();
+    if (!enc) { set_error("cuTensorMapEncodeTiled entry point unavailable (no CUDA driver?)"); return SSL4P_ERR_CUDA; }
+    SSL4P_REQUIRE((reinterpret_cast<uintptr_t>(ptr) & 15) == 0, "attention: operand pointer must be 16-byte aligned");
+    SSL4P_REQUIRE(cols % 64 == 0, "attention: H*head_dim must be a multiple of 64 (got row of %lld columns)", cols);
+    cuuint64_t dims[3] = {(cuuint64_t)cols, (cuuint64_t)T, (cuuint64_t)B};
+    cuuint64_t strides[2] = {(cuuint64_t)cols * 2, (cuuint64_t)cols * 2 * (cuuint64_t)T};
+    cuuint32_t box[3] = {64u, 128u, 1u};
+    cuuint32_t estr[3] = {1u, 1u, 1u};
+    CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(ptr), dims, strides, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) { set_error("attention: cuTensorMapEncodeTiled failed (CUresult %d) cols=%lld T=%lld B=%lld", (int)r, cols, T, B); return SSL4P_ERR_CUDA; }
+    if (cache.size() > 1024) cache.clear();
+    cache.emplace(key, *out);
+    return SSL4P_OK;
+}
+
+constexpr int kFwdSmem = 14 * kTileBytes + 256 + 1024;
+constexpr int kBwdSmem = 12 * kTileBytes + 4096 + 256 + 1024;
+
+template <int HD>
+static int launch_fwd_tc(const void* qkv, void* out, float* lse, int B, int T, int H, float scale, cudaStream_t s) {
+    CUtensorMap tm;
+    int rc = make_tmap_tokens(&tm, qkv, 3LL * H * HD, T, B);
+    if (rc) return rc;
+    AttnFwdParams p;
+    p.T = T; p.H = H; p.slices_per_img = H * HD / 64; p.items = B * p.slices_per_img;
+    p.Npad = (T + 15) / 16 * 16; p.NB = (T + 127) / 128; p.NKB = (p.Npad + 127) / 128;
+    p.scale = scale; p.out = (__nv_bfloat16*)out; p.lse = lse;
+    auto kern = attention_fwd_tc_kernel<HD>;
+    static bool attr = false;
+    if (!attr) { SSL4P_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kFwdSmem)); attr = true; }
+    const int grid = p.items < num_sms() ? p.items : num_sms();
+    kern<<<grid, kAttnThreads, kFwdSmem, s>>>(tm, p);
+    return check_launch("attention_fwd_tc_kernel");
+}
+
+template <int HD>
+static int launch_bwd_tc(const void* qkv, const void* out, const void* dout, const float* lse, void* dqkv, int B, int T, int H,
+                         float scale, cudaStream_t s) {
+    CUtensorMap tmQ, tmD;
+    int rc = make_tmap_tokens(&tmQ, qkv, 3LL * H * HD, T, B);
+    if (rc) return rc;
+    rc = make_tmap_tokens(&tmD, dout, (long long)H * HD, T, B);
+    if (rc) return rc;
+    AttnBwdParams p;
+    p.T = T; p.H = H; p.slices_per_img = H * HD / 64; p.items = B * p.slices_per_img;
+    p.Npad = (T + 15) / 16 * 16; p.NB = (T + 127) / 128;
+    p.scale = scale; p.out = (const __nv_bfloat16*)out; p.dout = (const __nv_bfloat16*)dout; p.lse = lse; p.dqkv = (__nv_bfloat16*)dqkv;
+    auto kern = attention_bwd_tc_kernel<HD>;
+    static bool attr = false;
+    if (!attr) { SSL4P_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kBwdSmem)); attr = true; }
+    const int grid = p.items < num_sms() ? p.items : num_sms();
+    kern<<<grid, kAttnThreads, kBwdSmem, s>>>(tmQ, tmD, p);
+    return check_launch("attention_bwd_tc_kernel");
+}
+
+}  // namespace ssl4p
+
+using namespace ssl4p;
+
+static int attn_tc_check(int B, int T, int H, int hd) {
+    SSL4P_REQUIRE(B > 0 && H > 0 && T > 0, "attention: bad shape");
+    SSL4P_REQUIRE(hd == 32 || hd == 64, "attention: head_dim %d not supported (32 or 64)", hd);
+    SSL4P_REQUIRE((H * hd) % 64 == 0, "attention: H*head_dim (%d) must be a multiple of 64", H * hd);
+    SSL4P_REQUIRE(T <= 256, "attention: sequence length %d not supported (<= 256)", T);
+    return SSL4P_OK;
+}
+
+extern "C" int ssl4p_attention_fwd(const void* qkv, void* out, float* lse, int B, int T, int H, int hd, float scale, void* stream) {
+    SSL4P_REQUIRE(qkv && out && lse, "attention_fwd: null pointer");
+    int rc = attn_tc_check(B, T, H, hd);
+    if (rc) return rc;
+    cudaStream_t s = (cudaStream_t)stream;
+    if (hd == 64) return launch_fwd_tc<64>(qkv, out, lse, B, T, H, scale, s);
+    return launch_fwd_tc<32>(qkv, out, lse, B, T, H, scale, s);
+}
+
+extern "C" int ssl4p_attention_bwd(const void* qkv, const void* out, const void* dout, const float* lse, void* dqkv,
+                                   int B, int T, int H, int hd, float scale, void* stream) {
+    SSL4P_REQUIRE(qkv && out && dout && lse && dqkv, "attention_bwd: null pointer");
+    int rc = attn_tc_check(B, T, H, hd);
+    if (rc) return rc;
+    cudaStream_t s = (cudaStream_t)stream;
+    if (hd == 64) return launch_bwd_tc<64>(qkv, out, dout, lse, dqkv, B, T, H, scale, s);
+    return launch_bwd_tc<32>(qkv, out, dout, lse, dqkv, B, T, H, scale, s);
+}
