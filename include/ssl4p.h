@@ -38,10 +38,11 @@ unsigned long long ssl4p_launch_count(void);
 enum { SSL4P_GEMM_NT = 0, SSL4P_GEMM_NN = 1, SSL4P_GEMM_TN = 2 };
 enum {
     SSL4P_EPI_BIAS_BF16 = 0,         /* C(bf16)  = acc + bias (bias may be NULL)                          */
-    SSL4P_EPI_BIAS_GELU_BF16 = 1,    /* C(bf16)  = h = acc + bias ; C2(bf16) = gelu_erf(h)     (Mlp.fc1)  */
+    SSL4P_EPI_BIAS_GELU_BF16 = 1,    /* h = acc + bias ; C2(bf16) = gelu_erf(h) ; C(bf16) = gelu_erf'(h) (Mlp.fc1: the derivative
+                                        is what backward needs; both come from one erf evaluation)         */
     SSL4P_EPI_BIAS_RESIDUAL_F32 = 2, /* C(fp32)  = acc + bias + aux(fp32)     (attn.proj / Mlp.fc2 + skip) */
     SSL4P_EPI_BIAS_F32 = 3,          /* C(fp32)  = acc + bias                                             */
-    SSL4P_EPI_DGELU_BF16 = 4,        /* C(bf16)  = acc * gelu_erf'(aux(bf16))       (dgrad through GELU)  */
+    SSL4P_EPI_DGELU_BF16 = 4,        /* C(bf16)  = acc * aux(bf16), aux = the saved gelu_erf'(h)   (dgrad through GELU)  */
     SSL4P_EPI_PARTIAL_F32 = 5        /* C(fp32)[split] = acc  (split-K partial planes, M*ldc apart)       */
 };
 #define SSL4P_MAX_SPLITS 16

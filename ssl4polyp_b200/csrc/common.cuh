@@ -64,12 +64,22 @@ __device__ __forceinline__ float2 unpack_bf16(uint32_t u) {
     return __bfloat1622float2(v);
 }
 
-// exact-erf GELU (nn.GELU default) and its derivative
-__device__ __forceinline__ float gelu_f(float x) { return 0.5f * x * (1.0f + erff(x * 0.70710678118654752f)); }
-__device__ __forceinline__ float gelu_grad_f(float x) {
-    const float cdf = 0.5f * (1.0f + erff(x * 0.70710678118654752f));
-    const float pdf = 0.3989422804014327f * __expf(-0.5f * x * x);
-    return cdf + x * pdf;
+// GELU (exact-erf definition) and its derivative from ONE evaluation of erf via Abramowitz-Stegun 7.1.26
+// (|error| <= 1.5e-7, far below bf16 resolution): 2 MUFU (rcp, ex2) + ~16 FMA-pipe instructions per element, against
+// ~35 for erff + expf.  gelu(x) = x Phi(x);  gelu'(x) = Phi(x) + x phi(x),  phi(x) = exp(-x^2/2)/sqrt(2 pi).
+__device__ __forceinline__ void gelu_and_grad_f(float x, float& g, float& dg) {
+    const float z = fabsf(x) * 0.70710678118654752f;
+    float t, e;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t) : "f"(fmaf(0.3275911f, z, 1.0f)));
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(x * x * -0.72134752044448170f));      // exp(-x^2/2)
+    float poly = fmaf(t, 1.061405429f, -1.453152027f);
+    poly = fmaf(poly, t, 1.421413741f);
+    poly = fmaf(poly, t, -0.284496736f);
+    poly = fmaf(poly, t, 0.254829592f);
+    const float erf_abs = fmaf(-poly * t, e, 1.0f);                                           // erf(|x|/sqrt 2)
+    const float phi_cdf = fmaf(0.5f, copysignf(erf_abs, x), 0.5f);
+    g = x * phi_cdf;
+    dg = fmaf(x * e, 0.3989422804014327f, phi_cdf);
 }
 
 // ---- mbarrier -----------------------------------------------------------------------------------

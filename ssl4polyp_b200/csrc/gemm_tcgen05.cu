@@ -5,10 +5,13 @@
 // /root/reference/src/ssl4polyp/models/mae/models_mae.py:39-41,53-55,47,58 (SURVEY §2d K1,K9,K11-K14,K16) and
 // their autograd backward (dgrad = NN layout, wgrad = TN layout with deterministic split-K).
 //
-// Persistent kernel, one CTA per SM, 192 threads:
+// Persistent kernel, one CTA per SM, 320 threads:
 //   warp 0      : TMA producer (one elected lane)
 //   warp 1      : TMEM allocator + tcgen05.mma issuer (one elected lane)
-//   warps 2..5  : epilogue; warp w owns TMEM lanes 32*(w%4) .. 32*(w%4)+31  (= 32 rows of the 128-row tile)
+//   warps 2..9  : epilogue; warp w owns TMEM lanes 32*(w%4) .. 32*(w%4)+31  (= 32 rows of the 128-row tile); the two
+//                 warps that share a lane quarter take alternate 32-column chunks.  Eight warps (two per scheduler)
+//                 because at K = 512..768 the epilogue (bias/GELU/residual + stores) costs as much issue time as the
+//                 main loop: it has to run on all four schedulers with a second warp to hide tcgen05.ld/erf latency.
 // Pipelines: smem full/empty ring (kStages), TMEM full/empty (2 accumulators).
 #include "common.cuh"
 #include "ssl4p.h"
@@ -20,7 +23,8 @@ namespace ssl4p {
 constexpr int BM = 128;          // tile rows (UMMA M, cta_group::1)
 constexpr int BK = 64;           // K per stage: 64 bf16 = 128 B = one SWIZZLE_128B row
 constexpr int UMMA_K = 16;
-constexpr int kGemmThreads = 192;
+constexpr int kGemmThreads = 320;
+constexpr int kEpiWarps = 8;
 
 struct GemmParams {
     int M, N, K;                 // C[M,N] = sum_k A[m,k] B[n,k]
@@ -106,13 +110,32 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, int row, int
 #pragma unroll
                     for (int q = 0; q < 4; ++q) {
                         const float2 hf = unpack_bf16(hw[q]);
-                        v[j + 2 * q] *= gelu_grad_f(hf.x);
-                        v[j + 2 * q + 1] *= gelu_grad_f(hf.y);
+                        v[j + 2 * q] *= hf.x;
+                        v[j + 2 * q + 1] *= hf.y;
                     }
                 }
             } else {
 #pragma unroll
-                for (int j = 0; j < 32; ++j) if (j < ncols) v[j] *= gelu_grad_f(__bfloat162float(h[j]));
+                for (int j = 0; j < 32; ++j) if (j < ncols) v[j] *= __bfloat162float(h[j]);
+            }
+        }
+        if constexpr (EPI == SSL4P_EPI_BIAS_GELU_BF16) {
+            // C = gelu'(h) (what the backward multiplies by), C2 = gelu(h): one erf evaluation serves both
+            float g[32];
+#pragma unroll
+            for (int j = 0; j < 32; ++j) { float a, d; gelu_and_grad_f(v[j], a, d); g[j] = a; v[j] = d; }
+            __nv_bfloat16* out2 = reinterpret_cast<__nv_bfloat16*>(p.C2) + (size_t)row * p.ldc2 + col0;
+            if (ncols == 32) {
+#pragma unroll
+                for (int j = 0; j < 32; j += 8) {
+                    uint4 o;
+                    o.x = pack_bf16(g[j], g[j + 1]); o.y = pack_bf16(g[j + 2], g[j + 3]);
+                    o.z = pack_bf16(g[j + 4], g[j + 5]); o.w = pack_bf16(g[j + 6], g[j + 7]);
+                    *reinterpret_cast<uint4*>(out2 + j) = o;
+                }
+            } else {
+#pragma unroll
+                for (int j = 0; j < 32; ++j) if (j < ncols) out2[j] = __float2bfloat16(g[j]);
             }
         }
         __nv_bfloat16* out = reinterpret_cast<__nv_bfloat16*>(p.C) + off;
@@ -127,21 +150,6 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, int row, int
         } else {
 #pragma unroll
             for (int j = 0; j < 32; ++j) if (j < ncols) out[j] = __float2bfloat16(v[j]);
-        }
-        if constexpr (EPI == SSL4P_EPI_BIAS_GELU_BF16) {
-            __nv_bfloat16* out2 = reinterpret_cast<__nv_bfloat16*>(p.C2) + (size_t)row * p.ldc2 + col0;
-            if (ncols == 32) {
-#pragma unroll
-                for (int j = 0; j < 32; j += 8) {
-                    uint4 o;
-                    o.x = pack_bf16(gelu_f(v[j]), gelu_f(v[j + 1])); o.y = pack_bf16(gelu_f(v[j + 2]), gelu_f(v[j + 3]));
-                    o.z = pack_bf16(gelu_f(v[j + 4]), gelu_f(v[j + 5])); o.w = pack_bf16(gelu_f(v[j + 6]), gelu_f(v[j + 7]));
-                    *reinterpret_cast<uint4*>(out2 + j) = o;
-                }
-            } else {
-#pragma unroll
-                for (int j = 0; j < 32; ++j) if (j < ncols) out2[j] = __float2bfloat16(gelu_f(v[j]));
-            }
         }
     }
 }
@@ -179,7 +187,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     if (warp == 1) {
         if (lane_id() == 0) {
             for (int i = 0; i < kStages; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], 1); }
-            for (int i = 0; i < 2; ++i) { mbar_init(&tmem_full[i], 1); mbar_init(&tmem_empty[i], 4); }
+            for (int i = 0; i < 2; ++i) { mbar_init(&tmem_full[i], 1); mbar_init(&tmem_empty[i], kEpiWarps); }
             mbar_fence_init();
             fence_proxy_async();
         }
@@ -270,6 +278,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     } else {
         // ===================== epilogue warps =====================
         const int q = warp & 3;                                       // TMEM lane quarter this warp may access
+        const int chunk0 = ((warp - 2) >> 2) * 32;                    // the quarter's two warps interleave 32-column chunks
         int acc = 0; uint32_t acc_phase = 0;
         for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
             const int split = tile / tiles_mn;
@@ -280,7 +289,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             const int row = m0 + q * 32 + (int)lane_id();
             const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + acc * kAccStride;
 #pragma unroll 1
-            for (int c = 0; c < BN; c += 32) {
+            for (int c = chunk0; c < BN; c += 64) {
                 uint32_t r[32];
                 tmem_ld_32x32(taddr + c, r);
                 tmem_ld_wait();

@@ -144,9 +144,9 @@ def block_fwd(W: Weights, pre: str, x: torch.Tensor, B: int, T: int, H: int, eps
     o, lse = ops.attention_fwd(qkv, B, T, H, hd, hd ** -0.5)
     x1 = ops.gemm(o, W.b(pre + "attn.proj.weight"), GEMM_NT, EPI_BIAS_RESIDUAL_F32, bias=W.f(pre + "attn.proj.bias"), aux=x)
     h2, mean2, rstd2 = ops.layernorm_fwd(x1, W.f(pre + "norm2.weight"), W.f(pre + "norm2.bias"), eps)
-    pre_act, act = ops.gemm(h2, W.b(pre + "mlp.fc1.weight"), GEMM_NT, EPI_BIAS_GELU_BF16, bias=W.f(pre + "mlp.fc1.bias"))
+    dact, act = ops.gemm(h2, W.b(pre + "mlp.fc1.weight"), GEMM_NT, EPI_BIAS_GELU_BF16, bias=W.f(pre + "mlp.fc1.bias"))
     x2 = ops.gemm(act, W.b(pre + "mlp.fc2.weight"), GEMM_NT, EPI_BIAS_RESIDUAL_F32, bias=W.f(pre + "mlp.fc2.bias"), aux=x1)
-    saved = (x, mean1, rstd1, h, qkv, o, lse, x1, mean2, rstd2, h2, pre_act, act) if save else None
+    saved = (x, mean1, rstd1, h, qkv, o, lse, x1, mean2, rstd2, h2, dact, act) if save else None
     return x2, saved
 
 
@@ -154,12 +154,12 @@ def block_bwd(W: Weights, sink: GradSink, pre: str, saved, dx: torch.Tensor, dxb
               want_bf16: bool = True):
     """dx (fp32, updated in place) / dxb (its bf16 copy) = gradient w.r.t. the block output.
     Returns (dx, dxb) w.r.t. the block input."""
-    x, mean1, rstd1, h, qkv, o, lse, x1, mean2, rstd2, h2, pre_act, act = saved
+    x, mean1, rstd1, h, qkv, o, lse, x1, mean2, rstd2, h2, dact, act = saved
     D = x.shape[1]
     hd = D // H
     # ---- MLP branch
     _wgrad(W, sink, pre + "mlp.fc2.weight", pre + "mlp.fc2.bias", dxb, act)
-    dpre = ops.gemm(dxb, W.b(pre + "mlp.fc2.weight"), GEMM_NN, EPI_DGELU_BF16, aux=pre_act)
+    dpre = ops.gemm(dxb, W.b(pre + "mlp.fc2.weight"), GEMM_NN, EPI_DGELU_BF16, aux=dact)
     _wgrad(W, sink, pre + "mlp.fc1.weight", pre + "mlp.fc1.bias", dpre, h2)
     dh2 = ops.gemm(dpre, W.b(pre + "mlp.fc1.weight"), GEMM_NN, EPI_BIAS_BF16)
     dx, dxb = _ln_bwd(W, sink, pre + "norm2.", dh2, x1, mean2, rstd2, dx)

@@ -42,9 +42,12 @@ def test_gemm_nt_gelu_residual():
     w = (torch.randn(N, K, device=dev()) / math.sqrt(K)).bfloat16()
     bias = torch.randn(N, device=dev())
     h_ref = a.float() @ w.float().t() + bias
-    h, g = ops.gemm(a, w, ops.GEMM_NT, ops.EPI_BIAS_GELU_BF16, bias=bias)
-    assert rel_err(h, h_ref) < 1e-2
-    assert rel_err(g, F.gelu(h_ref)) < 1e-2
+    dg, g = ops.gemm(a, w, ops.GEMM_NT, ops.EPI_BIAS_GELU_BF16, bias=bias)
+    x = h_ref
+    dgelu = 0.5 * (1 + torch.erf(x / math.sqrt(2))) + x * torch.exp(-0.5 * x * x) / math.sqrt(2 * math.pi)
+    assert rel_err(g, F.gelu(h_ref)) < 4e-3                       # bf16 rounding only: the erf evaluation is 1.5e-7 accurate
+    assert rel_err(dg, dgelu) < 4e-3
+    assert (g.float() - F.gelu(h_ref)).abs().max().item() < 2e-2 and (dg.float() - dgelu).abs().max().item() < 1e-2
     res = torch.randn(M, N, device=dev())
     out = ops.gemm(a, w, ops.GEMM_NT, ops.EPI_BIAS_RESIDUAL_F32, bias=bias, aux=res)
     assert rel_err(out, h_ref + res) < 2e-3
@@ -59,11 +62,9 @@ def test_gemm_nn_dgrad(M, N, K, bn):
     ref = dy.float() @ w.float()
     out = ops.gemm(dy, w, ops.GEMM_NN, ops.EPI_BIAS_BF16, force_bn=bn)
     assert rel_err(out, ref) < 1e-2, rel_err(out, ref)
-    h = torch.randn(M, N, device=dev()).bfloat16()
-    out2 = ops.gemm(dy, w, ops.GEMM_NN, ops.EPI_DGELU_BF16, aux=h, force_bn=bn)
-    x = h.float()
-    dgelu = 0.5 * (1 + torch.erf(x / math.sqrt(2))) + x * torch.exp(-0.5 * x * x) / math.sqrt(2 * math.pi)
-    assert rel_err(out2, ref * dgelu) < 1e-2
+    dact = torch.randn(M, N, device=dev()).bfloat16()            # the saved gelu'(h) of the forward epilogue
+    out2 = ops.gemm(dy, w, ops.GEMM_NN, ops.EPI_DGELU_BF16, aux=dact, force_bn=bn)
+    assert rel_err(out2, ref * dact.float()) < 1e-2
 
 
 @pytest.mark.parametrize("M,N,K", [(128, 64, 64), (768, 768, 100), (2304, 768, 394), (512, 2048, 12800), (768, 3072, 1000)])
