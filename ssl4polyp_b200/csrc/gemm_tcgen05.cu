@@ -43,115 +43,122 @@ struct SmemLayout {
     static constexpr int kABytes = BM * BK * 2;
     static constexpr int kBBytes = BN * BK * 2;
     static constexpr int kStageBytes = kABytes + kBBytes;
-    static constexpr int kBudget = 200 * 1024;
+    static constexpr int kBudget = 192 * 1024;
     static constexpr int kStagesRaw = kBudget / kStageBytes;
     static constexpr int kStages = kStagesRaw > 8 ? 8 : kStagesRaw;
     static constexpr int kBarBytes = 1024;
-    static constexpr int kTotal = kStages * kStageBytes + kBarBytes + 1024 /*align slack*/;
+    static constexpr int kEpiBytes = kEpiWarps * 32 * 32 * 4;          // per-warp transpose patches of the epilogue
+    static constexpr int kTotal = kStages * kStageBytes + kBarBytes + kEpiBytes + 1024 /*align slack*/;
 };
 
-// ---- epilogue math ------------------------------------------------------------------------------
-// Each epilogue thread owns one output row and receives 32 consecutive fp32 accumulator columns.
-template <int EPI>
-__device__ __forceinline__ void epilogue_chunk(const GemmParams& p, int row, int col0, int ncols, int split, uint32_t (&acc)[32]) {
-    float v[32];
-#pragma unroll
-    for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(acc[j]);
+// ---- epilogue ------------------------------------------------------------------------------------
+// tcgen05.ld hands every thread ONE row x 32 columns.  Written to global memory like that, a warp-wide 16-byte access
+// touches 32 different 128-byte lines (one L1 tag cycle each), and at K = 512..768 those accesses cost more than the
+// main loop.  So each warp first transposes its 32x32 fp32 block through a private 4 KB shared-memory patch (XOR
+// swizzle, conflict free both ways) and then touches global memory in row-contiguous 512-byte warp accesses:
+// fp32 outputs 4 rows x 128 B per instruction, bf16 outputs 8 rows x 64 B.
+constexpr int kStageBytesPerWarp = 32 * 32 * 4;
 
-    if constexpr (EPI == SSL4P_EPI_BIAS_BF16 || EPI == SSL4P_EPI_BIAS_GELU_BF16 || EPI == SSL4P_EPI_BIAS_RESIDUAL_F32 ||
-                  EPI == SSL4P_EPI_BIAS_F32) {
-        if (p.bias != nullptr) {
-            if (ncols == 32) {
+__device__ __forceinline__ float4 f4_add(float4 a, float4 b) { return make_float4(a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w); }
+
+// The second epilogue operand of a chunk (fp32 residual: 8 x 16 B per lane; saved gelu': 4 x 16 B per lane), in the
+// transposed (row-contiguous) mapping.  Loaded one chunk ahead so that its HBM latency hides behind the previous chunk.
+struct AuxRegs { uint4 v[8]; };
+
+template <int EPI>
+__device__ __forceinline__ void load_aux(const GemmParams& p, int row_base, int col0, AuxRegs& a) {
+    const int lane = (int)lane_id();
+    if constexpr (EPI == SSL4P_EPI_BIAS_RESIDUAL_F32) {
+        const int col = col0 + (lane & 7) * 4;
 #pragma unroll
-                for (int j = 0; j < 32; j += 4) {
-                    const float4 b = __ldg(reinterpret_cast<const float4*>(p.bias + col0 + j));
-                    v[j] += b.x; v[j + 1] += b.y; v[j + 2] += b.z; v[j + 3] += b.w;
-                }
-            } else {
+        for (int i = 0; i < 8; ++i) {
+            const int row = row_base + 4 * i + (lane >> 3);
+            a.v[i] = (row < p.M && col < p.N) ? *reinterpret_cast<const uint4*>(reinterpret_cast<const float*>(p.aux) + (size_t)row * p.ldaux + col)
+                                              : make_uint4(0u, 0u, 0u, 0u);
+        }
+    } else if constexpr (EPI == SSL4P_EPI_DGELU_BF16) {
+        const int col = col0 + (lane & 3) * 8;
 #pragma unroll
-                for (int j = 0; j < 32; ++j) if (j < ncols) v[j] += __ldg(p.bias + col0 + j);
-            }
+        for (int i = 0; i < 4; ++i) {
+            const int row = row_base + 8 * i + (lane >> 2);
+            a.v[i] = (row < p.M && col < p.N) ? *reinterpret_cast<const uint4*>(reinterpret_cast<const __nv_bfloat16*>(p.aux) + (size_t)row * p.ldaux + col)
+                                              : make_uint4(0u, 0u, 0u, 0u);
         }
     }
+}
 
-    const size_t off = (size_t)row * p.ldc + col0;
-    if constexpr (EPI == SSL4P_EPI_BIAS_RESIDUAL_F32) {
-        const float* res = reinterpret_cast<const float*>(p.aux) + (size_t)row * p.ldaux + col0;
-        float* out = reinterpret_cast<float*>(p.C) + off;
-        if (ncols == 32) {
+template <int EPI>
+__device__ __forceinline__ void epilogue_chunk(const GemmParams& p, uint8_t* stg, int row_base, int col0, int split, uint32_t (&acc)[32],
+                                               const AuxRegs& aux) {
+    const int lane = (int)lane_id();
+    auto transpose_in = [&]() {                                    // called after the global loads of the chunk have been issued
 #pragma unroll
-            for (int j = 0; j < 32; j += 4) {
-                const float4 r = *reinterpret_cast<const float4*>(res + j);
-                float4 o; o.x = v[j] + r.x; o.y = v[j + 1] + r.y; o.z = v[j + 2] + r.z; o.w = v[j + 3] + r.w;
-                *reinterpret_cast<float4*>(out + j) = o;
-            }
-        } else {
+        for (int c = 0; c < 8; ++c)
+            *reinterpret_cast<uint4*>(stg + lane * 128 + ((c ^ (lane & 7)) << 4)) = make_uint4(acc[4 * c], acc[4 * c + 1], acc[4 * c + 2], acc[4 * c + 3]);
+        __syncwarp();
+    };
+
+    constexpr bool kHasBias = EPI == SSL4P_EPI_BIAS_BF16 || EPI == SSL4P_EPI_BIAS_GELU_BF16 || EPI == SSL4P_EPI_BIAS_RESIDUAL_F32 ||
+                              EPI == SSL4P_EPI_BIAS_F32;
+    constexpr bool kOutF32 = EPI == SSL4P_EPI_BIAS_RESIDUAL_F32 || EPI == SSL4P_EPI_BIAS_F32 || EPI == SSL4P_EPI_PARTIAL_F32;
+
+    if constexpr (kOutF32) {
+        const int cc = lane & 7;                                   // 16-byte chunk = 4 columns
+        const int col = col0 + cc * 4;
+        const bool col_ok = col < p.N;                             // N % 8 == 0 (checked on the host)
+        float4 b = make_float4(0.f, 0.f, 0.f, 0.f);
+        if constexpr (kHasBias) if (p.bias != nullptr && col_ok) b = __ldg(reinterpret_cast<const float4*>(p.bias + col));
+        float* outp = reinterpret_cast<float*>(p.C) + (EPI == SSL4P_EPI_PARTIAL_F32 ? (size_t)split * p.split_stride : 0);
+        transpose_in();
 #pragma unroll
-            for (int j = 0; j < 32; ++j) if (j < ncols) out[j] = v[j] + res[j];
-        }
-    } else if constexpr (EPI == SSL4P_EPI_BIAS_F32 || EPI == SSL4P_EPI_PARTIAL_F32) {
-        float* out = reinterpret_cast<float*>(p.C) + off + (EPI == SSL4P_EPI_PARTIAL_F32 ? (size_t)split * p.split_stride : 0);
-        if (ncols == 32) {
-#pragma unroll
-            for (int j = 0; j < 32; j += 4) *reinterpret_cast<float4*>(out + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
-        } else {
-#pragma unroll
-            for (int j = 0; j < 32; ++j) if (j < ncols) out[j] = v[j];
+        for (int i = 0; i < 8; ++i) {
+            const int rr = 4 * i + (lane >> 3);
+            const int row = row_base + rr;
+            float4 v = *reinterpret_cast<const float4*>(stg + rr * 128 + ((cc ^ (rr & 7)) << 4));
+            v = f4_add(v, b);
+            if constexpr (EPI == SSL4P_EPI_BIAS_RESIDUAL_F32)
+                v = f4_add(v, make_float4(__uint_as_float(aux.v[i].x), __uint_as_float(aux.v[i].y), __uint_as_float(aux.v[i].z), __uint_as_float(aux.v[i].w)));
+            if (row < p.M && col_ok) *reinterpret_cast<float4*>(outp + (size_t)row * p.ldc + col) = v;
         }
     } else {
-        // bf16 outputs
-        if constexpr (EPI == SSL4P_EPI_DGELU_BF16) {
-            const __nv_bfloat16* h = reinterpret_cast<const __nv_bfloat16*>(p.aux) + (size_t)row * p.ldaux + col0;
-            if (ncols == 32) {
-#pragma unroll
-                for (int j = 0; j < 32; j += 8) {
-                    const uint4 hv = *reinterpret_cast<const uint4*>(h + j);
-                    const uint32_t hw[4] = {hv.x, hv.y, hv.z, hv.w};
-#pragma unroll
-                    for (int q = 0; q < 4; ++q) {
-                        const float2 hf = unpack_bf16(hw[q]);
-                        v[j + 2 * q] *= hf.x;
-                        v[j + 2 * q + 1] *= hf.y;
-                    }
-                }
-            } else {
-#pragma unroll
-                for (int j = 0; j < 32; ++j) if (j < ncols) v[j] *= __bfloat162float(h[j]);
-            }
+        const int cc = lane & 3;                                   // 16-byte bf16 chunk = 8 columns
+        const int col = col0 + cc * 8;
+        const bool col_ok = col < p.N;
+        float4 b0 = make_float4(0.f, 0.f, 0.f, 0.f), b1 = b0;
+        if constexpr (kHasBias) if (p.bias != nullptr && col_ok) {
+            b0 = __ldg(reinterpret_cast<const float4*>(p.bias + col));
+            b1 = __ldg(reinterpret_cast<const float4*>(p.bias + col + 4));
         }
-        if constexpr (EPI == SSL4P_EPI_BIAS_GELU_BF16) {
-            // C = gelu'(h) (what the backward multiplies by), C2 = gelu(h): one erf evaluation serves both
-            float g[32];
+        transpose_in();
 #pragma unroll
-            for (int j = 0; j < 32; ++j) { float a, d; gelu_and_grad_f(v[j], a, d); g[j] = a; v[j] = d; }
-            __nv_bfloat16* out2 = reinterpret_cast<__nv_bfloat16*>(p.C2) + (size_t)row * p.ldc2 + col0;
-            if (ncols == 32) {
+        for (int i = 0; i < 4; ++i) {
+            const int rr = 8 * i + (lane >> 2);
+            const int row = row_base + rr;
+            const float4 lo = *reinterpret_cast<const float4*>(stg + rr * 128 + (((2 * cc) ^ (rr & 7)) << 4));
+            const float4 hi = *reinterpret_cast<const float4*>(stg + rr * 128 + (((2 * cc + 1) ^ (rr & 7)) << 4));
+            if (row < p.M && col_ok) {
+                float v[8] = {lo.x + b0.x, lo.y + b0.y, lo.z + b0.z, lo.w + b0.w, hi.x + b1.x, hi.y + b1.y, hi.z + b1.z, hi.w + b1.w};
+                if constexpr (EPI == SSL4P_EPI_DGELU_BF16) {
+                    const uint32_t hw[4] = {aux.v[i].x, aux.v[i].y, aux.v[i].z, aux.v[i].w};
 #pragma unroll
-                for (int j = 0; j < 32; j += 8) {
-                    uint4 o;
-                    o.x = pack_bf16(g[j], g[j + 1]); o.y = pack_bf16(g[j + 2], g[j + 3]);
-                    o.z = pack_bf16(g[j + 4], g[j + 5]); o.w = pack_bf16(g[j + 6], g[j + 7]);
-                    *reinterpret_cast<uint4*>(out2 + j) = o;
+                    for (int q = 0; q < 4; ++q) { const float2 hf = unpack_bf16(hw[q]); v[2 * q] *= hf.x; v[2 * q + 1] *= hf.y; }
                 }
-            } else {
+                if constexpr (EPI == SSL4P_EPI_BIAS_GELU_BF16) {
+                    // C = gelu'(h) (what the backward multiplies by), C2 = gelu(h): one erf evaluation serves both
+                    float g[8];
 #pragma unroll
-                for (int j = 0; j < 32; ++j) if (j < ncols) out2[j] = __float2bfloat16(g[j]);
-            }
-        }
-        __nv_bfloat16* out = reinterpret_cast<__nv_bfloat16*>(p.C) + off;
-        if (ncols == 32) {
-#pragma unroll
-            for (int j = 0; j < 32; j += 8) {
+                    for (int j = 0; j < 8; ++j) { float a, d; gelu_and_grad_f(v[j], a, d); g[j] = a; v[j] = d; }
+                    uint4 o2;
+                    o2.x = pack_bf16(g[0], g[1]); o2.y = pack_bf16(g[2], g[3]); o2.z = pack_bf16(g[4], g[5]); o2.w = pack_bf16(g[6], g[7]);
+                    *reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(p.C2) + (size_t)row * p.ldc2 + col) = o2;
+                }
                 uint4 o;
-                o.x = pack_bf16(v[j], v[j + 1]); o.y = pack_bf16(v[j + 2], v[j + 3]);
-                o.z = pack_bf16(v[j + 4], v[j + 5]); o.w = pack_bf16(v[j + 6], v[j + 7]);
-                *reinterpret_cast<uint4*>(out + j) = o;
+                o.x = pack_bf16(v[0], v[1]); o.y = pack_bf16(v[2], v[3]); o.z = pack_bf16(v[4], v[5]); o.w = pack_bf16(v[6], v[7]);
+                *reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(p.C) + (size_t)row * p.ldc + col) = o;
             }
-        } else {
-#pragma unroll
-            for (int j = 0; j < 32; ++j) if (j < ncols) out[j] = __float2bfloat16(v[j]);
         }
     }
+    __syncwarp();                                                  // the patch is rewritten by the next chunk
 }
 
 // ---- the kernel ---------------------------------------------------------------------------------
@@ -173,6 +180,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     uint64_t* tmem_full = bars + 2 * kStages;                // [2]
     uint64_t* tmem_empty = bars + 2 * kStages + 2;           // [2]
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * kStages + 4);
+    uint8_t* epi_stage = smem + kStages * L::kStageBytes + L::kBarBytes;   // kEpiWarps x 4 KB
 
     const int warp = threadIdx.x >> 5;
     const int mt = (p.M + BM - 1) / BM;
@@ -284,22 +292,29 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             const int split = tile / tiles_mn;
             const int t = tile - split * tiles_mn;
             const int m0 = (t / nt) * BM, n0 = (t % nt) * BN;
+            const int row_base = m0 + q * 32;
+            constexpr bool kAux = EPI == SSL4P_EPI_BIAS_RESIDUAL_F32 || EPI == SSL4P_EPI_DGELU_BF16;
+            AuxRegs aux_cur, aux_nxt;
+            if constexpr (kAux) load_aux<EPI>(p, row_base, n0 + chunk0, aux_cur);      // in flight while the MMAs of the tile finish
             mbar_wait(&tmem_full[acc], acc_phase);
             tc_fence_after();
-            const int row = m0 + q * 32 + (int)lane_id();
+            uint8_t* stg = epi_stage + (warp - 2) * kStageBytesPerWarp;
             const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + acc * kAccStride;
+            const bool empty_split = split * p.k_per_split >= p.K;   // empty split-K range: the accumulator was never written
 #pragma unroll 1
             for (int c = chunk0; c < BN; c += 64) {
+                const int col0 = n0 + c;
+                if (col0 >= p.N) break;
+                if constexpr (kAux) if (c + 64 < BN) load_aux<EPI>(p, row_base, col0 + 64, aux_nxt);
                 uint32_t r[32];
                 tmem_ld_32x32(taddr + c, r);
                 tmem_ld_wait();
-                if (split * p.k_per_split >= p.K) {              // empty split-K range: the accumulator was never written
+                if (empty_split) {
 #pragma unroll
                     for (int j = 0; j < 32; ++j) r[j] = 0u;
                 }
-                const int col0 = n0 + c;
-                const int ncols = min(32, p.N - col0);
-                if (row < p.M && ncols > 0) epilogue_chunk<EPI>(p, row, col0, ncols, split, r);
+                if (row_base < p.M) epilogue_chunk<EPI>(p, stg, row_base, col0, split, r, aux_cur);
+                if constexpr (kAux) aux_cur = aux_nxt;
             }
             tc_fence_before();
             __syncwarp();
@@ -457,6 +472,7 @@ extern "C" int ssl4p_gemm_bf16(const void* A, const void* B, void* C, void* C2, 
     if (epilogue == SSL4P_EPI_BIAS_RESIDUAL_F32 || epilogue == SSL4P_EPI_DGELU_BF16) SSL4P_REQUIRE(aux != nullptr, "gemm: epilogue needs aux");
     // vectorised epilogue accesses
     SSL4P_REQUIRE(ldc % 8 == 0 && (reinterpret_cast<uintptr_t>(C) & 15) == 0, "gemm: C must be 16B aligned with ldc %% 8 == 0");
+    SSL4P_REQUIRE(N % 8 == 0, "gemm: N must be a multiple of 8 (vectorised epilogue), got %d", N);
     if (C2) SSL4P_REQUIRE(ldc2 % 8 == 0 && (reinterpret_cast<uintptr_t>(C2) & 15) == 0, "gemm: C2 alignment");
     if (aux) SSL4P_REQUIRE(ldaux % 8 == 0 && (reinterpret_cast<uintptr_t>(aux) & 15) == 0, "gemm: aux alignment");
     if (bias) SSL4P_REQUIRE((reinterpret_cast<uintptr_t>(bias) & 15) == 0, "gemm: bias alignment");
