@@ -315,7 +315,14 @@ def b200_arm(args):
         }
         print(json.dumps(line), flush=True)
     if world > 1:
-        dist.destroy_process_group()
+        # Tear down without ProcessGroupNCCL's destructor: with NCCL collectives captured in a live CUDA graph,
+        # destroy_process_group() was observed to hang after the result line had been printed (N=2, B200).
+        torch.cuda.synchronize()
+        dist.barrier()
+        torch.cuda.synchronize()
+        sys.stdout.flush()
+        sys.stderr.flush()
+        os._exit(0)
 
 
 def main():
