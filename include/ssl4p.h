@@ -84,10 +84,13 @@ int ssl4p_assemble_tokens_bwd(const float* dx, void* dtok_bf16, float* dcls, int
 int ssl4p_layernorm_fwd(const float* x, const float* gamma, const float* beta, float eps,
                         void* y_bf16, float* mean, float* rstd, int M, int D, void* stream);
 /* dx_out(fp32) = (residual_grad ? residual_grad : 0) + LN'(dy);  dxb(bf16) = bf16(dx_out) if non-NULL;
- * dgamma/dbeta (+)= column sums (two-stage, deterministic; workspace >= ssl4p_layernorm_bwd_workspace_bytes) */
+ * dgamma/dbeta (+)= column sums (two-stage, deterministic; workspace >= ssl4p_layernorm_bwd_workspace_bytes);
+ * dx_colsum (optional, [D]) (+)= column sums of dx_out = the bias gradient of the Linear whose output (plus skip) this
+ * LayerNorm consumed (attn.proj / mlp.fc2 of the timm Block), produced in the same pass. */
 int ssl4p_layernorm_bwd(const void* dy_bf16, const float* x, const float* mean, const float* rstd, const float* gamma,
                         const float* residual_grad, float* dx_out, void* dxb_bf16, float* dgamma, float* dbeta,
-                        int M, int D, int accumulate, void* workspace, size_t workspace_bytes, void* stream);
+                        float* dx_colsum, int M, int D, int accumulate, int accumulate_colsum,
+                        void* workspace, size_t workspace_bytes, void* stream);
 size_t ssl4p_layernorm_bwd_workspace_bytes(int M, int D);
 
 /* Multi-head self-attention of timm 0.4.12 Attention.forward (softmax(q k^T * scale) v), fused, per (batch, head).

@@ -75,15 +75,15 @@ __global__ void __launch_bounds__(kLnWarps * 32)
 layernorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const float* __restrict__ x, const float* __restrict__ mean_in,
                      const float* __restrict__ rstd_in, const float* __restrict__ gamma, const float* __restrict__ res_grad,
                      float* __restrict__ dx_out, __nv_bfloat16* __restrict__ dxb, float* __restrict__ part, int M, int D) {
-    extern __shared__ float s_red[];                           // [kLnWarps][2*D]
+    extern __shared__ float s_red[];                           // [kLnWarps][3*D]
     const int lane = lane_id();
     const int warp = threadIdx.x >> 5;
     const float inv_d = 1.0f / (float)D;
     const float4* g4 = reinterpret_cast<const float4*>(gamma);
     static_assert(NV > 0, "register-resident variant only");
-    float4 dg[NV], db[NV], gam[NV];
+    float4 dg[NV], db[NV], ds[NV], gam[NV];                    // ds = column sums of the dx written below (bias gradients upstream)
 #pragma unroll
-    for (int i = 0; i < NV; ++i) { dg[i] = make_float4(0, 0, 0, 0); db[i] = make_float4(0, 0, 0, 0); gam[i] = g4[lane + 32 * i]; }
+    for (int i = 0; i < NV; ++i) { dg[i] = make_float4(0, 0, 0, 0); db[i] = make_float4(0, 0, 0, 0); ds[i] = make_float4(0, 0, 0, 0); gam[i] = g4[lane + 32 * i]; }
 
     for (int row = blockIdx.x * kLnWarps + warp; row < M; row += gridDim.x * kLnWarps) {
         const float4* xr = reinterpret_cast<const float4*>(x + (size_t)row * D);
@@ -115,19 +115,20 @@ layernorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const float* __restri
             o.z = rstd * (gy[i].z - c1 - xh[i].z * c2); o.w = rstd * (gy[i].w - c1 - xh[i].w * c2);
             if (rr) { const float4 r = rr[lane + 32 * i]; o.x += r.x; o.y += r.y; o.z += r.z; o.w += r.w; }
             dxr[lane + 32 * i] = o;
+            ds[i].x += o.x; ds[i].y += o.y; ds[i].z += o.z; ds[i].w += o.w;
             if (dbr) { uint2 b; b.x = pack_bf16(o.x, o.y); b.y = pack_bf16(o.z, o.w); dbr[lane + 32 * i] = b; }
         }
     }
     // block reduce of the per-warp partial sums (fixed order), then one partial row per block
-    float4* sw = reinterpret_cast<float4*>(s_red + (size_t)warp * 2 * D);
+    float4* sw = reinterpret_cast<float4*>(s_red + (size_t)warp * 3 * D);
 #pragma unroll
-    for (int i = 0; i < NV; ++i) { sw[lane + 32 * i] = dg[i]; sw[D / 4 + lane + 32 * i] = db[i]; }
+    for (int i = 0; i < NV; ++i) { sw[lane + 32 * i] = dg[i]; sw[D / 4 + lane + 32 * i] = db[i]; sw[D / 2 + lane + 32 * i] = ds[i]; }
     __syncthreads();
-    for (int j = threadIdx.x; j < 2 * D; j += blockDim.x) {
+    for (int j = threadIdx.x; j < 3 * D; j += blockDim.x) {
         float acc = 0.f;
 #pragma unroll
-        for (int w = 0; w < kLnWarps; ++w) acc += s_red[(size_t)w * 2 * D + j];
-        part[(size_t)blockIdx.x * 2 * D + j] = acc;
+        for (int w = 0; w < kLnWarps; ++w) acc += s_red[(size_t)w * 3 * D + j];
+        part[(size_t)blockIdx.x * 3 * D + j] = acc;
     }
 }
 
@@ -137,12 +138,12 @@ __global__ void __launch_bounds__(kLnWarps * 32)
 layernorm_bwd_generic_kernel(const __nv_bfloat16* __restrict__ dy, const float* __restrict__ x, const float* __restrict__ mean_in,
                              const float* __restrict__ rstd_in, const float* __restrict__ gamma, const float* __restrict__ res_grad,
                              float* __restrict__ dx_out, __nv_bfloat16* __restrict__ dxb, float* __restrict__ part, int M, int D) {
-    extern __shared__ float s_red[];                           // [kLnWarps][2*D]
+    extern __shared__ float s_red[];                           // [kLnWarps][3*D]
     const int lane = lane_id();
     const int warp = threadIdx.x >> 5;
     const float inv_d = 1.0f / (float)D;
-    float* my = s_red + (size_t)warp * 2 * D;
-    for (int j = lane; j < 2 * D; j += 32) my[j] = 0.f;
+    float* my = s_red + (size_t)warp * 3 * D;
+    for (int j = lane; j < 3 * D; j += 32) my[j] = 0.f;
     __syncwarp();
     for (int row = blockIdx.x * kLnWarps + warp; row < M; row += gridDim.x * kLnWarps) {
         const float* xr = x + (size_t)row * D;
@@ -161,26 +162,40 @@ layernorm_bwd_generic_kernel(const __nv_bfloat16* __restrict__ dy, const float* 
             float o = rstd * (gy - c1 - xh * c2);
             if (res_grad) o += res_grad[(size_t)row * D + j];
             dx_out[(size_t)row * D + j] = o;
+            my[2 * D + j] += o;
             if (dxb) dxb[(size_t)row * D + j] = __float2bfloat16(o);
         }
     }
     __syncthreads();
-    for (int j = threadIdx.x; j < 2 * D; j += blockDim.x) {
+    for (int j = threadIdx.x; j < 3 * D; j += blockDim.x) {
         float acc = 0.f;
-        for (int w = 0; w < kLnWarps; ++w) acc += s_red[(size_t)w * 2 * D + j];
-        part[(size_t)blockIdx.x * 2 * D + j] = acc;
+        for (int w = 0; w < kLnWarps; ++w) acc += s_red[(size_t)w * 3 * D + j];
+        part[(size_t)blockIdx.x * 3 * D + j] = acc;
     }
 }
 
-// out[j] (+)= sum_g part[g][j]  over [G][2D] -> dgamma (j < D) and dbeta (j >= D)
-__global__ void ln_param_grad_reduce_kernel(const float* __restrict__ part, int G, int D, float* __restrict__ dgamma,
-                                            float* __restrict__ dbeta, int accumulate) {
-    const int j = blockIdx.x * blockDim.x + threadIdx.x;
-    if (j >= 2 * D) return;
-    float* dst = j < D ? dgamma + j : dbeta + (j - D);
-    float acc = accumulate ? *dst : 0.f;
-    for (int g = 0; g < G; ++g) acc += part[(size_t)g * 2 * D + j];
-    *dst = acc;
+// out[j] (+)= sum_g part[g][j]  over [G][3D] -> dgamma (j < D), dbeta (D <= j < 2D), column sums of dx (j >= 2D, optional).
+// 32 columns per block, 8 row groups summed in parallel and combined in fixed order (deterministic).
+__global__ void __launch_bounds__(256)
+ln_param_grad_reduce_kernel(const float* __restrict__ part, int G, int D, float* __restrict__ dgamma,
+                            float* __restrict__ dbeta, float* __restrict__ dxsum, int accumulate, int accumulate_dxsum) {
+    __shared__ float sh[8][33];
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    const int j = blockIdx.x * 32 + tx;
+    const int W = 3 * D;
+    float acc = 0.f;
+    if (j < W)
+        for (int g = ty; g < G; g += 8) acc += part[(size_t)g * W + j];
+    sh[ty][tx] = acc;
+    __syncthreads();
+    if (ty == 0 && j < W) {
+        float t = 0.f;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) t += sh[k][tx];
+        if (j < D) dgamma[j] = (accumulate ? dgamma[j] : 0.f) + t;
+        else if (j < 2 * D) dbeta[j - D] = (accumulate ? dbeta[j - D] : 0.f) + t;
+        else if (dxsum != nullptr) dxsum[j - 2 * D] = (accumulate_dxsum ? dxsum[j - 2 * D] : 0.f) + t;
+    }
 }
 
 static int ln_bwd_grid(int M) {
@@ -212,18 +227,19 @@ extern "C" int ssl4p_layernorm_fwd(const float* x, const float* gamma, const flo
 
 extern "C" size_t ssl4p_layernorm_bwd_workspace_bytes(int M, int D) {
     (void)M;
-    return (size_t)2 * 148 * 2 * 2 * (size_t)D * sizeof(float);     // up to 592 partial rows of [2*D]
+    return (size_t)2 * 148 * 2 * 3 * (size_t)D * sizeof(float);     // up to 592 partial rows of [3*D]
 }
 
 extern "C" int ssl4p_layernorm_bwd(const void* dy, const float* x, const float* mean, const float* rstd, const float* gamma,
                                    const float* residual_grad, float* dx_out, void* dxb, float* dgamma, float* dbeta,
-                                   int M, int D, int accumulate, void* workspace, size_t workspace_bytes, void* stream) {
+                                   float* dx_colsum, int M, int D, int accumulate, int accumulate_colsum,
+                                   void* workspace, size_t workspace_bytes, void* stream) {
     SSL4P_REQUIRE(dy && x && mean && rstd && gamma && dx_out && dgamma && dbeta, "layernorm_bwd: null pointer");
     SSL4P_REQUIRE(M > 0 && D > 0 && D % 4 == 0, "layernorm_bwd: bad shape");
     const int grid = ln_bwd_grid(M);
-    SSL4P_REQUIRE(workspace && workspace_bytes >= (size_t)grid * 2 * D * sizeof(float), "layernorm_bwd: workspace too small");
+    SSL4P_REQUIRE(workspace && workspace_bytes >= (size_t)grid * 3 * D * sizeof(float), "layernorm_bwd: workspace too small");
     const int threads = kLnWarps * 32;
-    const size_t smem = (size_t)kLnWarps * 2 * D * sizeof(float);
+    const size_t smem = (size_t)kLnWarps * 3 * D * sizeof(float);
     float* part = (float*)workspace;
     const __nv_bfloat16* dyb = (const __nv_bfloat16*)dy;
     __nv_bfloat16* dxbb = (__nv_bfloat16*)dxb;
@@ -238,13 +254,13 @@ extern "C" int ssl4p_layernorm_bwd(const void* dy, const float* x, const float* 
         case 768: LN_BWD(6) break;
         case 1024: LN_BWD(8) break;
         default: {
-            SSL4P_REQUIRE(smem <= 48 * 1024, "layernorm_bwd: generic path supports D <= 768");
+            SSL4P_REQUIRE(smem <= 48 * 1024, "layernorm_bwd: generic path supports D <= 512");
             layernorm_bwd_generic_kernel<<<grid, threads, smem, STREAM>>>(dyb, x, mean, rstd, gamma, residual_grad, dx_out, dxbb, part, M, D);
         }
     }
 #undef LN_BWD
     int rc = check_launch("layernorm_bwd_kernel");
     if (rc) return rc;
-    ln_param_grad_reduce_kernel<<<(2 * D + 127) / 128, 128, 0, STREAM>>>(part, grid, D, dgamma, dbeta, accumulate);
+    ln_param_grad_reduce_kernel<<<(3 * D + 31) / 32, 256, 0, STREAM>>>(part, grid, D, dgamma, dbeta, dx_colsum, accumulate, accumulate_colsum);
     return check_launch("ln_param_grad_reduce_kernel");
 }

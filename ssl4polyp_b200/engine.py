@@ -130,11 +130,11 @@ class TrainEngine:
         if self._graph is None:
             if self._graph_warm < 2:                          # lazy attribute / NCCL / workspace initialisation happens
                 self._graph_warm += 1                         # in ordinary eager steps on the caller's own batches
-                return eager_step(*static)
+                return eager_step(*static, lr=lr)
             torch.cuda.synchronize()
             g = torch.cuda.CUDAGraph()
             with torch.cuda.graph(g):
-                self._static_out = eager_step(*static)
+                self._static_out = eager_step(*static, lr=lr)   # lr is read from self.hyper on the device when replayed
             self._graph = g
         self._graph.replay()
         self.t += 1
@@ -187,8 +187,8 @@ class PretrainEngine(TrainEngine):
             if accum_iter != 1:
                 raise RuntimeError("graph replay does not accumulate gradients")
             if noise is not None:                             # caller-supplied noise becomes a second static input
-                return self._replay(lambda x, z: self.step(x, noise=z), [imgs, noise], lr)
-            return self._replay(lambda x: self.step(x), [imgs], lr)
+                return self._replay(lambda x, z, lr: self.step(x, lr=lr, noise=z), [imgs, noise], lr)
+            return self._replay(lambda x, lr: self.step(x, lr=lr), [imgs], lr)
         m = self.model
         if noise is None:
             noise = torch.rand(imgs.shape[0], m.patch_embed.num_patches, device=imgs.device)   # models_mae.py:132
@@ -211,7 +211,7 @@ class ClassifierEngine(TrainEngine):
 
     def step(self, imgs, target, lr=None, graph: bool = False):
         if graph:
-            return self._replay(lambda x, y: self.step(x, y), [imgs, target], lr)
+            return self._replay(lambda x, y, lr: self.step(x, y, lr=lr), [imgs, target], lr)
         m = self.model
         logits, sv = vit_core.classifier_fwd(self.store, m._dims, imgs, m.out_token == "spatial", True)
         lg = logits.detach().requires_grad_(True)

@@ -257,8 +257,10 @@ def layernorm_fwd(x, gamma, beta, eps):
     return y, mean, rstd
 
 
-def layernorm_bwd(dy, x, mean, rstd, gamma, residual_grad, dgamma, dbeta, *, want_bf16=True, accumulate=False, dx_out=None):
-    """-> (dx fp32 [M,D], dxb bf16 [M,D] | None).  dx = residual_grad + LN'(dy); may alias residual_grad (in place)."""
+def layernorm_bwd(dy, x, mean, rstd, gamma, residual_grad, dgamma, dbeta, *, want_bf16=True, accumulate=False, dx_out=None,
+                  dx_colsum=None, accumulate_colsum=False):
+    """-> (dx fp32 [M,D], dxb bf16 [M,D] | None).  dx = residual_grad + LN'(dy); may alias residual_grad (in place).
+    dx_colsum (fp32 [D], optional) (+)= column sums of dx (the upstream Linear's bias gradient)."""
     lib = _lib.load()
     _req(dy, bf16, "ln dy")
     M, D = dy.shape
@@ -268,8 +270,8 @@ def layernorm_bwd(dy, x, mean, rstd, gamma, residual_grad, dgamma, dbeta, *, wan
     nb = lib.ssl4p_layernorm_bwd_workspace_bytes(M, D)
     ws = workspace(nb, dy.device, "ln")
     _lib.check(lib.ssl4p_layernorm_bwd(dy.data_ptr(), x.data_ptr(), mean.data_ptr(), rstd.data_ptr(), gamma.data_ptr(), _ptr(residual_grad),
-                                       dx_out.data_ptr(), _ptr(dxb), dgamma.data_ptr(), dbeta.data_ptr(), M, D, int(accumulate),
-                                       ws.data_ptr(), ws.numel(), _stream()), "layernorm_bwd")
+                                       dx_out.data_ptr(), _ptr(dxb), dgamma.data_ptr(), dbeta.data_ptr(), _ptr(dx_colsum), M, D, int(accumulate),
+                                       int(accumulate_colsum), ws.data_ptr(), ws.numel(), _stream()), "layernorm_bwd")
     return dx_out, dxb
 
 

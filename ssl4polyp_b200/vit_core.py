@@ -96,7 +96,8 @@ def _block_needs(W: Weights, pre: str) -> bool:
 # linear layer backward helpers
 # ----------------------------------------------------------------------------------------------------------
 def _wgrad(W: Weights, sink: GradSink, wname: str, bname: str | None, dy: torch.Tensor, x: torch.Tensor):
-    """dW[out,in] = dy^T x (TN GEMM, deterministic split-K), db = column sums of dy."""
+    """dW[out,in] = dy^T x (TN GEMM, deterministic split-K), db = column sums of dy (bname None: the bias gradient
+    was already produced by the LayerNorm backward that wrote dy, see _ln_bwd)."""
     if W.need(wname):
         w = W.f(wname)
         buf, acc = sink.buf(wname, w)
@@ -114,8 +115,10 @@ def _wgrad(W: Weights, sink: GradSink, wname: str, bname: str | None, dy: torch.
         sink.ready(bname)
 
 
-def _ln_bwd(W: Weights, sink: GradSink, pre: str, dy, x, mean, rstd, residual_grad, want_bf16=True):
-    """LayerNorm backward; gamma/beta gradients go to the sink (or to a scratch pair when frozen)."""
+def _ln_bwd(W: Weights, sink: GradSink, pre: str, dy, x, mean, rstd, residual_grad, want_bf16=True, upstream_bias=None):
+    """LayerNorm backward; gamma/beta gradients go to the sink (or to a scratch pair when frozen).
+    upstream_bias: name of the Linear bias whose output (+ skip) this norm read; its gradient is the column sum of
+    the dx produced here and comes out of the same kernel (no separate pass over dx)."""
     gname, bname = pre + "weight", pre + "bias"
     gamma = W.f(gname)
     if W.need(gname) or W.need(bname):
@@ -127,9 +130,15 @@ def _ln_bwd(W: Weights, sink: GradSink, pre: str, dy, x, mean, rstd, residual_gr
         dg = torch.empty_like(gamma, dtype=torch.float32)
         db = torch.empty_like(gamma, dtype=torch.float32)
         acc = False
-    out = ops.layernorm_bwd(dy, x, mean, rstd, gamma, residual_grad, dg, db, want_bf16=want_bf16, accumulate=acc)
+    cs, cs_acc = None, False
+    if upstream_bias is not None and W.need(upstream_bias):
+        cs, cs_acc = sink.buf(upstream_bias, W.f(upstream_bias))
+    out = ops.layernorm_bwd(dy, x, mean, rstd, gamma, residual_grad, dg, db, want_bf16=want_bf16, accumulate=acc,
+                            dx_colsum=cs, accumulate_colsum=cs_acc)
     sink.ready(gname)
     sink.ready(bname)
+    if cs is not None:
+        sink.ready(upstream_bias)
     return out
 
 
@@ -151,25 +160,27 @@ def block_fwd(W: Weights, pre: str, x: torch.Tensor, B: int, T: int, H: int, eps
 
 
 def block_bwd(W: Weights, sink: GradSink, pre: str, saved, dx: torch.Tensor, dxb: torch.Tensor, B: int, T: int, H: int,
-              want_bf16: bool = True):
-    """dx (fp32, updated in place) / dxb (its bf16 copy) = gradient w.r.t. the block output.
+              want_bf16: bool = True, prev_fc2_bias: str | None = None, fc2_bias_done: bool = False):
+    """dx (fp32, updated in place) / dxb (its bf16 copy) = gradient w.r.t. the block output.  fc2_bias_done: the
+    LayerNorm backward that produced them has already written this block's mlp.fc2.bias gradient.
+    prev_fc2_bias: bias of the previous block's fc2 (its gradient = column sums of the dx returned here).
     Returns (dx, dxb) w.r.t. the block input."""
     x, mean1, rstd1, h, qkv, o, lse, x1, mean2, rstd2, h2, dact, act = saved
     D = x.shape[1]
     hd = D // H
     # ---- MLP branch
-    _wgrad(W, sink, pre + "mlp.fc2.weight", pre + "mlp.fc2.bias", dxb, act)
+    _wgrad(W, sink, pre + "mlp.fc2.weight", None if fc2_bias_done else pre + "mlp.fc2.bias", dxb, act)
     dpre = ops.gemm(dxb, W.b(pre + "mlp.fc2.weight"), GEMM_NN, EPI_DGELU_BF16, aux=dact)
     _wgrad(W, sink, pre + "mlp.fc1.weight", pre + "mlp.fc1.bias", dpre, h2)
     dh2 = ops.gemm(dpre, W.b(pre + "mlp.fc1.weight"), GEMM_NN, EPI_BIAS_BF16)
-    dx, dxb = _ln_bwd(W, sink, pre + "norm2.", dh2, x1, mean2, rstd2, dx)
+    dx, dxb = _ln_bwd(W, sink, pre + "norm2.", dh2, x1, mean2, rstd2, dx, upstream_bias=pre + "attn.proj.bias")
     # ---- attention branch
-    _wgrad(W, sink, pre + "attn.proj.weight", pre + "attn.proj.bias", dxb, o)
+    _wgrad(W, sink, pre + "attn.proj.weight", None, dxb, o)
     do = ops.gemm(dxb, W.b(pre + "attn.proj.weight"), GEMM_NN, EPI_BIAS_BF16)
     dqkv = ops.attention_bwd(qkv, o, do, lse, B, T, H, hd, hd ** -0.5)
     _wgrad(W, sink, pre + "attn.qkv.weight", pre + "attn.qkv.bias", dqkv, h)
     dh = ops.gemm(dqkv, W.b(pre + "attn.qkv.weight"), GEMM_NN, EPI_BIAS_BF16)
-    dx, dxb = _ln_bwd(W, sink, pre + "norm1.", dh, x, mean1, rstd1, dx, want_bf16=want_bf16)
+    dx, dxb = _ln_bwd(W, sink, pre + "norm1.", dh, x, mean1, rstd1, dx, want_bf16=want_bf16, upstream_bias=prev_fc2_bias)
     return dx, dxb
 
 
@@ -226,10 +237,12 @@ def encoder_bwd(W: Weights, sink: GradSink, dims: ViTDims, sv: EncoderSaved, dla
     first = _first_needed_block(W, dims, dims.block_prefix, dims.depth, stem_needed)
     if first == dims.depth and not (W.need("norm.weight") or W.need("norm.bias")) and not stem_needed:
         return
-    dx, dxb = _ln_bwd(W, sink, "norm.", dlatent, sv.x_final, sv.mean, sv.rstd, None)
+    dx, dxb = _ln_bwd(W, sink, "norm.", dlatent, sv.x_final, sv.mean, sv.rstd, None,
+                      upstream_bias=f"{dims.block_prefix}{dims.depth - 1}.mlp.fc2.bias" if dims.depth > 0 else None)
     for i in range(dims.depth - 1, first - 1, -1):
         dx, dxb = block_bwd(W, sink, f"{dims.block_prefix}{i}.", sv.blocks[i], dx, dxb, N, Te, dims.num_heads,
-                            want_bf16=(i > first))
+                            want_bf16=(i > first), prev_fc2_bias=f"{dims.block_prefix}{i - 1}.mlp.fc2.bias" if i > 0 else None,
+                            fc2_bias_done=True)
         sv.blocks[i] = None                      # free the block's activations as soon as they are consumed
     if not stem_needed:
         return
@@ -288,10 +301,12 @@ def decoder_bwd(W: Weights, sink: GradSink, dims: ViTDims, sv: DecoderSaved, dpr
     dp = dpred_full.view(N * T, -1)
     _wgrad(W, sink, "decoder_pred.weight", "decoder_pred.bias", dp, sv.hn)
     dhn = ops.gemm(dp, W.b("decoder_pred.weight"), GEMM_NN, EPI_BIAS_BF16)
-    dx, dxb = _ln_bwd(W, sink, "decoder_norm.", dhn, sv.x_final, sv.mean, sv.rstd, None)
+    dx, dxb = _ln_bwd(W, sink, "decoder_norm.", dhn, sv.x_final, sv.mean, sv.rstd, None,
+                      upstream_bias=f"decoder_blocks.{dims.decoder_depth - 1}.mlp.fc2.bias" if dims.decoder_depth > 0 else None)
     for i in range(dims.decoder_depth - 1, -1, -1):
         dx, dxb = block_bwd(W, sink, f"decoder_blocks.{i}.", sv.blocks[i], dx, dxb, N, T, dims.decoder_num_heads,
-                            want_bf16=(i > 0))
+                            want_bf16=(i > 0), prev_fc2_bias=f"decoder_blocks.{i - 1}.mlp.fc2.bias" if i > 0 else None,
+                            fc2_bias_done=True)
         sv.blocks[i] = None
     mt = W.f("mask_token")
     if W.need("mask_token"):

@@ -294,5 +294,10 @@ def test_engine_step_matches_oracle_adamw_step():
     for k, p in m.named_parameters():
         delta_o = params[k].detach() - sd[k]
         delta = p.detach().cpu() - sd[k]
+        if k.endswith("attn.qkv.bias"):
+            # the k-bias gradient is analytically zero (softmax is invariant to a shift of all keys), so Adam turns
+            # pure round-off into +-lr steps there on both sides: compare the q and v thirds only
+            n = delta.numel() // 3
+            delta, delta_o = torch.cat([delta[:n], delta[2 * n:]]), torch.cat([delta_o[:n], delta_o[2 * n:]])
         if delta_o.abs().max() > 0:
             assert cos(delta, delta_o) > 0.98, k

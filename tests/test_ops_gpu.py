@@ -179,7 +179,7 @@ def test_decoder_unshuffle_fwd_bwd():
 
 
 # ---------------------------------------------------------------------------------------------- LayerNorm
-@pytest.mark.parametrize("M,D", [(100, 768), (394, 512), (50, 1024), (37, 64), (20, 32)])
+@pytest.mark.parametrize("M,D", [(100, 768), (394, 512), (50, 1024), (37, 64), (20, 32), (5000, 512)])
 def test_layernorm_fwd_bwd(M, D):
     from ssl4polyp_b200 import ops
     x = (torch.randn(M, D) * 2 + 0.5).requires_grad_(True)
@@ -192,8 +192,11 @@ def test_layernorm_fwd_bwd(M, D):
     y_ref.backward(dy.float())
     res = torch.randn(M, D)
     dgamma = torch.zeros(D, device=dev()); dbeta = torch.zeros(D, device=dev())
-    dx, dxb = ops.layernorm_bwd(dy.to(dev()), x.detach().to(dev()), mean, rstd, gamma.detach().to(dev()), res.to(dev()).clone(), dgamma, dbeta)
+    colsum = torch.ones(D, device=dev())
+    dx, dxb = ops.layernorm_bwd(dy.to(dev()), x.detach().to(dev()), mean, rstd, gamma.detach().to(dev()), res.to(dev()).clone(), dgamma, dbeta,
+                                dx_colsum=colsum, accumulate_colsum=True)
     assert rel_err(dx.cpu(), x.grad + res) < 1e-4
+    assert rel_err(colsum.cpu(), 1 + (x.grad + res).sum(0)) < 1e-4          # the upstream Linear's bias gradient, same pass
     assert rel_err(dxb.cpu(), x.grad + res) < 5e-3
     assert rel_err(dgamma.cpu(), gamma.grad) < 1e-4
     assert rel_err(dbeta.cpu(), beta.grad) < 1e-4
