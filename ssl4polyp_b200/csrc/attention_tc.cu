@@ -20,46 +20,11 @@
 //   S^T = K Q^T and dP^T = V dO^T into TMEM; 8 warps turn them into P^T and dS^T (bf16, shared memory) using the saved
 //   log-sum-exp and D = rowsum(dO * O); then dV += P^T dO, dK += dS^T Q, dQ += dS K accumulate in TMEM.
 //   Deterministic (no atomics).
-#include "common.cuh"
-#include "ssl4p.h"
+#include "attn_common.cuh"
 #include <mutex>
 #include <unordered_map>
 
 namespace ssl4p {
-
-constexpr int kAttnThreads = 320;
-constexpr float kLog2eF = 1.4426950408889634f;
-
-__device__ __forceinline__ float fast_exp2(float x) {
-    float y;
-    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
-    return y;
-}
-
-// 3-D tiled load: coordinates {c0 = column, c1 = token, c2 = image}
-__device__ __forceinline__ void tma_load_3d(void* smem_dst, const CUtensorMap* m, uint64_t* bar, int c0, int c1, int c2) {
-    asm volatile(
-        "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
-        ::"r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2)
-        : "memory");
-}
-
-__device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
-    asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
-}
-
-// runtime-N instruction descriptor (same fields as umma_idesc_bf16)
-__device__ __forceinline__ uint32_t idesc_rt(int M, int N, bool a_mn, bool b_mn) {
-    return (1u << 4) | (1u << 7) | (1u << 10) | ((a_mn ? 1u : 0u) << 15) | ((b_mn ? 1u : 0u) << 16) |
-           ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
-}
-
-// byte offset of the 16-byte chunk `chunk16` (0..7) of row `row` inside a [rows x 128 B] SWIZZLE_128B tile
-__device__ __forceinline__ uint32_t sw128_off(int row, int chunk16) {
-    return (uint32_t)row * 128u + (uint32_t)((chunk16 ^ (row & 7)) << 4);
-}
-
-constexpr int kTileBytes = 128 * 128;          // one [128 rows x 64 bf16] SW128 tile
 
 struct AttnFwdParams {
     int T, H, items, slices_per_img;           // slices_per_img = H*hd/64
@@ -612,11 +577,11 @@ static EncodeTiledFn3 attn_encode_fn() {
 }
 
 // bf16 [B, T, cols] (cols contiguous): box = 64 columns x 128 tokens x 1 image, SWIZZLE_128B, zero fill for t >= T.
-static int make_tmap_tokens(CUtensorMap* out, const void* ptr, long long cols, long long T, long long B) {
-    struct Key { const void* p; long long c, t, b; bool operator==(const Key& o) const { return p == o.p && c == o.c && t == o.t && b == o.b; } };
-    struct Hash { size_t operator()(const Key& k) const { return std::hash<const void*>()(k.p) ^ (size_t)(k.c * 1315423911ull) ^ (size_t)(k.t * 2654435761ull) ^ (size_t)(k.b << 9); } };
+int make_tmap_tokens(CUtensorMap* out, const void* ptr, long long cols, long long T, long long B, int box_rows) {
+    struct Key { const void* p; long long c, t, b; int r; bool operator==(const Key& o) const { return p == o.p && c == o.c && t == o.t && b == o.b && r == o.r; } };
+    struct Hash { size_t operator()(const Key& k) const { return std::hash<const void*>()(k.p) ^ (size_t)(k.c * 1315423911ull) ^ (size_t)(k.t * 2654435761ull) ^ (size_t)(k.b << 9) ^ (size_t)k.r; } };
     static thread_local std::unordered_map<Key, CUtensorMap, Hash> cache;
-    Key key{ptr, cols, T, B};
+    Key key{ptr, cols, T, B, box_rows};
     auto it = cache.find(key);
     if (it != cache.end()) { *out = it->second; return SSL4P_OK; }
     EncodeTiledFn3 enc = attn_encode_fn();
@@ -625,7 +590,8 @@ static int make_tmap_tokens(CUtensorMap* out, const void* ptr, long long cols, l
     SSL4P_REQUIRE(cols % 64 == 0, "attention: H*head_dim must be a multiple of 64 (got row of %lld columns)", cols);
     cuuint64_t dims[3] = {(cuuint64_t)cols, (cuuint64_t)T, (cuuint64_t)B};
     cuuint64_t strides[2] = {(cuuint64_t)cols * 2, (cuuint64_t)cols * 2 * (cuuint64_t)T};
-    cuuint32_t box[3] = {64u, 128u, 1u};
+    SSL4P_REQUIRE(box_rows >= 8 && box_rows <= 256 && box_rows % 8 == 0, "attention: bad TMA box (%d rows)", box_rows);
+    cuuint32_t box[3] = {64u, (cuuint32_t)box_rows, 1u};
     cuuint32_t estr[3] = {1u, 1u, 1u};
     CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(ptr), dims, strides, box, estr,
                      CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
@@ -642,7 +608,7 @@ constexpr int kBwdSmem = 12 * kTileBytes + 4096 + 256 + 1024;
 template <int HD>
 static int launch_fwd_tc(const void* qkv, void* out, float* lse, int B, int T, int H, float scale, cudaStream_t s) {
     CUtensorMap tm;
-    int rc = make_tmap_tokens(&tm, qkv, 3LL * H * HD, T, B);
+    int rc = make_tmap_tokens(&tm, qkv, 3LL * H * HD, T, B, 128);
     if (rc) return rc;
     AttnFwdParams p;
     p.T = T; p.H = H; p.slices_per_img = H * HD / 64; p.items = B * p.slices_per_img;
@@ -660,9 +626,9 @@ template <int HD>
 static int launch_bwd_tc(const void* qkv, const void* out, const void* dout, const float* lse, void* dqkv, int B, int T, int H,
                          float scale, cudaStream_t s) {
     CUtensorMap tmQ, tmD;
-    int rc = make_tmap_tokens(&tmQ, qkv, 3LL * H * HD, T, B);
+    int rc = make_tmap_tokens(&tmQ, qkv, 3LL * H * HD, T, B, 128);
     if (rc) return rc;
-    rc = make_tmap_tokens(&tmD, dout, (long long)H * HD, T, B);
+    rc = make_tmap_tokens(&tmD, dout, (long long)H * HD, T, B, 128);
     if (rc) return rc;
     AttnBwdParams p;
     p.T = T; p.H = H; p.slices_per_img = H * HD / 64; p.items = B * p.slices_per_img;
@@ -688,7 +654,7 @@ static int attn_tc_check(int B, int T, int H, int hd) {
     return SSL4P_OK;
 }
 
-extern "C" int ssl4p_attention_fwd(const void* qkv, void* out, float* lse, int B, int T, int H, int hd, float scale, void* stream) {
+extern "C" int ssl4p_attention_fwd_tc1(const void* qkv, void* out, float* lse, int B, int T, int H, int hd, float scale, void* stream) {
     SSL4P_REQUIRE(qkv && out && lse, "attention_fwd: null pointer");
     int rc = attn_tc_check(B, T, H, hd);
     if (rc) return rc;

@@ -281,7 +281,7 @@ def attention_fwd(qkv, B, T, H, hd, scale, impl="tcgen05"):
     _req(qkv, bf16, "qkv")
     out = torch.empty(B * T, H * hd, dtype=bf16, device=qkv.device)
     lse = torch.empty(B, H, T, dtype=f32, device=qkv.device)
-    fn = lib.ssl4p_attention_fwd if impl == "tcgen05" else lib.ssl4p_attention_fwd_mma
+    fn = {"tcgen05": lib.ssl4p_attention_fwd, "tc1": lib.ssl4p_attention_fwd_tc1, "mma": lib.ssl4p_attention_fwd_mma}[impl]
     _lib.check(fn(qkv.data_ptr(), out.data_ptr(), lse.data_ptr(), B, T, H, hd, float(scale), _stream()), "attention_fwd")
     return out, lse
 
@@ -290,7 +290,7 @@ def attention_bwd(qkv, out, dout, lse, B, T, H, hd, scale, impl="tcgen05"):
     lib = _lib.load()
     _req(dout, bf16, "dout")
     dqkv = torch.empty_like(qkv)
-    fn = lib.ssl4p_attention_bwd if impl == "tcgen05" else lib.ssl4p_attention_bwd_mma
+    fn = lib.ssl4p_attention_bwd_mma if impl == "mma" else lib.ssl4p_attention_bwd
     _lib.check(fn(qkv.data_ptr(), out.data_ptr(), dout.data_ptr(), lse.data_ptr(), dqkv.data_ptr(), B, T, H, hd, float(scale),
                                        _stream()), "attention_bwd")
     return dqkv

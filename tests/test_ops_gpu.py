@@ -206,15 +206,18 @@ def test_layernorm_fwd_bwd(M, D):
 
 
 # ---------------------------------------------------------------------------------------------- attention
-@pytest.mark.parametrize("impl", ["tcgen05", "mma"])
+@pytest.mark.parametrize("impl", ["tcgen05", "tc1", "fwd2", "mma"])
 @pytest.mark.parametrize("B,T,H,hd", [(2, 50, 12, 64), (2, 197, 16, 32), (1, 197, 12, 64), (3, 5, 2, 32), (2, 17, 2, 32), (2, 64, 4, 64),
-                                      (40, 50, 12, 64), (21, 197, 16, 32), (3, 128, 2, 64), (2, 129, 4, 32), (1, 256, 2, 32)])
-def test_attention_fwd_bwd(B, T, H, hd, impl):
+                                      (40, 50, 12, 64), (21, 197, 16, 32), (3, 128, 2, 64), (2, 129, 4, 32), (1, 256, 2, 32), (300, 208, 2, 32), (5, 209, 2, 64), (160, 16, 2, 32)])
+def test_attention_fwd_bwd(B, T, H, hd, impl, monkeypatch):
     """Both attention kernels against fp32 torch on the same bf16 inputs (the larger batches put several work items
     on every persistent CTA; T = 128/129/256 sit on the tile boundaries)."""
     from ssl4polyp_b200 import ops
     if impl == "mma" and T > 208:
         pytest.skip("the mma.sync cross-check kernel stops at T = 208")
+    if impl == "fwd2":
+        monkeypatch.setenv("SSL4P_ATTN_FWD", "2")            # force the ring-buffered forward for every T
+        impl = "tcgen05"
     torch.manual_seed(B * 1000 + T)
     qkv = torch.randn(B, T, 3, H, hd).bfloat16()
     scale = hd ** -0.5
