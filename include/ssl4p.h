@@ -42,7 +42,9 @@ enum {
                                         is what backward needs; both come from one erf evaluation)         */
     SSL4P_EPI_BIAS_RESIDUAL_F32 = 2, /* C(fp32)  = acc + bias + aux(fp32)     (attn.proj / Mlp.fc2 + skip) */
     SSL4P_EPI_BIAS_F32 = 3,          /* C(fp32)  = acc + bias                                             */
-    SSL4P_EPI_DGELU_BF16 = 4,        /* C(bf16)  = acc * aux(bf16), aux = the saved gelu_erf'(h)   (dgrad through GELU)  */
+    SSL4P_EPI_DGELU_BF16 = 4,        /* C(bf16)  = acc * aux(bf16), aux = the saved gelu_erf'(h)   (dgrad through GELU);
+                                        optional C2 = fp32 [ceil(M/32), N]: column sums of C per 32-row group (the Mlp.fc1 bias
+                                        gradient without a second pass over C; finish with ssl4p_reduce_rows_f32)  */
     SSL4P_EPI_PARTIAL_F32 = 5        /* C(fp32)[split] = acc  (split-K partial planes, M*ldc apart)       */
 };
 #define SSL4P_MAX_SPLITS 16
@@ -51,6 +53,8 @@ int ssl4p_gemm_bf16(const void* A, const void* B, void* C, void* C2, const float
                     int layout, int epilogue, int splits, int force_bn, void* stream);
 int ssl4p_gemm_pick_splits(int M, int N, int K);
 size_t ssl4p_gemm_workspace_bytes(int M, int N, int K, int layout, int epilogue);
+/* out[j] (+)= sum_g part[g*N + j], g < G  (two fixed-order stages: deterministic); workspace >= 32*N floats */
+int ssl4p_reduce_rows_f32(const float* part, int G, int N, float* out, int accumulate, void* workspace, size_t workspace_bytes, void* stream);
 /* out[i] (+)= sum_s parts[s*stride + i]   (fixed order: deterministic) */
 int ssl4p_splitk_reduce(const float* parts, int splits, long long stride, float* out, long long n, int accumulate, void* stream);
 

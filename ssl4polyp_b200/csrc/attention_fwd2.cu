@@ -368,7 +368,11 @@ extern "C" int ssl4p_attention_fwd(const void* qkv, void* out, float* lse, int B
     cudaStream_t s = (cudaStream_t)stream;
     // Measured on B200 (scripts/attn_bench.py, B=256): the ring-buffered kernel wins for one-tile sequences (T=50: 62 vs
     // 76 us); with two query tiles per head the two-warpgroup kernel of attention_tc.cu is ahead (T=197: 199 vs 211 us).
+    // For T <= 64 (the 50-token encoder of the pretraining step) nothing is tensor bound: 0.09 GFLOP/img against 79 MB
+    // of qkv/out traffic per layer; the register-resident mma.sync kernel of attention.cu (one CTA per (image, head),
+    // no TMEM round trips) finishes in 51 us where the tcgen05 pipelines need 76-84 us.
     const char* force = getenv("SSL4P_ATTN_FWD");
+    if (!force && T <= 64) return ssl4p_attention_fwd_mma(qkv, out, lse, B, T, H, hd, scale, stream);
     const bool use2 = force ? (force[0] == '2') : (T <= 128);
     if (!use2) return ssl4p_attention_fwd_tc1(qkv, out, lse, B, T, H, hd, scale, stream);
     if (hd == 64) return launch_fwd2<64>(qkv, out, lse, B, T, H, scale, s);

@@ -82,6 +82,65 @@ __device__ __forceinline__ void gelu_and_grad_f(float x, float& g, float& dg) {
     dg = fmaf(x * e, 0.3989422804014327f, phi_cdf);
 }
 
+// ---- packed fp32x2 arithmetic (sm_100: FFMA2 / FMUL2 / FADD2 process two fp32 lanes per issue slot) ----------
+typedef unsigned long long f32x2;
+__device__ __forceinline__ f32x2 f2_pack(float lo, float hi) {
+    f32x2 r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi)); return r;
+}
+__device__ __forceinline__ void f2_unpack(f32x2 v, float& lo, float& hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
+__device__ __forceinline__ f32x2 f2_fma(f32x2 a, f32x2 b, f32x2 c) { f32x2 d; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c)); return d; }
+__device__ __forceinline__ f32x2 f2_mul(f32x2 a, f32x2 b) { f32x2 d; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b)); return d; }
+__device__ __forceinline__ f32x2 f2_add(f32x2 a, f32x2 b) { f32x2 d; asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b)); return d; }
+__device__ __forceinline__ f32x2 f2_splat(float v) { return f2_pack(v, v); }
+
+// The same GELU / GELU' for two elements at once: the polynomial, the products and the final combinations run on
+// FFMA2 (13 packed issue slots per pair instead of 2 x 16 scalar ones); rcp / ex2 / |x| / copysign stay scalar.
+__device__ __forceinline__ void gelu_and_grad_f2(float x0, float x1, float& g0, float& g1, float& d0, float& d1) {
+    const f32x2 x = f2_pack(x0, x1);
+    const f32x2 ax = f2_pack(fabsf(x0), fabsf(x1));
+    float u0, u1, t0, t1, e0, e1, q0, q1;
+    f2_unpack(f2_fma(ax, f2_splat(0.3275911f * 0.70710678118654752f), f2_splat(1.0f)), u0, u1);
+    f2_unpack(f2_mul(f2_mul(x, x), f2_splat(-0.72134752044448170f)), q0, q1);
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t0) : "f"(u0));
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t1) : "f"(u1));
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e0) : "f"(q0));
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e1) : "f"(q1));
+    const f32x2 t = f2_pack(t0, t1), e = f2_pack(e0, e1);
+    f32x2 poly = f2_fma(t, f2_splat(1.061405429f), f2_splat(-1.453152027f));
+    poly = f2_fma(poly, t, f2_splat(1.421413741f));
+    poly = f2_fma(poly, t, f2_splat(-0.284496736f));
+    poly = f2_fma(poly, t, f2_splat(0.254829592f));
+    const f32x2 erf_abs = f2_fma(f2_mul(poly, t), f2_mul(e, f2_splat(-1.0f)), f2_splat(1.0f));   // erf(|x|/sqrt 2)
+    float a0, a1;
+    f2_unpack(erf_abs, a0, a1);
+    const f32x2 cdf = f2_fma(f2_pack(copysignf(a0, x0), copysignf(a1, x1)), f2_splat(0.5f), f2_splat(0.5f));
+    f2_unpack(f2_mul(x, cdf), g0, g1);
+    f2_unpack(f2_fma(f2_mul(x, e), f2_splat(0.3989422804014327f), cdf), d0, d1);
+}
+
+// ---- explicit state-space accesses: a pointer computed from the dynamic shared-memory base or taken out of a
+// parameter struct is GENERIC to the compiler; generic LD/ST are slower and, worse, may alias each other, which
+// pins every shared-memory load behind the preceding global store.
+__device__ __forceinline__ void sts_v4(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d));
+}
+__device__ __forceinline__ float4 lds_v4f(uint32_t addr) {
+    float4 v;
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
+    return v;
+}
+__device__ __forceinline__ void stg_v4(void* p, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+    asm volatile("st.global.v4.b32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(a), "r"(b), "r"(c), "r"(d));
+}
+__device__ __forceinline__ void stg_v4f(void* p, float4 v) {
+    asm volatile("st.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w));
+}
+__device__ __forceinline__ uint4 ldg_v4(const void* p) {
+    uint4 v;
+    asm volatile("ld.global.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
+    return v;
+}
+
 // ---- mbarrier -----------------------------------------------------------------------------------
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));

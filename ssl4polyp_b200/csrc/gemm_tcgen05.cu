@@ -73,7 +73,7 @@ __device__ __forceinline__ void load_aux(const GemmParams& p, int row_base, int 
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
             const int row = row_base + 4 * i + (lane >> 3);
-            a.v[i] = (row < p.M && col < p.N) ? *reinterpret_cast<const uint4*>(reinterpret_cast<const float*>(p.aux) + (size_t)row * p.ldaux + col)
+            a.v[i] = (row < p.M && col < p.N) ? ldg_v4(reinterpret_cast<const float*>(p.aux) + (size_t)row * p.ldaux + col)
                                               : make_uint4(0u, 0u, 0u, 0u);
         }
     } else if constexpr (EPI == SSL4P_EPI_DGELU_BF16) {
@@ -81,84 +81,115 @@ __device__ __forceinline__ void load_aux(const GemmParams& p, int row_base, int 
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
             const int row = row_base + 8 * i + (lane >> 2);
-            a.v[i] = (row < p.M && col < p.N) ? *reinterpret_cast<const uint4*>(reinterpret_cast<const __nv_bfloat16*>(p.aux) + (size_t)row * p.ldaux + col)
+            a.v[i] = (row < p.M && col < p.N) ? ldg_v4(reinterpret_cast<const __nv_bfloat16*>(p.aux) + (size_t)row * p.ldaux + col)
                                               : make_uint4(0u, 0u, 0u, 0u);
         }
     }
 }
 
+// stg: shared-space address of this warp's 4 KB transpose patch.
 template <int EPI>
-__device__ __forceinline__ void epilogue_chunk(const GemmParams& p, uint8_t* stg, int row_base, int col0, int split, uint32_t (&acc)[32],
+__device__ __forceinline__ void epilogue_chunk(const GemmParams& p, uint32_t stg, int row_base, int col0, int split, uint32_t (&acc)[32],
                                                const AuxRegs& aux) {
     const int lane = (int)lane_id();
-    auto transpose_in = [&]() {                                    // called after the global loads of the chunk have been issued
-#pragma unroll
-        for (int c = 0; c < 8; ++c)
-            *reinterpret_cast<uint4*>(stg + lane * 128 + ((c ^ (lane & 7)) << 4)) = make_uint4(acc[4 * c], acc[4 * c + 1], acc[4 * c + 2], acc[4 * c + 3]);
-        __syncwarp();
-    };
-
     constexpr bool kHasBias = EPI == SSL4P_EPI_BIAS_BF16 || EPI == SSL4P_EPI_BIAS_GELU_BF16 || EPI == SSL4P_EPI_BIAS_RESIDUAL_F32 ||
                               EPI == SSL4P_EPI_BIAS_F32;
     constexpr bool kOutF32 = EPI == SSL4P_EPI_BIAS_RESIDUAL_F32 || EPI == SSL4P_EPI_BIAS_F32 || EPI == SSL4P_EPI_PARTIAL_F32;
 
+    // ---- transpose through the patch: every lane writes its row (32 columns), then reads 8 x 16 B in the
+    // row-contiguous mapping.  All shared-memory reads are issued before any global store.
+#pragma unroll
+    for (int c = 0; c < 8; ++c)
+        sts_v4(stg + lane * 128 + ((c ^ (lane & 7)) << 4), acc[4 * c], acc[4 * c + 1], acc[4 * c + 2], acc[4 * c + 3]);
+    __syncwarp();
+    float4 t[8];
     if constexpr (kOutF32) {
         const int cc = lane & 7;                                   // 16-byte chunk = 4 columns
-        const int col = col0 + cc * 4;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const int rr = 4 * i + (lane >> 3);
+            t[i] = lds_v4f(stg + rr * 128 + ((cc ^ (rr & 7)) << 4));
+        }
+    } else {
+        const int cc = lane & 3;                                   // 16-byte bf16 chunk = 8 columns
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int rr = 8 * i + (lane >> 2);
+            t[2 * i] = lds_v4f(stg + rr * 128 + (((2 * cc) ^ (rr & 7)) << 4));
+            t[2 * i + 1] = lds_v4f(stg + rr * 128 + (((2 * cc + 1) ^ (rr & 7)) << 4));
+        }
+    }
+    __syncwarp();                                                  // the patch may be rewritten by the next chunk
+
+    if constexpr (kOutF32) {
+        const int col = col0 + (lane & 7) * 4;
         const bool col_ok = col < p.N;                             // N % 8 == 0 (checked on the host)
         float4 b = make_float4(0.f, 0.f, 0.f, 0.f);
         if constexpr (kHasBias) if (p.bias != nullptr && col_ok) b = __ldg(reinterpret_cast<const float4*>(p.bias + col));
         float* outp = reinterpret_cast<float*>(p.C) + (EPI == SSL4P_EPI_PARTIAL_F32 ? (size_t)split * p.split_stride : 0);
-        transpose_in();
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
-            const int rr = 4 * i + (lane >> 3);
-            const int row = row_base + rr;
-            float4 v = *reinterpret_cast<const float4*>(stg + rr * 128 + ((cc ^ (rr & 7)) << 4));
-            v = f4_add(v, b);
+            const int row = row_base + 4 * i + (lane >> 3);
+            float4 v = f4_add(t[i], b);
             if constexpr (EPI == SSL4P_EPI_BIAS_RESIDUAL_F32)
                 v = f4_add(v, make_float4(__uint_as_float(aux.v[i].x), __uint_as_float(aux.v[i].y), __uint_as_float(aux.v[i].z), __uint_as_float(aux.v[i].w)));
-            if (row < p.M && col_ok) *reinterpret_cast<float4*>(outp + (size_t)row * p.ldc + col) = v;
+            if (row < p.M && col_ok) stg_v4f(outp + (size_t)row * p.ldc + col, v);
         }
     } else {
-        const int cc = lane & 3;                                   // 16-byte bf16 chunk = 8 columns
-        const int col = col0 + cc * 8;
+        const int col = col0 + (lane & 3) * 8;
         const bool col_ok = col < p.N;
         float4 b0 = make_float4(0.f, 0.f, 0.f, 0.f), b1 = b0;
         if constexpr (kHasBias) if (p.bias != nullptr && col_ok) {
             b0 = __ldg(reinterpret_cast<const float4*>(p.bias + col));
             b1 = __ldg(reinterpret_cast<const float4*>(p.bias + col + 4));
         }
-        transpose_in();
+        float csum[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};   // DGELU: column sums of this warp's 32 rows (fc1 bias gradient)
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
-            const int rr = 8 * i + (lane >> 2);
-            const int row = row_base + rr;
-            const float4 lo = *reinterpret_cast<const float4*>(stg + rr * 128 + (((2 * cc) ^ (rr & 7)) << 4));
-            const float4 hi = *reinterpret_cast<const float4*>(stg + rr * 128 + (((2 * cc + 1) ^ (rr & 7)) << 4));
-            if (row < p.M && col_ok) {
-                float v[8] = {lo.x + b0.x, lo.y + b0.y, lo.z + b0.z, lo.w + b0.w, hi.x + b1.x, hi.y + b1.y, hi.z + b1.z, hi.w + b1.w};
-                if constexpr (EPI == SSL4P_EPI_DGELU_BF16) {
-                    const uint32_t hw[4] = {aux.v[i].x, aux.v[i].y, aux.v[i].z, aux.v[i].w};
+            const int row = row_base + 8 * i + (lane >> 2);
+            const float4 lo = t[2 * i], hi = t[2 * i + 1];
+            float v[8] = {lo.x + b0.x, lo.y + b0.y, lo.z + b0.z, lo.w + b0.w, hi.x + b1.x, hi.y + b1.y, hi.z + b1.z, hi.w + b1.w};
+            if constexpr (EPI == SSL4P_EPI_DGELU_BF16) {
+                const uint32_t hw[4] = {aux.v[i].x, aux.v[i].y, aux.v[i].z, aux.v[i].w};
 #pragma unroll
-                    for (int q = 0; q < 4; ++q) { const float2 hf = unpack_bf16(hw[q]); v[2 * q] *= hf.x; v[2 * q + 1] *= hf.y; }
-                }
-                if constexpr (EPI == SSL4P_EPI_BIAS_GELU_BF16) {
-                    // C = gelu'(h) (what the backward multiplies by), C2 = gelu(h): one erf evaluation serves both
-                    float g[8];
+                for (int q = 0; q < 4; ++q) { const float2 hf = unpack_bf16(hw[q]); v[2 * q] *= hf.x; v[2 * q + 1] *= hf.y; }
+            }
+            const bool ok = row < p.M && col_ok;
+            if constexpr (EPI == SSL4P_EPI_DGELU_BF16) {
 #pragma unroll
-                    for (int j = 0; j < 8; ++j) { float a, d; gelu_and_grad_f(v[j], a, d); g[j] = a; v[j] = d; }
-                    uint4 o2;
-                    o2.x = pack_bf16(g[0], g[1]); o2.y = pack_bf16(g[2], g[3]); o2.z = pack_bf16(g[4], g[5]); o2.w = pack_bf16(g[6], g[7]);
-                    *reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(p.C2) + (size_t)row * p.ldc2 + col) = o2;
+                for (int j = 0; j < 8; ++j) csum[j] += ok ? v[j] : 0.f;
+            }
+            if constexpr (EPI == SSL4P_EPI_BIAS_GELU_BF16) {
+                // C = gelu'(h) (what the backward multiplies by), C2 = gelu(h): one erf evaluation serves both
+                float g[8];
+#pragma unroll
+                for (int j = 0; j < 8; j += 2) {
+                    float a0, a1, d0, d1;
+                    gelu_and_grad_f2(v[j], v[j + 1], a0, a1, d0, d1);
+                    g[j] = a0; g[j + 1] = a1; v[j] = d0; v[j + 1] = d1;
                 }
-                uint4 o;
-                o.x = pack_bf16(v[0], v[1]); o.y = pack_bf16(v[2], v[3]); o.z = pack_bf16(v[4], v[5]); o.w = pack_bf16(v[6], v[7]);
-                *reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(p.C) + (size_t)row * p.ldc + col) = o;
+                if (ok) stg_v4(reinterpret_cast<__nv_bfloat16*>(p.C2) + (size_t)row * p.ldc2 + col,
+                               pack_bf16(g[0], g[1]), pack_bf16(g[2], g[3]), pack_bf16(g[4], g[5]), pack_bf16(g[6], g[7]));
+            }
+            if (ok) stg_v4(reinterpret_cast<__nv_bfloat16*>(p.C) + (size_t)row * p.ldc + col,
+                           pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]), pack_bf16(v[4], v[5]), pack_bf16(v[6], v[7]));
+        }
+        if constexpr (EPI == SSL4P_EPI_DGELU_BF16) {
+            if (p.C2 != nullptr) {                                 // fixed-order butterfly over the 8 lanes that share a column group
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    csum[j] += __shfl_xor_sync(0xffffffffu, csum[j], 4);
+                    csum[j] += __shfl_xor_sync(0xffffffffu, csum[j], 8);
+                    csum[j] += __shfl_xor_sync(0xffffffffu, csum[j], 16);
+                }
+                if (lane < 4 && col_ok && row_base < p.M) {
+                    float* dst = reinterpret_cast<float*>(p.C2) + (size_t)(row_base >> 5) * p.N + col;
+                    stg_v4f(dst, make_float4(csum[0], csum[1], csum[2], csum[3]));
+                    stg_v4f(dst + 4, make_float4(csum[4], csum[5], csum[6], csum[7]));
+                }
             }
         }
     }
-    __syncwarp();                                                  // the patch is rewritten by the next chunk
 }
 
 // ---- the kernel ---------------------------------------------------------------------------------
@@ -298,7 +329,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             if constexpr (kAux) load_aux<EPI>(p, row_base, n0 + chunk0, aux_cur);      // in flight while the MMAs of the tile finish
             mbar_wait(&tmem_full[acc], acc_phase);
             tc_fence_after();
-            uint8_t* stg = epi_stage + (warp - 2) * kStageBytesPerWarp;
+            const uint32_t stg = smem_u32(epi_stage) + (warp - 2) * kStageBytesPerWarp;
             const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + acc * kAccStride;
             const bool empty_split = split * p.k_per_split >= p.K;   // empty split-K range: the accumulator was never written
 #pragma unroll 1
@@ -445,12 +476,14 @@ extern "C" size_t ssl4p_gemm_workspace_bytes(int M, int N, int K, int layout, in
 }
 
 extern "C" int ssl4p_gemm_pick_splits(int M, int N, int K) {
-    // split K so that the tile count reaches ~2 waves; each split keeps >= 8 K-blocks
+    // ONE wave of 128x256 tiles: the largest split count whose tile total still fits the SM count (measured on B200,
+    // scripts/wgrad_sweep.py: a second, partly filled wave costs more than the longer K loop of a single full one);
+    // each split keeps >= 4 K-blocks.
     const int sms = num_sms();
     const int tiles = ((M + BM - 1) / BM) * ((N + 255) / 256);
-    int s = (2 * sms + tiles - 1) / tiles;
+    int s = sms / tiles;
     const int kb = (K + BK - 1) / BK;
-    if (s > kb / 8) s = kb / 8;
+    if (s > kb / 4) s = kb / 4;
     if (s > SSL4P_MAX_SPLITS) s = SSL4P_MAX_SPLITS;
     if (s < 1) s = 1;
     return s;

@@ -211,6 +211,21 @@ __global__ void reduce_rows_kernel(const float* __restrict__ part, int G, int D,
     out[d] = acc;
 }
 
+// stage 1 of a tall reduce: block (128 columns) x slab of rows -> part2[slab][D]
+__global__ void reduce_rows_slab_kernel(const float* __restrict__ part, int G, int D, int rows_per_slab, float* __restrict__ part2) {
+    const int d = blockIdx.x * blockDim.x + threadIdx.x;
+    if (d >= D) return;
+    const int g0 = blockIdx.y * rows_per_slab, g1 = min(G, g0 + rows_per_slab);
+    float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+    int g = g0;
+    for (; g + 3 < g1; g += 4) {
+        a0 += part[(size_t)g * D + d]; a1 += part[(size_t)(g + 1) * D + d];
+        a2 += part[(size_t)(g + 2) * D + d]; a3 += part[(size_t)(g + 3) * D + d];
+    }
+    for (; g < g1; ++g) a0 += part[(size_t)g * D + d];
+    part2[(size_t)blockIdx.y * D + d] = (a0 + a1) + (a2 + a3);
+}
+
 // ---------------------------------------------------------------------------------------------------------
 // column sums of a bf16 matrix (bias gradients): stage 1 = slabs of rows, stage 2 = fixed-order reduce
 // block (32, 8): lane -> 2 adjacent columns, ty -> row phase
@@ -390,6 +405,22 @@ extern "C" int ssl4p_decoder_unshuffle_bwd(const float* dx, const int64_t* ids_k
     rc = check_launch("mask_token_grad_partial_kernel");
     if (rc) return rc;
     reduce_rows_kernel<<<(Dd + 127) / 128, 128, 0, STREAM>>>((const float*)workspace, G, Dd, dmask_token, accumulate);
+    return check_launch("reduce_rows_kernel");
+}
+
+extern "C" int ssl4p_reduce_rows_f32(const float* part, int G, int N, float* out, int accumulate, void* workspace, size_t workspace_bytes, void* stream) {
+    SSL4P_REQUIRE(part && out && G > 0 && N > 0, "reduce_rows: bad arguments");
+    if (G <= 32) {
+        reduce_rows_kernel<<<(N + 127) / 128, 128, 0, STREAM>>>(part, G, N, out, accumulate);
+        return check_launch("reduce_rows_kernel");
+    }
+    SSL4P_REQUIRE(workspace && workspace_bytes >= (size_t)32 * N * sizeof(float), "reduce_rows: workspace too small");
+    const int rows_per_slab = (G + 31) / 32;
+    const int S = (G + rows_per_slab - 1) / rows_per_slab;
+    reduce_rows_slab_kernel<<<dim3((N + 127) / 128, S), 128, 0, STREAM>>>(part, G, N, rows_per_slab, (float*)workspace);
+    int rc = check_launch("reduce_rows_slab_kernel");
+    if (rc) return rc;
+    reduce_rows_kernel<<<(N + 127) / 128, 128, 0, STREAM>>>((const float*)workspace, S, N, out, accumulate);
     return check_launch("reduce_rows_kernel");
 }
 

@@ -64,7 +64,7 @@ def _gemm_launch(lib, M, N, K, layout, epilogue, *args):
 
 
 def gemm(a, b, layout, epilogue, *, bias=None, aux=None, out=None, out2=None, splits=1, force_bn=0,
-         accumulate_into=None):
+         accumulate_into=None, colsum_out=None, colsum_accumulate=False):
     """C = op(A) . op(B) with a fused epilogue; see include/ssl4p.h.  a, b: bf16 2-D (last dim contiguous).
     layout NT: a [M,K], b [N,K];  NN: a [M,K], b [K,N];  TN: a [K,M], b [K,N].
     For TN (wgrad) the result is fp32; `splits`>1 goes through a deterministic split-K reduce, optionally
@@ -112,9 +112,23 @@ def gemm(a, b, layout, epilogue, *, bias=None, aux=None, out=None, out2=None, sp
         _req(aux, f32 if epilogue == EPI_BIAS_RESIDUAL_F32 else bf16, "gemm aux", contiguous=False)
         assert aux.shape == (M, N) and aux.stride(1) == 1
         ldaux = aux.stride(0)
-    _lib.check(_gemm_launch(lib, M, N, K, layout, epilogue, a.data_ptr(), b.data_ptr(), out.data_ptr(), _ptr(out2), _ptr(bias), _ptr(aux), M, N, K,
+    part = None
+    if colsum_out is not None:
+        # EPI_DGELU_BF16 only: the epilogue also emits the column sums of C per 32-row group (Mlp.fc1 bias gradient)
+        if epilogue != EPI_DGELU_BF16:
+            raise RuntimeError("gemm: colsum_out needs the DGELU epilogue")
+        _req(colsum_out, f32, "gemm colsum_out")
+        assert colsum_out.numel() == N
+        G = (M + 31) // 32
+        part = workspace(G * N * 4, dev, "gemm_colsum").view(f32)
+    _lib.check(_gemm_launch(lib, M, N, K, layout, epilogue, a.data_ptr(), b.data_ptr(), out.data_ptr(),
+                            part.data_ptr() if part is not None else _ptr(out2), _ptr(bias), _ptr(aux), M, N, K,
                                    a.stride(0), b.stride(0), out.stride(0), out2.stride(0) if out2 is not None else 0, ldaux,
                                    layout, epilogue, 1, force_bn, _stream()), "gemm")
+    if part is not None:
+        ws2 = workspace(32 * N * 4, dev, "reduce_rows")
+        _lib.check(lib.ssl4p_reduce_rows_f32(part.data_ptr(), (M + 31) // 32, N, colsum_out.data_ptr(), int(colsum_accumulate),
+                                             ws2.data_ptr(), ws2.numel(), _stream()), "reduce_rows")
     return (out, out2) if epilogue == EPI_BIAS_GELU_BF16 else out
 
 

@@ -170,8 +170,14 @@ def block_bwd(W: Weights, sink: GradSink, pre: str, saved, dx: torch.Tensor, dxb
     hd = D // H
     # ---- MLP branch
     _wgrad(W, sink, pre + "mlp.fc2.weight", None if fc2_bias_done else pre + "mlp.fc2.bias", dxb, act)
-    dpre = ops.gemm(dxb, W.b(pre + "mlp.fc2.weight"), GEMM_NN, EPI_DGELU_BF16, aux=dact)
-    _wgrad(W, sink, pre + "mlp.fc1.weight", pre + "mlp.fc1.bias", dpre, h2)
+    b1 = pre + "mlp.fc1.bias"
+    if W.need(b1):                               # fc1 bias gradient = column sums of dpre, out of the same GEMM epilogue
+        cs, cs_acc = sink.buf(b1, W.f(b1))
+        dpre = ops.gemm(dxb, W.b(pre + "mlp.fc2.weight"), GEMM_NN, EPI_DGELU_BF16, aux=dact, colsum_out=cs, colsum_accumulate=cs_acc)
+        sink.ready(b1)
+    else:
+        dpre = ops.gemm(dxb, W.b(pre + "mlp.fc2.weight"), GEMM_NN, EPI_DGELU_BF16, aux=dact)
+    _wgrad(W, sink, pre + "mlp.fc1.weight", None, dpre, h2)
     dh2 = ops.gemm(dpre, W.b(pre + "mlp.fc1.weight"), GEMM_NN, EPI_BIAS_BF16)
     dx, dxb = _ln_bwd(W, sink, pre + "norm2.", dh2, x1, mean2, rstd2, dx, upstream_bias=pre + "attn.proj.bias")
     # ---- attention branch

@@ -65,6 +65,14 @@ def test_gemm_nn_dgrad(M, N, K, bn):
     dact = torch.randn(M, N, device=dev()).bfloat16()            # the saved gelu'(h) of the forward epilogue
     out2 = ops.gemm(dy, w, ops.GEMM_NN, ops.EPI_DGELU_BF16, aux=dact, force_bn=bn)
     assert rel_err(out2, ref * dact.float()) < 1e-2
+    # the same epilogue emits the column sums of its output (Mlp.fc1 bias gradient) with no second pass
+    cs = torch.full((N,), 7.0, device=dev())
+    out3 = ops.gemm(dy, w, ops.GEMM_NN, ops.EPI_DGELU_BF16, aux=dact, force_bn=bn, colsum_out=cs)
+    assert torch.equal(out3, out2)
+    want = (ref * dact.float()).sum(0)
+    assert rel_err(cs, want) < 2e-3, rel_err(cs, want)
+    ops.gemm(dy, w, ops.GEMM_NN, ops.EPI_DGELU_BF16, aux=dact, force_bn=bn, colsum_out=cs, colsum_accumulate=True)
+    assert rel_err(cs, 2 * want) < 2e-3
 
 
 @pytest.mark.parametrize("M,N,K", [(128, 64, 64), (768, 768, 100), (2304, 768, 394), (512, 2048, 12800), (768, 3072, 1000)])
