@@ -26,7 +26,10 @@ for tag, M, D in (("enc", Me, 768), ("dec", Md, 512)):
               (f"{tag} wproj TN", GEMM_TN, EPI_PARTIAL_F32, D, D, M)]
 cases.append(("dec pred  NT f32", GEMM_NT, EPI_BIAS_F32, Md, 768, 512))
 tot = 0.0
+only = os.environ.get("GEMM_ONLY")          # e.g. GEMM_ONLY="dec fc1,dec dfc2" (ncu captures)
 for name, layout, epi, M, N, K in cases:
+    if only and not any(name.startswith(o) for o in only.split(",")):
+        continue
     if layout == GEMM_NT:
         a = torch.randn(M, K, device=dev).bfloat16(); b = torch.randn(N, K, device=dev).bfloat16()
     elif layout == GEMM_NN:

@@ -60,6 +60,18 @@ struct SmemLayout {
 constexpr int kStageBytesPerWarp = 32 * 32 * 4;
 
 __device__ __forceinline__ float4 f4_add(float4 a, float4 b) { return make_float4(a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w); }
+__device__ __forceinline__ float4 shfl_f4(float4 v, int src) {
+    return make_float4(__shfl_sync(0xffffffffu, v.x, src), __shfl_sync(0xffffffffu, v.y, src), __shfl_sync(0xffffffffu, v.z, src),
+                       __shfl_sync(0xffffffffu, v.w, src));
+}
+// The bias of the <= 4 column chunks a warp handles in one tile (4 x 32 floats), one float4 per lane: lane 8k + j holds
+// columns [n0 + chunk0 + 64 k + 4 j, +4).  Loaded BEFORE the wait for the accumulator, so its latency is never exposed.
+__device__ __forceinline__ float4 load_bias_lane(const GemmParams& p, int n0, int chunk0) {
+    const int lane = (int)lane_id();
+    const int col = n0 + chunk0 + (lane >> 3) * 64 + (lane & 7) * 4;
+    if (p.bias == nullptr || col >= p.N) return make_float4(0.f, 0.f, 0.f, 0.f);
+    return __ldg(reinterpret_cast<const float4*>(p.bias + col));
+}
 
 // The second epilogue operand of a chunk (fp32 residual: 8 x 16 B per lane; saved gelu': 4 x 16 B per lane), in the
 // transposed (row-contiguous) mapping.  Loaded one chunk ahead so that its HBM latency hides behind the previous chunk.
@@ -90,7 +102,7 @@ __device__ __forceinline__ void load_aux(const GemmParams& p, int row_base, int 
 // stg: shared-space address of this warp's 4 KB transpose patch.
 template <int EPI>
 __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, uint32_t stg, int row_base, int col0, int split, uint32_t (&acc)[32],
-                                               const AuxRegs& aux) {
+                                               const AuxRegs& aux, const float4 bias_lane, const int kchunk) {
     const int lane = (int)lane_id();
     constexpr bool kHasBias = EPI == SSL4P_EPI_BIAS_BF16 || EPI == SSL4P_EPI_BIAS_GELU_BF16 || EPI == SSL4P_EPI_BIAS_RESIDUAL_F32 ||
                               EPI == SSL4P_EPI_BIAS_F32;
@@ -125,7 +137,7 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, uint32_t stg
         const int col = col0 + (lane & 7) * 4;
         const bool col_ok = col < p.N;                             // N % 8 == 0 (checked on the host)
         float4 b = make_float4(0.f, 0.f, 0.f, 0.f);
-        if constexpr (kHasBias) if (p.bias != nullptr && col_ok) b = __ldg(reinterpret_cast<const float4*>(p.bias + col));
+        if constexpr (kHasBias) b = shfl_f4(bias_lane, kchunk * 8 + (lane & 7));
         float* outp = reinterpret_cast<float*>(p.C) + (EPI == SSL4P_EPI_PARTIAL_F32 ? (size_t)split * p.split_stride : 0);
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
@@ -139,9 +151,9 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, uint32_t stg
         const int col = col0 + (lane & 3) * 8;
         const bool col_ok = col < p.N;
         float4 b0 = make_float4(0.f, 0.f, 0.f, 0.f), b1 = b0;
-        if constexpr (kHasBias) if (p.bias != nullptr && col_ok) {
-            b0 = __ldg(reinterpret_cast<const float4*>(p.bias + col));
-            b1 = __ldg(reinterpret_cast<const float4*>(p.bias + col + 4));
+        if constexpr (kHasBias) {
+            b0 = shfl_f4(bias_lane, kchunk * 8 + 2 * (lane & 3));
+            b1 = shfl_f4(bias_lane, kchunk * 8 + 2 * (lane & 3) + 1);
         }
         float csum[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};   // DGELU: column sums of this warp's 32 rows (fc1 bias gradient)
 #pragma unroll
@@ -327,6 +339,10 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             constexpr bool kAux = EPI == SSL4P_EPI_BIAS_RESIDUAL_F32 || EPI == SSL4P_EPI_DGELU_BF16;
             AuxRegs aux_cur, aux_nxt;
             if constexpr (kAux) load_aux<EPI>(p, row_base, n0 + chunk0, aux_cur);      // in flight while the MMAs of the tile finish
+            constexpr bool kBias = EPI == SSL4P_EPI_BIAS_BF16 || EPI == SSL4P_EPI_BIAS_GELU_BF16 || EPI == SSL4P_EPI_BIAS_RESIDUAL_F32 ||
+                                   EPI == SSL4P_EPI_BIAS_F32;
+            float4 bias_lane = make_float4(0.f, 0.f, 0.f, 0.f);
+            if constexpr (kBias) bias_lane = load_bias_lane(p, n0, chunk0);
             mbar_wait(&tmem_full[acc], acc_phase);
             tc_fence_after();
             const uint32_t stg = smem_u32(epi_stage) + (warp - 2) * kStageBytesPerWarp;
@@ -344,7 +360,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 #pragma unroll
                     for (int j = 0; j < 32; ++j) r[j] = 0u;
                 }
-                if (row_base < p.M) epilogue_chunk<EPI>(p, stg, row_base, col0, split, r, aux_cur);
+                if (row_base < p.M) epilogue_chunk<EPI>(p, stg, row_base, col0, split, r, aux_cur, bias_lane, (c - chunk0) >> 6);
                 if constexpr (kAux) aux_cur = aux_nxt;
             }
             tc_fence_before();
