@@ -288,8 +288,27 @@ __device__ __forceinline__ void store_row32_bf16(__nv_bfloat16* dst, const uint3
     }
 }
 
-// TMEM column map (512 columns): S^T [0,128)  dP^T [128,256)  dV [256,320)  dK [320,384)  dQ[qt] [384 + 64 qt, +64)
-constexpr uint32_t kColST = 0, kColDP = 128, kColDV = 256, kColDK = 320, kColDQ = 384;
+// TMEM column map (512 columns): two score buffers of a HALF block (128 keys x 64 queries), buffer u at 128 u:
+// S^T [0,64) dP^T [64,128);  then dV [256,320)  dK [320,384)  dQ[qt] [384 + 64 qt, +64).
+// Half blocks are numbered j = 0,1,2,... in issue order and use buffer j & 1, so the tensor pipe computes the scores of
+// half block j+1 (and the dV/dK/dQ updates of j-1) while the element-wise warps turn half block j into P^T / dS^T.
+constexpr uint32_t kColST = 0, kColDP = 64, kColBuf = 128, kColDV = 256, kColDK = 320, kColDQ = 384;
+
+// Position of a half block inside one work item: head of the pair, key tile, query tile, half of the query tile.
+struct HalfBlk {
+    int hh, kt, qt, h;
+    __device__ __forceinline__ static int nq(int Npad, int qt) { return min(128, Npad - qt * 128); }
+    __device__ __forceinline__ static int halves(int Npad, int qt) { return nq(Npad, qt) > 64 ? 2 : 1; }
+    __device__ __forceinline__ int nqh(int Npad) const { const int n = nq(Npad, qt); return h == 0 ? min(64, n) : n - 64; }
+    __device__ __forceinline__ void next(int Npad, int NB) {
+        if (h + 1 < halves(Npad, qt)) { ++h; return; }
+        h = 0;
+        if (++qt < NB) return;
+        qt = 0;
+        if (++kt < NB) return;
+        kt = 0; ++hh;
+    }
+};
 
 template <int HD>
 __global__ void __launch_bounds__(kAttnThreads, 1)
@@ -308,14 +327,14 @@ attention_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 12 * kTileBytes + 4096);
     uint64_t* in_full = bars;
     uint64_t* in_empty = bars + 1;
-    uint64_t* st_full = bars + 2;
-    uint64_t* pt_full = bars + 3;
-    uint64_t* blk_done = bars + 4;
-    uint64_t* dvk_full = bars + 5;
-    uint64_t* dvk_empty = bars + 6;
-    uint64_t* dq_full = bars + 7;
-    uint64_t* dq_empty = bars + 8;
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 9);
+    uint64_t* st_full = bars + 2;                                // [2] scores of half block j in TMEM buffer j & 1
+    uint64_t* pt_full = bars + 4;                                // [2] P^T / dS^T of half block j in shared memory, buffer drained
+    uint64_t* blk_done = bars + 6;                               // all tensor reads of a block's P^T / dS^T retired
+    uint64_t* dvk_full = bars + 7;
+    uint64_t* dvk_empty = bars + 8;
+    uint64_t* dq_full = bars + 9;
+    uint64_t* dq_empty = bars + 10;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 11);
 
     const int warp = threadIdx.x >> 5;
     const int lane = lane_id();
@@ -326,7 +345,8 @@ attention_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_
     if (warp == 9) {
         if (lane == 0) {
             mbar_init(in_full, 1); mbar_init(in_empty, 1);
-            mbar_init(st_full, 1); mbar_init(pt_full, 256); mbar_init(blk_done, 1);
+            for (int i = 0; i < 2; ++i) { mbar_init(&st_full[i], 1); mbar_init(&pt_full[i], 256); }
+            mbar_init(blk_done, 1);
             mbar_init(dvk_full, 1); mbar_init(dvk_empty, 256);
             mbar_init(dq_full, 1); mbar_init(dq_empty, 256);
             mbar_fence_init();
@@ -354,6 +374,18 @@ attention_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_
                     tma_load_3d(sV + i * kTileBytes, &tmQKV, in_full, 2 * HHD + sl * 64, i * 128, b);
                     tma_load_3d(sDO + i * kTileBytes, &tmDO, in_full, sl * 64, i * 128, b);
                 }
+                // the operands are single buffered: pull the next item's boxes into L2 now, so that the loads issued
+                // after this item's last MMA pay L2 latency instead of HBM latency
+                if (il + 1 < my_items) {
+                    const int item2 = item + gridDim.x;
+                    const int b2 = item2 / p.slices_per_img, sl2_ = item2 % p.slices_per_img;
+                    for (int i = 0; i < p.NB; ++i) {
+                        tma_prefetch_3d(&tmQKV, sl2_ * 64, i * 128, b2);
+                        tma_prefetch_3d(&tmQKV, HHD + sl2_ * 64, i * 128, b2);
+                        tma_prefetch_3d(&tmQKV, 2 * HHD + sl2_ * 64, i * 128, b2);
+                        tma_prefetch_3d(&tmDO, sl2_ * 64, i * 128, b2);
+                    }
+                }
             }
         }
         __syncwarp();
@@ -364,52 +396,60 @@ attention_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_
             const uint32_t sPTa = smem_u32(sPT), sDSa = smem_u32(sDS);
             const uint32_t idesc_acc = idesc_rt(128, 64, false, true);     // A K-major (P^T / dS^T rows = keys), B MN-major
             const uint32_t idesc_dq = idesc_rt(128, 64, true, true);       // A MN-major (dS^T read as [keys][queries]), B MN-major
-            int nblk = 0, nkt = 0, nhead = 0;
+            int j = 0, nkt = 0, nhead = 0;                       // half blocks, key tiles, heads issued so far (all items)
+            // scores of one half block: S^T = K[kt] Q[qt,h]^T and dP^T = V[kt] dO[qt,h]^T into TMEM buffer jj & 1
+            auto issue_scores = [&](const HalfBlk& x, int jj) {
+                const uint32_t koff = x.hh * (HD * 2);
+                const uint32_t idesc_s = idesc_rt(128, x.nqh(p.Npad), false, false);
+                const uint32_t tb = tmem_base + (uint32_t)(jj & 1) * kColBuf;
+                const uint32_t qoff = x.qt * kTileBytes + x.h * (64 * 128) + koff;
+#pragma unroll
+                for (int kk = 0; kk < HD / 16; ++kk)
+                    umma_bf16(tb + kColST, umma_smem_desc(sKa + x.kt * kTileBytes + koff + kk * 32, 16, 1024),
+                              umma_smem_desc(sQa + qoff + kk * 32, 16, 1024), idesc_s, kk > 0);
+#pragma unroll
+                for (int kk = 0; kk < HD / 16; ++kk)
+                    umma_bf16(tb + kColDP, umma_smem_desc(sVa + x.kt * kTileBytes + koff + kk * 32, 16, 1024),
+                              umma_smem_desc(sDOa + qoff + kk * 32, 16, 1024), idesc_s, kk > 0);
+                umma_commit(&st_full[jj & 1]);
+            };
             for (int il = 0; il < my_items; ++il) {
                 mbar_wait(in_full, il & 1);
                 tc_fence_after();
-                for (int hh = 0; hh < HP; ++hh, ++nhead) {
-                    const uint32_t koff = hh * (HD * 2);
-                    mbar_wait(dq_empty, (nhead & 1) ^ 1);                 // previous head's dQ has been read out
-                    tc_fence_after();
-                    for (int kt = 0; kt < p.NB; ++kt, ++nkt) {
-                        mbar_wait(dvk_empty, (nkt & 1) ^ 1);              // previous key tile's dV/dK have been read out
-                        tc_fence_after();
-                        for (int qt = 0; qt < p.NB; ++qt, ++nblk) {
-                            const int nq = min(128, p.Npad - qt * 128);
-                            const uint32_t idesc_s = idesc_rt(128, nq, false, false);
-                            // S^T = K[kt] Q[qt]^T ; dP^T = V[kt] dO[qt]^T   (TMEM columns were drained before pt_full of the previous block)
-#pragma unroll
-                            for (int kk = 0; kk < HD / 16; ++kk)
-                                umma_bf16(tmem_base + kColST, umma_smem_desc(sKa + kt * kTileBytes + koff + kk * 32, 16, 1024),
-                                          umma_smem_desc(sQa + qt * kTileBytes + koff + kk * 32, 16, 1024), idesc_s, kk > 0);
-#pragma unroll
-                            for (int kk = 0; kk < HD / 16; ++kk)
-                                umma_bf16(tmem_base + kColDP, umma_smem_desc(sVa + kt * kTileBytes + koff + kk * 32, 16, 1024),
-                                          umma_smem_desc(sDOa + qt * kTileBytes + koff + kk * 32, 16, 1024), idesc_s, kk > 0);
-                            umma_commit(st_full);
-                            mbar_wait(pt_full, nblk & 1);
-                            tc_fence_after();
-                            const int ksteps = nq >> 4;
-                            for (int ks = 0; ks < ksteps; ++ks) {
-                                const uint32_t aoff = (ks >> 2) * kTileBytes + (ks & 3) * 32;
-                                // dV[kt] += P^T dO[qt]
-                                umma_bf16(tmem_base + kColDV, umma_smem_desc(sPTa + aoff, 16, 1024),
-                                          umma_smem_desc(sDOa + qt * kTileBytes + ks * 2048, kTileBytes, 1024), idesc_acc, (qt > 0) || (ks > 0));
-                                // dK[kt] += dS^T Q[qt]
-                                umma_bf16(tmem_base + kColDK, umma_smem_desc(sDSa + aoff, 16, 1024),
-                                          umma_smem_desc(sQa + qt * kTileBytes + ks * 2048, kTileBytes, 1024), idesc_acc, (qt > 0) || (ks > 0));
-                            }
-                            // dQ[qt] += dS K[kt] : A = dS^T tile read MN-major (M = queries: 2 chunks of 64, 16 KB apart; K = keys)
-#pragma unroll
-                            for (int ks = 0; ks < 8; ++ks)
-                                umma_bf16(tmem_base + kColDQ + qt * 64, umma_smem_desc(sDSa + ks * 2048, kTileBytes, 1024),
-                                          umma_smem_desc(sKa + kt * kTileBytes + ks * 2048, kTileBytes, 1024), idesc_dq, (kt > 0) || (ks > 0));
-                            umma_commit(blk_done);
-                        }
-                        umma_commit(dvk_full);
+                HalfBlk ahead{0, 0, 0, 0};                        // next half block whose scores have not been issued
+                int ja = j;
+                for (int i = 0; i < 2 && ahead.hh < HP; ++i) { issue_scores(ahead, ja++); ahead.next(p.Npad, p.NB); }
+                for (HalfBlk c{0, 0, 0, 0}; c.hh < HP; c.next(p.Npad, p.NB), ++j) {
+                    if (c.qt == 0 && c.h == 0) {
+                        if (c.kt == 0) { mbar_wait(dq_empty, (nhead & 1) ^ 1); }      // previous head's dQ has been read out
+                        mbar_wait(dvk_empty, (nkt & 1) ^ 1);                          // previous key tile's dV/dK have been read out
                     }
-                    umma_commit(dq_full);
+                    mbar_wait(&pt_full[j & 1], (j >> 1) & 1);     // P^T / dS^T of this half block written, its TMEM buffer drained
+                    tc_fence_after();
+                    const int ks0 = c.h * 4, ks1 = ks0 + (c.nqh(p.Npad) >> 4);
+                    for (int ks = ks0; ks < ks1; ++ks) {
+                        const uint32_t aoff = (ks >> 2) * kTileBytes + (ks & 3) * 32;
+                        // dV[kt] += P^T dO[qt]
+                        umma_bf16(tmem_base + kColDV, umma_smem_desc(sPTa + aoff, 16, 1024),
+                                  umma_smem_desc(sDOa + c.qt * kTileBytes + ks * 2048, kTileBytes, 1024), idesc_acc, (c.qt > 0) || (ks > 0));
+                        // dK[kt] += dS^T Q[qt]
+                        umma_bf16(tmem_base + kColDK, umma_smem_desc(sDSa + aoff, 16, 1024),
+                                  umma_smem_desc(sQa + c.qt * kTileBytes + ks * 2048, kTileBytes, 1024), idesc_acc, (c.qt > 0) || (ks > 0));
+                    }
+                    const bool last_half = c.h + 1 == HalfBlk::halves(p.Npad, c.qt);
+                    if (last_half) {
+                        // dQ[qt] += dS K[kt] : A = dS^T tile read MN-major (M = queries: 2 chunks of 64, 16 KB apart; K = keys)
+#pragma unroll
+                        for (int ks = 0; ks < 8; ++ks)
+                            umma_bf16(tmem_base + kColDQ + c.qt * 64, umma_smem_desc(sDSa + ks * 2048, kTileBytes, 1024),
+                                      umma_smem_desc(sKa + c.kt * kTileBytes + ks * 2048, kTileBytes, 1024), idesc_dq, (c.kt > 0) || (ks > 0));
+                        umma_commit(blk_done);
+                        if (c.qt == p.NB - 1) {
+                            umma_commit(dvk_full); ++nkt;
+                            if (c.kt == p.NB - 1) { umma_commit(dq_full); ++nhead; }
+                        }
+                    }
+                    if (ahead.hh < HP) { issue_scores(ahead, ja++); ahead.next(p.Npad, p.NB); }   // refill the buffer just drained
                 }
                 umma_commit(in_empty);
             }
@@ -422,130 +462,163 @@ attention_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_
         const uint32_t tlane = tmem_base + ((uint32_t)(q4 * 32) << 16);
         const float sl2 = p.scale * kLog2eF;
         const int tid = threadIdx.x;                             // 0..255
-        int nblk = 0, nkt = 0, nhead = 0;
+        const uint32_t sLa = smem_u32(sL), sDa = smem_u32(sD), sPTa = smem_u32(sPT), sDSa = smem_u32(sDS);
+        int j = 0, nblk = 0;                                     // half blocks / blocks processed (all items)
+        int wkt = 0, whd = 0;                                    // key tiles / heads whose gradients have been written out
+        // Deferred read-out of the TMEM gradient accumulators: it is done inside the NEXT half block, between its
+        // arithmetic and its shared-memory stores, so the wait for the last dV/dK (dQ) MMAs hides behind useful work.
+        int pend_kt = -1, pend_kt_hh = 0, pend_dq_hh = -1, pend_b = 0, pend_sl = 0;
+        auto write_dvk = [&]() {                                 // dV / dK of key tile pend_kt: warps 0-3 write dV, warps 4-7 dK
+            const int key = pend_kt * 128 + row;
+            const int head = pend_sl * HP + pend_kt_hh;
+            mbar_wait(dvk_full, wkt & 1);
+            tc_fence_after();
+            const uint32_t col = half == 0 ? kColDV : kColDK;
+            __nv_bfloat16* dst = p.dqkv + (size_t)(pend_b * p.T + key) * (3 * HHD) + (half == 0 ? 2 * HHD : HHD) + head * HD;
+            if constexpr (HD == 64) {
+#pragma unroll
+                for (int h2 = 0; h2 < 2; ++h2) {
+                    uint32_t r[32];
+                    tmem_ld_32x32(tlane + col + h2 * 32, r);
+                    tmem_ld_wait();
+                    if (key < p.T) store_row32_bf16(dst + h2 * 32, r);
+                }
+            } else {
+                uint32_t r[32];
+                tmem_ld_32x32(tlane + col + pend_kt_hh * 32, r);
+                tmem_ld_wait();
+                if (key < p.T) store_row32_bf16(dst, r);
+            }
+            tc_fence_before();
+            mbar_arrive(dvk_empty);
+            ++wkt; pend_kt = -1;
+        };
+        auto write_dq = [&]() {                                  // dQ of head pend_dq_hh: warps 0-3 take query tile 0, warps 4-7 tile 1
+            const int head = pend_sl * HP + pend_dq_hh;
+            mbar_wait(dq_full, whd & 1);
+            tc_fence_after();
+            if (half < p.NB) {
+                const int q = half * 128 + row;
+                __nv_bfloat16* dst = p.dqkv + (size_t)(pend_b * p.T + q) * (3 * HHD) + head * HD;
+                if constexpr (HD == 64) {
+#pragma unroll
+                    for (int h2 = 0; h2 < 2; ++h2) {
+                        uint32_t r[32];
+                        tmem_ld_32x32(tlane + kColDQ + half * 64 + h2 * 32, r);
+                        tmem_ld_wait();
+                        if (q < p.T) store_row32_bf16(dst + h2 * 32, r);
+                    }
+                } else {
+                    uint32_t r[32];
+                    tmem_ld_32x32(tlane + kColDQ + half * 64 + pend_dq_hh * 32, r);
+                    tmem_ld_wait();
+                    if (q < p.T) store_row32_bf16(dst, r);
+                }
+            }
+            tc_fence_before();
+            mbar_arrive(dq_empty);
+            ++whd; pend_dq_hh = -1;
+        };
         for (int il = 0; il < my_items; ++il) {
             const int item = blockIdx.x + il * gridDim.x;
             const int b = item / p.slices_per_img, sl = item % p.slices_per_img;
-            // ---- per-query statistics of both heads: lse*log2e and D*scale, D = sum_d dO*O
-            named_bar_sync(1, 256);
-            for (int hh = 0; hh < HP; ++hh) {
-                const int head = sl * HP + hh;
+            // ---- per-query statistics of both heads: lse*log2e and D*scale, D = sum_d dO*O.  All global loads of the
+            // thread are issued before the first use (one memory round trip per item).
+            {
                 const int q = tid;
-                float lv = INFINITY, dv = 0.f;
+                uint4 ra[HP][HD / 8], rd[HP][HD / 8];
+                float lv[HP], dv[HP];
                 if (q < p.T) {
-                    const size_t off = ((size_t)(b * p.T + q) * p.H + head) * HD;
-                    float acc = 0.f;
 #pragma unroll
-                    for (int c = 0; c < HD / 8; ++c) {
-                        const uint4 a = *reinterpret_cast<const uint4*>(p.out + off + c * 8);
-                        const uint4 d = *reinterpret_cast<const uint4*>(p.dout + off + c * 8);
-                        const uint32_t aw[4] = {a.x, a.y, a.z, a.w}, dw[4] = {d.x, d.y, d.z, d.w};
+                    for (int hh = 0; hh < HP; ++hh) {
+                        const size_t off = ((size_t)(b * p.T + q) * p.H + sl * HP + hh) * HD;
 #pragma unroll
-                        for (int j = 0; j < 4; ++j) { const float2 x = unpack_bf16(aw[j]), y = unpack_bf16(dw[j]); acc += x.x * y.x + x.y * y.y; }
+                        for (int c = 0; c < HD / 8; ++c) { ra[hh][c] = ldg_v4(p.out + off + c * 8); rd[hh][c] = ldg_v4(p.dout + off + c * 8); }
+                        lv[hh] = __ldg(p.lse + ((size_t)b * p.H + sl * HP + hh) * p.T + q) * kLog2eF;
                     }
-                    dv = acc * p.scale;
-                    lv = p.lse[((size_t)b * p.H + head) * p.T + q] * kLog2eF;
+#pragma unroll
+                    for (int hh = 0; hh < HP; ++hh) {
+                        float acc = 0.f;
+#pragma unroll
+                        for (int c = 0; c < HD / 8; ++c) {
+                            const uint32_t aw[4] = {ra[hh][c].x, ra[hh][c].y, ra[hh][c].z, ra[hh][c].w};
+                            const uint32_t dw[4] = {rd[hh][c].x, rd[hh][c].y, rd[hh][c].z, rd[hh][c].w};
+#pragma unroll
+                            for (int u = 0; u < 4; ++u) { const float2 x = unpack_bf16(aw[u]), y = unpack_bf16(dw[u]); acc += x.x * y.x + x.y * y.y; }
+                        }
+                        dv[hh] = acc * p.scale;
+                    }
+                } else {
+#pragma unroll
+                    for (int hh = 0; hh < HP; ++hh) { lv[hh] = INFINITY; dv[hh] = 0.f; }
                 }
-                sL[hh * 256 + q] = lv;
-                sD[hh * 256 + q] = dv;
+                named_bar_sync(1, 256);                          // every thread is done reading the previous item's statistics
+#pragma unroll
+                for (int hh = 0; hh < HP; ++hh) { sts32f(sLa + (hh * 256 + q) * 4, lv[hh]); sts32f(sDa + (hh * 256 + q) * 4, dv[hh]); }
+                named_bar_sync(1, 256);
             }
-            named_bar_sync(1, 256);
 
-            for (int hh = 0; hh < HP; ++hh, ++nhead) {
-                const int head = sl * HP + hh;
-                const float* L = sL + hh * 256;
-                const float* Dq = sD + hh * 256;
-                for (int kt = 0; kt < p.NB; ++kt, ++nkt) {
+            for (int hh = 0; hh < HP; ++hh) {
+                for (int kt = 0; kt < p.NB; ++kt) {
                     const int key = kt * 128 + row;
                     const bool key_ok = key < p.T;
                     for (int qt = 0; qt < p.NB; ++qt, ++nblk) {
                         const int nq = min(128, p.Npad - qt * 128);
-                        mbar_wait(st_full, nblk & 1);
-                        tc_fence_after();
-                        if (nblk > 0) mbar_wait(blk_done, (nblk - 1) & 1);     // P^T / dS^T tiles of the previous block consumed
-#pragma unroll 1
-                        for (int cc = 0; cc < 2; ++cc) {
-                            const int c = half * 64 + cc * 32;                  // column (query) offset inside the block
-                            if (c >= nq) break;
-                            uint32_t rs[32], rd[32];
-                            tmem_ld_32x32(tlane + kColST + c, rs);
-                            tmem_ld_32x32(tlane + kColDP + c, rd);
-                            tmem_ld_wait();
-                            const int q0 = qt * 128 + c;
+                        const int nh = nq > 64 ? 2 : 1;
+                        for (int h = 0; h < nh; ++h, ++j) {
+                            const int nqh = h == 0 ? min(64, nq) : nq - 64;
+                            const int c = half * 32;                            // this warp's 32 query columns of the half block
+                            const bool active = c < nqh;
                             uint32_t pw[16], dw[16];
-#pragma unroll
-                            for (int j = 0; j < 32; j += 2) {
-                                const float2 l2 = *reinterpret_cast<const float2*>(L + q0 + j);
-                                const float2 d2 = *reinterpret_cast<const float2*>(Dq + q0 + j);
-                                float p0 = fast_exp2(fmaf(__uint_as_float(rs[j]), sl2, -l2.x));
-                                float p1 = fast_exp2(fmaf(__uint_as_float(rs[j + 1]), sl2, -l2.y));
-                                float e0 = p0 * fmaf(__uint_as_float(rd[j]), p.scale, -d2.x);
-                                float e1 = p1 * fmaf(__uint_as_float(rd[j + 1]), p.scale, -d2.y);
-                                if (!key_ok || q0 + j >= p.T) { p0 = 0.f; e0 = 0.f; }
-                                if (!key_ok || q0 + j + 1 >= p.T) { p1 = 0.f; e1 = 0.f; }
-                                pw[j >> 1] = pack_bf16(p0, p1);
-                                dw[j >> 1] = pack_bf16(e0, e1);
-                            }
-                            const uint32_t tile = (uint32_t)(c >> 6) * kTileBytes;
-                            const int sub = (c & 63) >> 3;
-#pragma unroll
-                            for (int i = 0; i < 4; ++i) {
-                                const uint32_t off = tile + sw128_off(row, sub + i);
-                                *reinterpret_cast<uint4*>(sPT + off) = make_uint4(pw[4 * i], pw[4 * i + 1], pw[4 * i + 2], pw[4 * i + 3]);
-                                *reinterpret_cast<uint4*>(sDS + off) = make_uint4(dw[4 * i], dw[4 * i + 1], dw[4 * i + 2], dw[4 * i + 3]);
-                            }
-                        }
-                        fence_proxy_async();
-                        tc_fence_before();
-                        mbar_arrive(pt_full);
-                    }
-                    // ---- dV / dK of this key tile: warps 0-3 write dV, warps 4-7 write dK
-                    mbar_wait(dvk_full, nkt & 1);
-                    tc_fence_after();
-                    {
-                        const uint32_t col = half == 0 ? kColDV : kColDK;
-                        __nv_bfloat16* dst = p.dqkv + (size_t)(b * p.T + key) * (3 * HHD) + (half == 0 ? 2 * HHD : HHD) + head * HD;
-                        if constexpr (HD == 64) {
-#pragma unroll
-                            for (int h2 = 0; h2 < 2; ++h2) {
-                                uint32_t r[32];
-                                tmem_ld_32x32(tlane + col + h2 * 32, r);
+                            mbar_wait(&st_full[j & 1], (j >> 1) & 1);
+                            tc_fence_after();
+                            if (active) {
+                                uint32_t rs[32], rd[32];
+                                const uint32_t tb = tlane + (uint32_t)(j & 1) * kColBuf;
+                                tmem_ld_32x32(tb + kColST + c, rs);
+                                tmem_ld_32x32(tb + kColDP + c, rd);
+                                const int q0 = qt * 128 + h * 64 + c;
+                                const uint32_t la = sLa + (hh * 256 + q0) * 4, da = sDa + (hh * 256 + q0) * 4;
                                 tmem_ld_wait();
-                                if (key_ok) store_row32_bf16(dst + h2 * 32, r);
-                            }
-                        } else {
-                            uint32_t r[32];
-                            tmem_ld_32x32(tlane + col + hh * 32, r);
-                            tmem_ld_wait();
-                            if (key_ok) store_row32_bf16(dst, r);
-                        }
-                    }
-                    tc_fence_before();
-                    mbar_arrive(dvk_empty);
-                }
-                // ---- dQ of this head: warps 0-3 take query tile 0, warps 4-7 query tile 1
-                mbar_wait(dq_full, nhead & 1);
-                tc_fence_after();
-                if (half < p.NB) {
-                    const int q = half * 128 + row;
-                    __nv_bfloat16* dst = p.dqkv + (size_t)(b * p.T + q) * (3 * HHD) + head * HD;
-                    if constexpr (HD == 64) {
 #pragma unroll
-                        for (int h2 = 0; h2 < 2; ++h2) {
-                            uint32_t r[32];
-                            tmem_ld_32x32(tlane + kColDQ + half * 64 + h2 * 32, r);
-                            tmem_ld_wait();
-                            if (q < p.T) store_row32_bf16(dst + h2 * 32, r);
+                                for (int jj = 0; jj < 32; jj += 4) {
+                                    const float4 l4 = lds_v4f(la + jj * 4);      // warp-uniform address: one broadcast wavefront
+                                    const float4 d4 = lds_v4f(da + jj * 4);
+                                    const float lq[4] = {l4.x, l4.y, l4.z, l4.w}, dq_[4] = {d4.x, d4.y, d4.z, d4.w};
+                                    float pv[4], ev[4];
+#pragma unroll
+                                    for (int u = 0; u < 4; ++u) {
+                                        pv[u] = fast_exp2(fmaf(__uint_as_float(rs[jj + u]), sl2, -lq[u]));
+                                        ev[u] = pv[u] * fmaf(__uint_as_float(rd[jj + u]), p.scale, -dq_[u]);
+                                        if (!key_ok || q0 + jj + u >= p.T) { pv[u] = 0.f; ev[u] = 0.f; }
+                                    }
+                                    pw[(jj >> 1)] = pack_bf16(pv[0], pv[1]); pw[(jj >> 1) + 1] = pack_bf16(pv[2], pv[3]);
+                                    dw[(jj >> 1)] = pack_bf16(ev[0], ev[1]); dw[(jj >> 1) + 1] = pack_bf16(ev[2], ev[3]);
+                                }
+                            }
+                            if (pend_kt >= 0) write_dvk();
+                            if (pend_dq_hh >= 0) write_dq();
+                            // the P^T / dS^T tiles are single buffered: the tensor reads of the previous block must have retired
+                            if (h == 0 && nblk > 0) mbar_wait(blk_done, (nblk - 1) & 1);
+                            if (active) {
+                                const uint32_t tile = (uint32_t)h * kTileBytes;
+                                const int sub = c >> 3;
+#pragma unroll
+                                for (int i = 0; i < 4; ++i) {
+                                    const uint32_t off = tile + sw128_off(row, sub + i);
+                                    sts_v4(sPTa + off, pw[4 * i], pw[4 * i + 1], pw[4 * i + 2], pw[4 * i + 3]);
+                                    sts_v4(sDSa + off, dw[4 * i], dw[4 * i + 1], dw[4 * i + 2], dw[4 * i + 3]);
+                                }
+                            }
+                            fence_proxy_async();
+                            tc_fence_before();
+                            mbar_arrive(&pt_full[j & 1]);
                         }
-                    } else {
-                        uint32_t r[32];
-                        tmem_ld_32x32(tlane + kColDQ + half * 64 + hh * 32, r);
-                        tmem_ld_wait();
-                        if (q < p.T) store_row32_bf16(dst, r);
                     }
+                    pend_kt = kt; pend_kt_hh = hh; pend_b = b; pend_sl = sl;
                 }
-                tc_fence_before();
-                mbar_arrive(dq_empty);
+                pend_dq_hh = hh;
+                if (hh == HP - 1) { write_dvk(); write_dq(); }   // last head of the item: nothing left to hide behind
             }
         }
     }
