@@ -104,8 +104,6 @@ int ssl4p_attention_bwd(const void* qkv, const void* out, const void* dout, cons
                         int B, int T, int H, int hd, float scale, void* stream);
 /* Same contract on warp-level mma.sync (the first revision of the kernels; kept as an independent on-device
  * cross-check of the tcgen05 kernels in tests, T <= 208). */
-/* first-generation tcgen05 forward (unpipelined; kept for A/B timing in scripts/attn_bench.py) */
-int ssl4p_attention_fwd_tc1(const void* qkv, void* out, float* lse, int B, int T, int H, int hd, float scale, void* stream);
 int ssl4p_attention_fwd_mma(const void* qkv, void* out, float* lse, int B, int T, int H, int hd, float scale, void* stream);
 int ssl4p_attention_bwd_mma(const void* qkv, const void* out, const void* dout, const float* lse, void* dqkv,
                             int B, int T, int H, int hd, float scale, void* stream);

@@ -11,7 +11,7 @@ flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
 for (B, T, H, hd) in [(256, 197, 16, 32), (256, 50, 12, 64), (128, 197, 12, 64)]:
     qkv = torch.randn(B * T, 3 * H * hd, device=dev).bfloat16()
     do = torch.randn(B * T, H * hd, device=dev).bfloat16()
-    for impl in ("tcgen05", "tc1", "mma"):
+    for impl in ("tcgen05", "mma"):
         tf, tb = [], []
         for _ in range(reps):
             flush.zero_()

@@ -22,6 +22,7 @@
 //   Deterministic (no atomics).
 #include "attn_common.cuh"
 #include <mutex>
+#include <stdlib.h>
 #include <unordered_map>
 
 namespace ssl4p {
@@ -29,6 +30,8 @@ namespace ssl4p {
 struct AttnFwdParams {
     int T, H, items, slices_per_img;           // slices_per_img = H*hd/64
     int Npad, NB, NKB;                         // keys padded to 16; query tiles of 128; key boxes of 128 rows
+    int sep;                                   // 1: O has its own TMEM columns (deferred read-out), 0: O overwrites S
+    int s_stride;                              // sep: TMEM columns between the two S buffers
     float scale;
     __nv_bfloat16* out;                        // [B*T, H*hd]
     float* lse;                                // [B, H, T]
@@ -37,6 +40,12 @@ struct AttnFwdParams {
 // =========================================================================================================
 // forward
 // =========================================================================================================
+// Two softmax warpgroups, each a chain  S = Q K^T -> softmax -> P -> O = P V  over its own tiles (g = wg, wg+2, ...).
+// TMEM plan `sep` (2 * round32(Npad) + 2 * hd <= 512, e.g. the 197-token decoder at hd 32): S_w at w * s_stride, O_w at
+// 2 * s_stride + w * hd.  O no longer aliases S, so the issuer starts S of the chain's NEXT tile the moment P of the
+// current one is complete (before P V), and the warpgroup reads O of tile g out only after the exponentials of tile
+// g+2: both round trips (commit -> mbarrier -> wake-up) that used to sit between two tiles are hidden.
+// Otherwise (`sep` = 0) O is accumulated over the dead S columns and read out before the next S may be issued.
 template <int HD>
 __global__ void __launch_bounds__(kAttnThreads, 1)
 attention_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnFwdParams p) {
@@ -48,24 +57,27 @@ attention_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnFwd
     uint8_t* sV = smem + 4 * kTileBytes;                         // 2 tiles
     uint8_t* sP = smem + 6 * kTileBytes;                         // 2 warpgroups x 4 key chunks x 16 KB
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 14 * kTileBytes);
-    uint64_t* qkv_full = bars;                                   // [1]
-    uint64_t* qkv_empty = bars + 1;                              // [1]
+    uint64_t* qk_full = bars;                                    // Q and K of the item landed
+    uint64_t* qk_empty = bars + 1;                               // all S MMAs of the item retired: Q/K may be overwritten
+    uint64_t* v_full = bars + 10;                                // V of the item landed
+    uint64_t* v_empty = bars + 11;                               // all P V MMAs of the item retired
     uint64_t* s_full = bars + 2;                                 // [2]
     uint64_t* p_full = bars + 4;                                 // [2]
     uint64_t* o_full = bars + 6;                                 // [2]
     uint64_t* s_empty = bars + 8;                                // [2]
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 10);
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 12);
 
     const int warp = threadIdx.x >> 5;
     const int lane = lane_id();
     const int NT = HP * p.NB;                                    // tiles per item
     const int my_items = p.items > (int)blockIdx.x ? (p.items - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
+    const bool sep = p.sep != 0;
 
     if (warp == 8 && lane == 0) tma_prefetch_desc(&tmQKV);
     if (warp == 9) {
         if (lane == 0) {
-            mbar_init(qkv_full, 1);
-            mbar_init(qkv_empty, NT);
+            mbar_init(qk_full, 1); mbar_init(qk_empty, NT);
+            mbar_init(v_full, 1); mbar_init(v_empty, NT);
             for (int i = 0; i < 2; ++i) {
                 mbar_init(&s_full[i], 1); mbar_init(&p_full[i], 128); mbar_init(&o_full[i], 1); mbar_init(&s_empty[i], 128);
             }
@@ -87,12 +99,23 @@ attention_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnFwd
             for (int il = 0; il < my_items; ++il) {
                 const int item = blockIdx.x + il * gridDim.x;
                 const int b = item / p.slices_per_img, sl = item % p.slices_per_img;
-                mbar_wait(qkv_empty, (il & 1) ^ 1);
-                mbar_expect_tx(qkv_full, (uint32_t)(p.NB + 2 * p.NKB) * kTileBytes);
-                for (int i = 0; i < p.NB; ++i) tma_load_3d(sQ + i * kTileBytes, &tmQKV, qkv_full, sl * 64, i * 128, b);
-                for (int i = 0; i < p.NKB; ++i) {
-                    tma_load_3d(sK + i * kTileBytes, &tmQKV, qkv_full, HHD + sl * 64, i * 128, b);
-                    tma_load_3d(sV + i * kTileBytes, &tmQKV, qkv_full, 2 * HHD + sl * 64, i * 128, b);
+                // Q/K are dead once the item's S MMAs have retired (about half way through the item), V after its last
+                // P V: two barrier pairs, so the next item's Q/K arrive while this item is still in its softmax
+                mbar_wait(qk_empty, (il & 1) ^ 1);
+                mbar_expect_tx(qk_full, (uint32_t)(p.NB + p.NKB) * kTileBytes);
+                for (int i = 0; i < p.NB; ++i) tma_load_3d(sQ + i * kTileBytes, &tmQKV, qk_full, sl * 64, i * 128, b);
+                for (int i = 0; i < p.NKB; ++i) tma_load_3d(sK + i * kTileBytes, &tmQKV, qk_full, HHD + sl * 64, i * 128, b);
+                mbar_wait(v_empty, (il & 1) ^ 1);
+                mbar_expect_tx(v_full, (uint32_t)p.NKB * kTileBytes);
+                for (int i = 0; i < p.NKB; ++i) tma_load_3d(sV + i * kTileBytes, &tmQKV, v_full, 2 * HHD + sl * 64, i * 128, b);
+                if (il + 1 < my_items) {                          // single-buffered operands: warm L2 with the next item's boxes
+                    const int item2 = item + gridDim.x;
+                    const int b2 = item2 / p.slices_per_img, s2 = item2 % p.slices_per_img;
+                    for (int i = 0; i < p.NKB; ++i) {
+                        tma_prefetch_3d(&tmQKV, s2 * 64, i * 128, b2);
+                        tma_prefetch_3d(&tmQKV, HHD + s2 * 64, i * 128, b2);
+                        tma_prefetch_3d(&tmQKV, 2 * HHD + s2 * 64, i * 128, b2);
+                    }
                 }
             }
         }
@@ -101,45 +124,57 @@ attention_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnFwd
         // ===================== MMA issuer (one thread, two chains) =====================
         if (lane == 0) {
             const uint32_t idesc_s = idesc_rt(128, p.Npad, false, false);
-            const uint32_t idesc_o = idesc_rt(128, 64, false, true);
+            const uint32_t idesc_o = idesc_rt(128, HD, false, true);   // hd 32: N = 32, half of a 64-wide MN-major swizzle atom
             const int total = my_items * NT;
-            int nxt[2] = {0, 1};
-            int stage[2] = {0, 0};
-            int loaded = 0;                                       // completions of qkv_full observed so far (in order)
+            int nxt[2] = {0, 1};                                  // tile whose P V is pending, per chain
+            int s_done[2] = {0, 0};                               // tiles of the chain whose S has been issued
+            int loaded = 0, loaded_v = 0;                         // completions of qk_full / v_full observed so far (in order)
             const uint32_t sQa = smem_u32(sQ), sKa = smem_u32(sK), sVa = smem_u32(sV), sPa = smem_u32(sP);
+            const uint32_t s_col[2] = {0u, sep ? (uint32_t)p.s_stride : 256u};
+            const uint32_t o_col[2] = {sep ? 2u * p.s_stride : 0u, sep ? 2u * p.s_stride + HD : 256u};
+            // S of tile u (index inside chain w) if its operands have landed and the S columns are free
+            auto try_issue_s = [&](int w) -> bool {
+                const int u = s_done[w], g = 2 * u + w;
+                if (g >= total) return false;
+                const int il = g / NT, t = g - il * NT;
+                if (loaded <= il && mbar_test_wait(qk_full, loaded & 1)) ++loaded;    // the barrier is at most one phase ahead
+                if (loaded <= il) return false;
+                if (!sep && !mbar_test_wait(&s_empty[w], (u & 1) ^ 1)) return false;  // alias plan: O of the previous tile read out
+                tc_fence_after();
+                const int hh = t / p.NB, mb = t - hh * p.NB;
+                const uint32_t a0 = sQa + mb * kTileBytes + hh * (HD * 2);
+                const uint32_t b0 = sKa + hh * (HD * 2);
+#pragma unroll
+                for (int kk = 0; kk < HD / 16; ++kk)
+                    umma_bf16(tmem_base + s_col[w], umma_smem_desc(a0 + kk * 32, 16, 1024), umma_smem_desc(b0 + kk * 32, 16, 1024), idesc_s, kk > 0);
+                umma_commit(&s_full[w]);
+                umma_commit(qk_empty);
+                ++s_done[w];
+                return true;
+            };
             while (nxt[0] < total || nxt[1] < total) {
 #pragma unroll
                 for (int w = 0; w < 2; ++w) {
                     const int g = nxt[w];
                     if (g >= total) continue;
                     const int u = g >> 1, il = g / NT, t = g - il * NT;
-                    const uint32_t tmem_d = tmem_base + (uint32_t)w * 256u;
-                    if (stage[w] == 0) {
-                        if (loaded <= il && mbar_try_wait(qkv_full, loaded & 1)) ++loaded;   // the barrier is at most one phase ahead
-                        if (loaded <= il) continue;
-                        if (!mbar_try_wait(&s_empty[w], (u & 1) ^ 1)) continue;
-                        tc_fence_after();
-                        const int hh = t / p.NB, mb = t - hh * p.NB;
-                        const uint32_t a0 = sQa + mb * kTileBytes + hh * (HD * 2);
-                        const uint32_t b0 = sKa + hh * (HD * 2);
-#pragma unroll
-                        for (int kk = 0; kk < HD / 16; ++kk)
-                            umma_bf16(tmem_d, umma_smem_desc(a0 + kk * 32, 16, 1024), umma_smem_desc(b0 + kk * 32, 16, 1024), idesc_s, kk > 0);
-                        umma_commit(&s_full[w]);
-                        stage[w] = 1;
-                    } else {
-                        if (!mbar_try_wait(&p_full[w], u & 1)) continue;
-                        tc_fence_after();
-                        const uint32_t pa = sPa + (uint32_t)w * 4u * kTileBytes;
-                        const int ksteps = p.Npad >> 4;
-                        for (int ks = 0; ks < ksteps; ++ks)
-                            umma_bf16(tmem_d, umma_smem_desc(pa + (ks >> 2) * kTileBytes + (ks & 3) * 32, 16, 1024),
-                                      umma_smem_desc(sVa + ks * 2048, kTileBytes, 1024), idesc_o, ks > 0);
-                        umma_commit(&o_full[w]);
-                        umma_commit(qkv_empty);
-                        stage[w] = 0;
-                        nxt[w] = g + 2;
-                    }
+                    if (s_done[w] <= u) { try_issue_s(w); continue; }                 // S(g) itself not issued yet
+                    if (!mbar_test_wait(&p_full[w], u & 1)) continue;
+                    tc_fence_after();
+                    // sep plan: P(g) complete means S(g) has been consumed -> the chain's next S goes first, then P V
+                    if (sep && s_done[w] == u + 1) try_issue_s(w);
+                    if (loaded_v <= il && mbar_test_wait(v_full, loaded_v & 1)) ++loaded_v;
+                    if (loaded_v <= il) continue;                 // V not there yet: come back (p_full stays complete)
+                    tc_fence_after();
+                    const uint32_t pa = sPa + (uint32_t)w * 4u * kTileBytes;
+                    const int ksteps = p.Npad >> 4;
+                    const uint32_t voff = (HD == 32) ? (uint32_t)(t / p.NB) * 64u : 0u;   // head of the pair: +64 B inside the 128 B row
+                    for (int ks = 0; ks < ksteps; ++ks)
+                        umma_bf16(tmem_base + o_col[w], umma_smem_desc(pa + (ks >> 2) * kTileBytes + (ks & 3) * 32, 16, 1024),
+                                  umma_smem_desc(sVa + ks * 2048 + voff, kTileBytes, 1024), idesc_o, ks > 0);
+                    umma_commit(&o_full[w]);
+                    umma_commit(v_empty);
+                    nxt[w] = g + 2;
                 }
             }
         }
@@ -148,9 +183,34 @@ attention_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnFwd
         // ===================== softmax warpgroups =====================
         const int wg = warp >> 2, q4 = warp & 3;
         const int row = q4 * 32 + lane;
-        const uint32_t taddr = tmem_base + ((uint32_t)(q4 * 32) << 16) + (uint32_t)wg * 256u;
-        uint8_t* pw = sP + wg * 4 * kTileBytes;
+        const uint32_t tlanes = tmem_base + ((uint32_t)(q4 * 32) << 16);
+        const uint32_t taddr = tlanes + (sep ? (uint32_t)(wg * p.s_stride) : (uint32_t)wg * 256u);            // S of this chain
+        const uint32_t oaddr = tlanes + (sep ? (uint32_t)(2 * p.s_stride + wg * HD) : (uint32_t)wg * 256u);   // O of this chain
+        const uint32_t pw = smem_u32(sP) + wg * 4 * kTileBytes;
         const float sl2 = p.scale * kLog2eF;
+        // O / rowsum -> bf16 row of `out`, log-sum-exp of the row
+        auto read_out = [&](int b, int head, int qrow, float mx, float sum) {
+            const float inv = 1.0f / sum;
+#pragma unroll
+            for (int hf = 0; hf < HD / 32; ++hf) {
+                uint32_t r[32];
+                tmem_ld_32x32(oaddr + hf * 32, r);
+                tmem_ld_wait();
+                if (qrow < p.T) {
+                    __nv_bfloat16* dst = p.out + ((size_t)(b * p.T + qrow) * p.H + head) * HD + hf * 32;
+#pragma unroll
+                    for (int i = 0; i < 4; ++i)
+                        stg_v4(dst + 8 * i,
+                               pack_bf16(__uint_as_float(r[8 * i + 0]) * inv, __uint_as_float(r[8 * i + 1]) * inv),
+                               pack_bf16(__uint_as_float(r[8 * i + 2]) * inv, __uint_as_float(r[8 * i + 3]) * inv),
+                               pack_bf16(__uint_as_float(r[8 * i + 4]) * inv, __uint_as_float(r[8 * i + 5]) * inv),
+                               pack_bf16(__uint_as_float(r[8 * i + 6]) * inv, __uint_as_float(r[8 * i + 7]) * inv));
+                }
+            }
+            if (qrow < p.T) p.lse[((size_t)b * p.H + head) * p.T + qrow] = mx * p.scale + __logf(sum);
+        };
+        int pb = 0, phead = 0, pqrow = 0, pu = -1;               // tile whose O is still in TMEM (sep plan)
+        float pmx = 0.f, psum = 1.f;
         for (int il = 0; il < my_items; ++il) {
             const int item = blockIdx.x + il * gridDim.x;
             const int b = item / p.slices_per_img, sl = item % p.slices_per_img;
@@ -163,20 +223,35 @@ attention_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnFwd
                 const int qrow = mb * 128 + row;
                 mbar_wait(&s_full[wg], u & 1);
                 tc_fence_after();
-                // ---- pass 1: row maximum over the valid keys
+                // ---- pass 1: row maximum over the valid keys (the TMEM load of chunk c+1 is in flight during the max of chunk c)
                 float mx = -INFINITY;
-                for (int c = 0; c < p.Npad; c += 32) {
-                    uint32_t r[32];
-                    tmem_ld_32x32(taddr + c, r);
-                    tmem_ld_wait();
-                    if (c + 32 <= p.T) {
+                {
+                    uint32_t ra[32], rb[32];
+                    tmem_ld_32x32(taddr, ra);
+                    for (int c = 0; c < p.Npad; c += 64) {
+                        tmem_ld_wait();
+                        if (c + 32 < p.Npad) tmem_ld_32x32(taddr + c + 32, rb);
+                        if (c + 32 <= p.T) {
 #pragma unroll
-                        for (int j = 0; j < 32; ++j) mx = fmaxf(mx, __uint_as_float(r[j]));
-                    } else {
+                            for (int jj = 0; jj < 32; ++jj) mx = fmaxf(mx, __uint_as_float(ra[jj]));
+                        } else {
 #pragma unroll
-                        for (int j = 0; j < 32; ++j) if (c + j < p.T) mx = fmaxf(mx, __uint_as_float(r[j]));
+                            for (int jj = 0; jj < 32; ++jj) if (c + jj < p.T) mx = fmaxf(mx, __uint_as_float(ra[jj]));
+                        }
+                        if (c + 32 >= p.Npad) break;
+                        tmem_ld_wait();
+                        if (c + 64 < p.Npad) tmem_ld_32x32(taddr + c + 64, ra);
+                        if (c + 64 <= p.T) {
+#pragma unroll
+                            for (int jj = 0; jj < 32; ++jj) mx = fmaxf(mx, __uint_as_float(rb[jj]));
+                        } else {
+#pragma unroll
+                            for (int jj = 0; jj < 32; ++jj) if (c + 32 + jj < p.T) mx = fmaxf(mx, __uint_as_float(rb[jj]));
+                        }
                     }
                 }
+                // sep plan: the P buffer of this chain is still being read by P V of the previous tile until o_full
+                if (sep && pu >= 0) { mbar_wait(&o_full[wg], pu & 1); tc_fence_after(); }
                 // ---- pass 2: p = exp2((s - max) * scale * log2e), row sum, bf16 P into the SW128 K-major tile
                 const float msl = mx * sl2;
                 float sum = 0.f;
@@ -187,70 +262,44 @@ attention_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnFwd
                     float e[32];
                     if (c + 32 <= p.T) {
 #pragma unroll
-                        for (int j = 0; j < 32; ++j) e[j] = fast_exp2(fmaf(__uint_as_float(r[j]), sl2, -msl));
+                        for (int jj = 0; jj < 32; ++jj) e[jj] = fast_exp2(fmaf(__uint_as_float(r[jj]), sl2, -msl));
                     } else {
 #pragma unroll
-                        for (int j = 0; j < 32; ++j) e[j] = (c + j < p.T) ? fast_exp2(fmaf(__uint_as_float(r[j]), sl2, -msl)) : 0.f;
+                        for (int jj = 0; jj < 32; ++jj) e[jj] = (c + jj < p.T) ? fast_exp2(fmaf(__uint_as_float(r[jj]), sl2, -msl)) : 0.f;
                     }
 #pragma unroll
-                    for (int j = 0; j < 32; ++j) sum += e[j];
-                    uint8_t* tile = pw + (c >> 6) * kTileBytes;
+                    for (int jj = 0; jj < 32; ++jj) sum += e[jj];
+                    const uint32_t tile = pw + (c >> 6) * kTileBytes;
                     const int sub = (c & 63) >> 3;
 #pragma unroll
-                    for (int i = 0; i < 4; ++i) {
-                        uint4 o;
-                        o.x = pack_bf16(e[8 * i + 0], e[8 * i + 1]); o.y = pack_bf16(e[8 * i + 2], e[8 * i + 3]);
-                        o.z = pack_bf16(e[8 * i + 4], e[8 * i + 5]); o.w = pack_bf16(e[8 * i + 6], e[8 * i + 7]);
-                        *reinterpret_cast<uint4*>(tile + sw128_off(row, sub + i)) = o;
-                    }
+                    for (int i = 0; i < 4; ++i)
+                        sts_v4(tile + sw128_off(row, sub + i), pack_bf16(e[8 * i + 0], e[8 * i + 1]), pack_bf16(e[8 * i + 2], e[8 * i + 3]),
+                               pack_bf16(e[8 * i + 4], e[8 * i + 5]), pack_bf16(e[8 * i + 6], e[8 * i + 7]));
                 }
-                fence_proxy_async();                              // generic-proxy smem writes -> visible to the tensor core
-                tc_fence_before();
-                mbar_arrive(&p_full[wg]);
-                // ---- epilogue: O / rowsum -> bf16
-                mbar_wait(&o_full[wg], u & 1);
-                tc_fence_after();
-                const float inv = 1.0f / sum;
-                if constexpr (HD == 64) {
-#pragma unroll
-                    for (int half = 0; half < 2; ++half) {
-                        uint32_t r[32];
-                        tmem_ld_32x32(taddr + half * 32, r);
-                        tmem_ld_wait();
-                        if (qrow < p.T) {
-                            __nv_bfloat16* dst = p.out + ((size_t)(b * p.T + qrow) * p.H + head) * HD + half * 32;
-#pragma unroll
-                            for (int i = 0; i < 4; ++i) {
-                                uint4 o;
-                                o.x = pack_bf16(__uint_as_float(r[8 * i + 0]) * inv, __uint_as_float(r[8 * i + 1]) * inv);
-                                o.y = pack_bf16(__uint_as_float(r[8 * i + 2]) * inv, __uint_as_float(r[8 * i + 3]) * inv);
-                                o.z = pack_bf16(__uint_as_float(r[8 * i + 4]) * inv, __uint_as_float(r[8 * i + 5]) * inv);
-                                o.w = pack_bf16(__uint_as_float(r[8 * i + 6]) * inv, __uint_as_float(r[8 * i + 7]) * inv);
-                                *reinterpret_cast<uint4*>(dst + 8 * i) = o;
-                            }
-                        }
-                    }
+                if (sep) {
+                    // O of the chain's previous tile (complete: o_full was observed above) leaves TMEM before P V of this
+                    // tile may overwrite it, i.e. before p_full
+                    if (pu >= 0) read_out(pb, phead, pqrow, pmx, psum);
+                    fence_proxy_async();                          // generic-proxy smem writes -> visible to the tensor core
+                    tc_fence_before();
+                    mbar_arrive(&p_full[wg]);
+                    pb = b; phead = head; pqrow = qrow; pmx = mx; psum = sum; pu = u;
                 } else {
-                    uint32_t r[32];
-                    tmem_ld_32x32(taddr + hh * 32, r);
-                    tmem_ld_wait();
-                    if (qrow < p.T) {
-                        __nv_bfloat16* dst = p.out + ((size_t)(b * p.T + qrow) * p.H + head) * HD;
-#pragma unroll
-                        for (int i = 0; i < 4; ++i) {
-                            uint4 o;
-                            o.x = pack_bf16(__uint_as_float(r[8 * i + 0]) * inv, __uint_as_float(r[8 * i + 1]) * inv);
-                            o.y = pack_bf16(__uint_as_float(r[8 * i + 2]) * inv, __uint_as_float(r[8 * i + 3]) * inv);
-                            o.z = pack_bf16(__uint_as_float(r[8 * i + 4]) * inv, __uint_as_float(r[8 * i + 5]) * inv);
-                            o.w = pack_bf16(__uint_as_float(r[8 * i + 6]) * inv, __uint_as_float(r[8 * i + 7]) * inv);
-                            *reinterpret_cast<uint4*>(dst + 8 * i) = o;
-                        }
-                    }
+                    fence_proxy_async();
+                    tc_fence_before();
+                    mbar_arrive(&p_full[wg]);
+                    mbar_wait(&o_full[wg], u & 1);
+                    tc_fence_after();
+                    read_out(b, head, qrow, mx, sum);
+                    tc_fence_before();
+                    mbar_arrive(&s_empty[wg]);
                 }
-                if (qrow < p.T) p.lse[((size_t)b * p.H + head) * p.T + qrow] = mx * p.scale + __logf(sum);
-                tc_fence_before();
-                mbar_arrive(&s_empty[wg]);
             }
+        }
+        if (sep && pu >= 0) {                                     // O of the chain's last tile
+            mbar_wait(&o_full[wg], pu & 1);
+            tc_fence_after();
+            read_out(pb, phead, pqrow, pmx, psum);
         }
     }
 
@@ -687,6 +736,12 @@ static int launch_fwd_tc(const void* qkv, void* out, float* lse, int B, int T, i
     p.T = T; p.H = H; p.slices_per_img = H * HD / 64; p.items = B * p.slices_per_img;
     p.Npad = (T + 15) / 16 * 16; p.NB = (T + 127) / 128; p.NKB = (p.Npad + 127) / 128;
     p.scale = scale; p.out = (__nv_bfloat16*)out; p.lse = lse;
+    p.s_stride = (p.Npad + 31) / 32 * 32;
+    // Separate O columns pay off when a chain has several tiles per item (T > 128: 175 -> 135 us at the decoder shape); for
+    // one-tile items (T = 50: 49 vs 55 us) the read-out that is deferred by a whole item costs more than it hides.
+    const bool fits = 2 * p.s_stride + 2 * HD <= 512;
+    p.sep = (fits && p.NB >= 2) ? 1 : 0;
+    if (const char* e = getenv("SSL4P_ATTN_SEP")) p.sep = (fits && e[0] != '0') ? 1 : 0;      // tests: force either TMEM plan
     auto kern = attention_fwd_tc_kernel<HD>;
     static bool attr = false;
     if (!attr) { SSL4P_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kFwdSmem)); attr = true; }
@@ -727,7 +782,7 @@ static int attn_tc_check(int B, int T, int H, int hd) {
     return SSL4P_OK;
 }
 
-extern "C" int ssl4p_attention_fwd_tc1(const void* qkv, void* out, float* lse, int B, int T, int H, int hd, float scale, void* stream) {
+extern "C" int ssl4p_attention_fwd(const void* qkv, void* out, float* lse, int B, int T, int H, int hd, float scale, void* stream) {
     SSL4P_REQUIRE(qkv && out && lse, "attention_fwd: null pointer");
     int rc = attn_tc_check(B, T, H, hd);
     if (rc) return rc;

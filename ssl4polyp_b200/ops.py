@@ -295,7 +295,7 @@ def attention_fwd(qkv, B, T, H, hd, scale, impl="tcgen05"):
     _req(qkv, bf16, "qkv")
     out = torch.empty(B * T, H * hd, dtype=bf16, device=qkv.device)
     lse = torch.empty(B, H, T, dtype=f32, device=qkv.device)
-    fn = {"tcgen05": lib.ssl4p_attention_fwd, "tc1": lib.ssl4p_attention_fwd_tc1, "mma": lib.ssl4p_attention_fwd_mma}[impl]
+    fn = {"tcgen05": lib.ssl4p_attention_fwd, "mma": lib.ssl4p_attention_fwd_mma}[impl]
     _lib.check(fn(qkv.data_ptr(), out.data_ptr(), lse.data_ptr(), B, T, H, hd, float(scale), _stream()), "attention_fwd")
     return out, lse
 

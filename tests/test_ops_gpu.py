@@ -214,7 +214,7 @@ def test_layernorm_fwd_bwd(M, D):
 
 
 # ---------------------------------------------------------------------------------------------- attention
-@pytest.mark.parametrize("impl", ["tcgen05", "tc1", "fwd2", "mma"])
+@pytest.mark.parametrize("impl", ["tcgen05", "tcgen05-alias", "tcgen05-sep", "mma"])
 @pytest.mark.parametrize("B,T,H,hd", [(2, 50, 12, 64), (2, 197, 16, 32), (1, 197, 12, 64), (3, 5, 2, 32), (2, 17, 2, 32), (2, 64, 4, 64),
                                       (40, 50, 12, 64), (21, 197, 16, 32), (3, 128, 2, 64), (2, 129, 4, 32), (1, 256, 2, 32), (300, 208, 2, 32), (5, 209, 2, 64), (160, 16, 2, 32)])
 def test_attention_fwd_bwd(B, T, H, hd, impl, monkeypatch):
@@ -223,8 +223,8 @@ def test_attention_fwd_bwd(B, T, H, hd, impl, monkeypatch):
     from ssl4polyp_b200 import ops
     if impl == "mma" and T > 208:
         pytest.skip("the mma.sync cross-check kernel stops at T = 208")
-    if impl == "fwd2":
-        monkeypatch.setenv("SSL4P_ATTN_FWD", "2")            # force the ring-buffered forward for every T
+    if impl.startswith("tcgen05-"):                          # force one of the two TMEM plans of the forward for every T
+        monkeypatch.setenv("SSL4P_ATTN_SEP", "0" if impl.endswith("alias") else "1")
         impl = "tcgen05"
     torch.manual_seed(B * 1000 + T)
     qkv = torch.randn(B, T, 3, H, hd).bfloat16()
