@@ -184,6 +184,8 @@ def b200_arm(args):
     dev = torch.device("cuda", local)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        from ssl4polyp_b200.dp import configure_overlap
+        configure_overlap(int(os.environ.get("SSL4P_DP_SMS", "0")))
         dist.init_process_group("nccl", device_id=dev)
     assert world == args.gpus or world == 1, f"--gpus {args.gpus} but WORLD_SIZE={world}"
 

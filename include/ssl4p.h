@@ -23,6 +23,9 @@ extern "C" {
 
 #define SSL4P_ABI_VERSION 1
 int ssl4p_abi_version(void);
+/* Leave n SMs out of every persistent grid (GEMM, attention) so that a concurrent collective (the NCCL gradient
+ * all-reduce overlapped with backward, main_pretrain.py:212-214 DDP) owns them; returns the previous value. */
+int ssl4p_reserve_sms(int n);
 const char* ssl4p_last_error(void);
 /* number of kernels this library has launched in the calling process (for bench.py's gpu_launches) */
 unsigned long long ssl4p_launch_count(void);

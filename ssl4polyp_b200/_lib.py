@@ -17,6 +17,7 @@ vp, i32, i64, f32, sz = C.c_void_p, C.c_int, C.c_longlong, C.c_float, C.c_size_t
 # name -> (restype, argtypes); must list every symbol include/ssl4p.h declares (tests/test_abi.py checks this)
 SIGNATURES = {
     "ssl4p_abi_version": (i32, []),
+    "ssl4p_reserve_sms": (i32, [i32]),
     "ssl4p_last_error": (C.c_char_p, []),
     "ssl4p_launch_count": (C.c_ulonglong, []),
     "ssl4p_gemm_bf16": (i32, [vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, i32, i32, i32, i32, vp]),

@@ -26,6 +26,12 @@ int check_launch(const char* what) {
     return SSL4P_OK;
 }
 
+static std::atomic<int> g_reserved_sms{0};
+
+// SMs our persistent kernels size their grids for: the device's count minus the ones set aside for a concurrent
+// collective (ssl4p_reserve_sms).  A persistent grid that covers EVERY SM cannot finish while a long-running NCCL
+// kernel holds a few of them (our CTAs need the whole shared memory of an SM), so under data parallelism the two
+// are given disjoint SM sets instead of fighting for the same ones.
 int num_sms() {
     static int sms = 0;
     if (sms == 0) {
@@ -33,7 +39,8 @@ int num_sms() {
         if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms <= 0)
             sms = 148;
     }
-    return sms;
+    const int r = g_reserved_sms.load(std::memory_order_relaxed);
+    return sms - r > 8 ? sms - r : 8;
 }
 
 // out[i] (+)= sum_s parts[s*stride + i], fixed summation order
@@ -68,6 +75,12 @@ __global__ void cast_f32_bf16_tail_kernel(const float* __restrict__ src, __nv_bf
 }  // namespace ssl4p
 
 using namespace ssl4p;
+
+extern "C" int ssl4p_reserve_sms(int n) {
+    if (n < 0) n = 0;
+    if (n > 64) n = 64;
+    return g_reserved_sms.exchange(n, std::memory_order_relaxed);
+}
 
 extern "C" int ssl4p_abi_version(void) { return SSL4P_ABI_VERSION; }
 extern "C" const char* ssl4p_last_error(void) { return g_err; }

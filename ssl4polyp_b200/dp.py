@@ -47,6 +47,20 @@ def plan_buckets(offsets: dict, trainable: list, limit_elems: int, align: int = 
     return buckets
 
 
+def configure_overlap(n_sms: int) -> None:
+    """Call BEFORE `init_process_group`: cap NCCL at `n_sms` CTAs (= SMs).  Together with `ssl4p_reserve_sms(n_sms)`
+    (done by the engine) the all-reduce and our persistent kernels run on disjoint SM sets.  The gradient all-reduce
+    needs little bandwidth (447 MB per ~25 ms step for ViT-B), so a handful of SMs is plenty."""
+    import os
+    if n_sms > 0:
+        os.environ.setdefault("NCCL_MAX_CTAS", str(n_sms))
+        os.environ.setdefault("NCCL_MAX_NCHANNELS", str(n_sms))
+
+
+# timing experiments only (scripts/dp_sweep.sh): enqueue everything except the collective itself
+_SKIP_COLLECTIVE = bool(int(__import__("os").environ.get("SSL4P_DP_SKIP_COLLECTIVE", "0")))
+
+
 class BucketReducer:
     def __init__(self, flat: torch.Tensor, buckets: list, group=None):
         self.flat = flat
@@ -88,7 +102,8 @@ class BucketReducer:
             ev.record(torch.cuda.current_stream())
             self.comm_stream.wait_event(ev)
             with torch.cuda.stream(self.comm_stream):
-                dist.all_reduce(view, op=dist.ReduceOp.SUM, group=self.group)
+                if not _SKIP_COLLECTIVE:
+                    dist.all_reduce(view, op=dist.ReduceOp.SUM, group=self.group)
         else:
             self._handles.append(dist.all_reduce(view, op=dist.ReduceOp.SUM, group=self.group, async_op=True))
 

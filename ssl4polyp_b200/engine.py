@@ -18,6 +18,7 @@ What `engine_pretrain.train_one_epoch` does per iteration in the reference
 from __future__ import annotations
 
 import math
+import os
 
 import torch
 import torch.distributed as dist
@@ -74,9 +75,16 @@ class TrainEngine:
         self.wd_flags = flags.to(dev)
         # ---- data parallel (dp.py): bucket plan over the gradient arena + overlapped all-reduce
         trainable = [n for n in store.offsets if store.params[n].requires_grad]
+        bucket_mb = float(os.environ.get("SSL4P_DP_BUCKET_MB", bucket_mb))
         self.buckets = plan_buckets(store.offsets, trainable, int(bucket_mb * (1 << 20) / 4), ALIGN)
         self.reducer = BucketReducer(self.grads, self.buckets, process_group)
         self.world = self.reducer.world
+        if self.world > 1 and dev.type == "cuda":
+            # optional: persistent grids leave SSL4P_DP_SMS SMs to the NCCL kernels of the overlapped all-reduce (see
+            # dp.configure_overlap).  Measured on 2 x B200 (scripts/dp_sweep.sh): 0 -> 26.4 ms, 2 -> 28.9, 4 -> 27.5,
+            # 16 -> 27.4 ms/step, so sharing the SMs is the default.
+            from . import _lib
+            _lib.load().ssl4p_reserve_sms(int(os.environ.get("SSL4P_DP_SMS", "0")))
         self.sink = ArenaSink(self)
         self._reduce_now = True
 
