@@ -131,3 +131,90 @@ class ViT_from_MAE(_ClassifierMixin, MaskedAutoencoderViT):
 
     def forward(self, imgs):
         return self._classify(imgs, bool(self.head))
+
+
+class VisionTransformer_from_Any(_ClassifierMixin, nn.Module):
+    """timm-0.4.12-shaped ViT-B/16 (learned `pos_embed`, `cls_token`, `qkv_bias=True`, LayerNorm eps 1e-6) + `lin_head`,
+    the `--pretraining random / ImageNet_class` backbone of the reference (models.py:26-140).  State-dict keys are
+    timm's (`cls_token, pos_embed, patch_embed.proj.*, blocks.i.*, norm.*`) plus `lin_head.*`.
+
+    Kept on purpose: timm 0.4.12 holds `blocks` in an `nn.Sequential`, so `classification/finetune.py:76-77`
+    (`isinstance(blocks, (nn.ModuleList, list, tuple))`) does not unfreeze tail blocks for this backbone in the
+    `head+1` / `head+2` modes; the reference behaves the same way.
+    `ImageNet_weights=True` downloads an .npz in the reference (models.py:52-56); there is no network here, so pass a
+    local torch checkpoint path through `load_pretrained` instead.
+    """
+
+    def __init__(self, head, num_classes, frozen, dense, embed_dim, depth, num_heads, out_token, ImageNet_weights=False):
+        super().__init__()
+        norm_layer = partial(nn.LayerNorm, eps=1e-6)
+        self.num_features = self.embed_dim = embed_dim
+        self.patch_embed = PatchEmbed(224, 16, 3, embed_dim)
+        n_patches = self.patch_embed.num_patches
+        self.cls_token = nn.Parameter(torch.zeros(1, 1, embed_dim))
+        self.pos_embed = nn.Parameter(torch.zeros(1, n_patches + 1, embed_dim))
+        self.pos_drop = nn.Dropout(p=0.0)
+        self.blocks = nn.Sequential(*[Block(embed_dim, num_heads, 4., qkv_bias=True, norm_layer=norm_layer) for _ in range(depth)])
+        self.norm = norm_layer(embed_dim)
+        self.pre_logits = nn.Identity()
+        self.head = nn.Identity()                                  # models.py:58
+        self.head_bool = head
+        if head:
+            self.lin_head = nn.Linear(embed_dim, num_classes)
+        self.frozen = frozen
+        self.dense = dense
+        if dense:
+            raise NotImplementedError("dense (DPT) decoding is outside the B200 hot path (see module docstring)")
+        self.out_token = out_token
+        # timm 0.4.12 VisionTransformer.init_weights(''): trunc_normal(.02) tables and Linear weights, zero biases
+        nn.init.trunc_normal_(self.pos_embed, std=.02)
+        nn.init.trunc_normal_(self.cls_token, std=.02)
+        for m in list(self.blocks.modules()) + [self.norm]:
+            if isinstance(m, nn.Linear):
+                nn.init.trunc_normal_(m.weight, std=.02)
+                if m.bias is not None:
+                    nn.init.zeros_(m.bias)
+            elif isinstance(m, nn.LayerNorm):
+                nn.init.zeros_(m.bias)
+                nn.init.ones_(m.weight)
+        self._dims = vit_core.ViTDims(img_size=224, patch_size=16, in_chans=3, embed_dim=embed_dim, depth=depth,
+                                      num_heads=num_heads, ln_eps=1e-6)
+        self._store = ParamStore(self)
+        if ImageNet_weights:
+            raise RuntimeError("ImageNet_weights=True needs the augreg .npz download (models.py:52-56); no network here: "
+                               "construct with ImageNet_weights=False and call load_pretrained(<local torch checkpoint>)")
+
+    # ---- arena plumbing (same contract as MaskedAutoencoderViT) ----------------------------------------------
+    _param_list = MaskedAutoencoderViT._param_list
+    _grads_in_order = MaskedAutoencoderViT._grads_in_order
+    _want_grad = MaskedAutoencoderViT._want_grad
+
+    def load_pretrained(self, checkpoint_path):
+        """torch checkpoints only (models.py:87-122: `state_dict` / `model` / `model_state` / `weights` / `params` or a bare
+        state dict, non-strict)."""
+        if str(checkpoint_path).lower().endswith(".npz"):
+            raise NotImplementedError("numpy (.npz) checkpoints need timm's _load_weights, which is not part of the hot path")
+        ckpt = torch.load(checkpoint_path, map_location="cpu")
+        sd = None
+        if isinstance(ckpt, dict):
+            for key in ("state_dict", "model", "model_state", "weights", "params"):
+                if isinstance(ckpt.get(key), dict):
+                    sd = ckpt[key]
+                    break
+            if sd is None and all(isinstance(k, str) for k in ckpt.keys()):
+                sd = ckpt
+        if not isinstance(sd, dict):
+            print(f"Warning: unsupported checkpoint format for {checkpoint_path!s}: {type(ckpt)}")
+            return
+        missing, unexpected = self.load_state_dict(sd, strict=False)
+        self._store.mark_dirty()
+        if missing:
+            print(f"Missing keys when loading pretrained weights: {missing}")
+        if unexpected:
+            print(f"Unexpected keys when loading pretrained weights: {unexpected}")
+
+    def forward_features(self, x):
+        return self._features(x)
+
+    def forward(self, x):
+        return self._classify(x, bool(self.head_bool))

@@ -150,6 +150,22 @@ def colsum(x, out=None, accumulate=False):
     return out
 
 
+def reduce_rows_f32(x, out=None, accumulate=False):
+    """out[j] (+)= sum_g x[g, j]; x fp32 [G, N] contiguous (fixed-order two-stage reduce: deterministic)."""
+    lib = _lib.load()
+    _req(x, f32, "reduce_rows x")
+    G, N = x.shape
+    if out is None:
+        out = torch.empty(N, dtype=f32, device=x.device)
+        accumulate = False
+    _req(out, f32, "reduce_rows out")
+    assert out.numel() == N
+    ws = workspace(32 * N * 4, x.device, "reduce_rows")
+    _lib.check(lib.ssl4p_reduce_rows_f32(x.data_ptr(), G, N, out.data_ptr(), int(accumulate), ws.data_ptr(), ws.numel(), _stream()),
+               "reduce_rows")
+    return out
+
+
 def cast_bf16(src, dst=None):
     lib = _lib.load()
     _req(src, f32, "cast src")

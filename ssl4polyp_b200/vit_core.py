@@ -202,6 +202,7 @@ class EncoderSaved:
     rstd: torch.Tensor = None
     N: int = 0
     keep: int = 0
+    all_patches: bool = False            # no masking: token r of every image is patch r
 
 
 def encoder_fwd(W: Weights, dims: ViTDims, imgs: torch.Tensor, ids_keep, keep: int, save: bool):
@@ -214,7 +215,7 @@ def encoder_fwd(W: Weights, dims: ViTDims, imgs: torch.Tensor, ids_keep, keep: i
     w_pe = W.b("patch_embed.proj.weight")
     tok = ops.gemm(cols, w_pe, GEMM_NT, EPI_BIAS_F32, bias=W.f("patch_embed.proj.bias"))
     x = ops.assemble_tokens(tok, ids_keep, W.f("pos_embed"), W.f("cls_token"), N, keep, D).view(N * Te, D)
-    sv = EncoderSaved(cols=cols, N=N, keep=keep) if save else None
+    sv = EncoderSaved(cols=cols, N=N, keep=keep, all_patches=ids_keep is None) if save else None
     for i in range(dims.depth):
         x, s = block_fwd(W, f"{dims.block_prefix}{i}.", x, N, Te, dims.num_heads, dims.ln_eps, save)
         if save:
@@ -239,7 +240,8 @@ def encoder_bwd(W: Weights, sink: GradSink, dims: ViTDims, sv: EncoderSaved, dla
     """dlatent: bf16 [N*Te, D], gradient w.r.t. the output of the final LayerNorm."""
     N, keep = sv.N, sv.keep
     Te = keep + 1
-    stem_needed = W.need("patch_embed.proj.weight") or W.need("patch_embed.proj.bias") or W.need("cls_token")
+    stem_needed = (W.need("patch_embed.proj.weight") or W.need("patch_embed.proj.bias") or W.need("cls_token")
+                   or W.need("pos_embed"))
     first = _first_needed_block(W, dims, dims.block_prefix, dims.depth, stem_needed)
     if first == dims.depth and not (W.need("norm.weight") or W.need("norm.bias")) and not stem_needed:
         return
@@ -259,6 +261,14 @@ def encoder_bwd(W: Weights, sink: GradSink, dims: ViTDims, sv: EncoderSaved, dla
         dcls, acc = torch.empty(cls.shape, dtype=torch.float32, device=cls.device), False
     dtok = ops.assemble_tokens_bwd(dx.view(N, Te, -1), dcls, accumulate=acc)
     sink.ready("cls_token")
+    if W.need("pos_embed"):
+        # learned position table (timm VisionTransformer, models.py:28-33 `x + self.pos_embed`): d pos = sum over images.
+        # The MAE encoder's table is a frozen sin-cos buffer (models_mae.py:36) and never gets here.
+        if not sv.all_patches:
+            raise RuntimeError("a trainable pos_embed is only supported without masking (classifier path)")
+        dpos, acc_p = sink.buf("pos_embed", W.f("pos_embed"))
+        ops.reduce_rows_f32(dx.view(N, -1), dpos.view(-1), accumulate=acc_p)
+        sink.ready("pos_embed")
     _wgrad(W, sink, "patch_embed.proj.weight", "patch_embed.proj.bias", dtok, sv.cols)
 
 

@@ -158,6 +158,16 @@ def test_reference_factories_and_classifier_surface():
     for p in list(m.blocks)[-1].parameters():
         p.requires_grad_(True)
     assert sum(p.requires_grad for p in m.parameters()) == 12
+    # --pretraining random / ImageNet_class backbone (models.py:26-140): timm 0.4.12 key set, learned pos_embed,
+    # `blocks` an nn.Sequential (so finetune.py's head+k modes leave it frozen, as in the reference)
+    v = utils.get_ImageNet_or_random_ViT(True, 2, False, None, False, out_token="spatial")
+    assert isinstance(v, models.VisionTransformer_from_Any) and isinstance(v.blocks, torch.nn.Sequential)
+    vk = list(v.state_dict())
+    assert vk[:4] == ["cls_token", "pos_embed", "patch_embed.proj.weight", "patch_embed.proj.bias"] and len(vk) == 152
+    assert v.pos_embed.requires_grad and v.pos_embed.shape == (1, 197, 768) and 0 < float(v.pos_embed.std()) < 0.03
+    assert v.blocks[0].attn.qkv.bias is not None and v.head_bool is True and isinstance(v.head, torch.nn.Identity)
+    with pytest.raises(RuntimeError):
+        utils.get_ImageNet_or_random_ViT(True, 2, False, None, True)
 
 
 def test_mae_to_classifier_checkpoint_handoff(tmp_path):

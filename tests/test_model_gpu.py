@@ -211,6 +211,42 @@ def test_classifier_against_oracle():
         assert cos(g.cpu(), v.grad) > 0.995, (k, cos(g.cpu(), v.grad))
 
 
+def test_vit_from_any_against_oracle():
+    """timm-shaped ViT with a LEARNED pos_embed (reference models.py:26-140): logits, BCE loss and every gradient,
+    including d pos_embed (sum over images) and d cls_token, against the CPU oracle on the same weights."""
+    from ssl4polyp_b200 import models, utils
+    torch.manual_seed(5)
+    m = utils.get_ImageNet_or_random_ViT(True, 2, False, None, False, out_token="spatial").to(dev()).train()
+    assert isinstance(m, models.VisionTransformer_from_Any) and isinstance(m.blocks, torch.nn.Sequential)
+    sd = {k: v.detach().cpu().clone() for k, v in m.state_dict().items()}
+    B = 3
+    imgs = synth_imgs(B, 11)
+    target = torch.tensor([1, 0, 1])
+    sd_g = {k: v.clone().requires_grad_(True) for k, v in sd.items()}
+    logits_o = O.classifier_forward(sd_g, imgs, O.MAE_BASE, "spatial", True)
+    loss_o = O.binary_polyp_loss(logits_o, target)
+    loss_o.backward()
+    logits = m(imgs.to(dev()))
+    assert logits.shape == (B, 2) and logits.dtype == torch.float32
+    assert (logits.cpu() - logits_o.detach()).abs().max().item() < 3e-2 * max(1.0, logits_o.abs().max().item())
+    loss = O.binary_polyp_loss(logits, target.to(dev()))
+    assert abs(loss.item() - loss_o.item()) / abs(loss_o.item()) < LOSS_RTOL
+    loss.backward()
+    params = dict(m.named_parameters())
+    assert params["pos_embed"].grad is not None
+    for k, v in sd_g.items():
+        g = params[k].grad
+        assert g is not None, k
+        assert cos(g.cpu(), v.grad) > 0.995, (k, cos(g.cpu(), v.grad))
+    # the fused fine-tune step (ClassifierEngine) accepts it too
+    from ssl4polyp_b200.engine import ClassifierEngine
+    eng = ClassifierEngine(m, lr=5e-5, weight_decay=0.05)
+    l0 = eng.step(imgs.to(dev()), target.to(dev())).item()
+    for _ in range(6):
+        l1 = eng.step(imgs.to(dev()), target.to(dev())).item()
+    assert l1 < l0, (l0, l1)
+
+
 def test_classifier_finetune_modes_prune_backward():
     from ssl4polyp_b200 import models
     torch.manual_seed(3)
