@@ -1,0 +1,279 @@
+"""`main_pretrain.py` with the reference's command line on the B200 engine.
+
+    python -m ssl4polyp_b200.main_pretrain --model mae_vit_base_patch16 --norm_pix_loss --batch_size 256 \
+        --data_path /data/hyperkvasir --no_train_dir --epochs 400 --warmup_epochs 40 --blr 1.5e-4 --weight_decay 0.05
+    torchrun --nproc-per-node 8 -m ssl4polyp_b200.main_pretrain ...            (one process per GPU)
+
+Flags, defaults and their meaning follow /root/reference/src/ssl4polyp/models/mae/main_pretrain.py:47-135; the loop
+follows `engine_pretrain.train_one_epoch` (:22-100) and `main` (:139-330):
+  * per-ITERATION half-cosine lr with linear warm-up (util/lr_sched.py:9-21), `lr = blr * eff_batch / 256`;
+  * `seed + rank` RNG streams (:146-148), `DistributedSampler(seed=args.seed)` + `set_epoch(seed + epoch)`;
+  * AdamW(betas 0.9/0.95) with timm's no-decay rule (:216-218);
+  * non-finite loss -> `sys.exit(1)` (engine_pretrain.py:59-62);
+  * checkpoints `<output_dir>/ckpts/checkpoint-<epoch>.pth` = {"model","optimizer","epoch","scaler","args"} plus the
+    `last.pth` symlink, keep-last / milestone rotation, SIGTERM/SIGINT save, `log.txt` json lines (:231-312,
+    util/misc.py:306-335); `--resume` restores model, optimiser moments and epoch (:337-352).
+What differs, on purpose: the step is `PretrainEngine.step` (our kernels, fused AdamW, bucketed all-reduce, no
+GradScaler: bf16 operands need no loss scaling, so "scaler" is an empty dict); `--precision fp32` is refused (the
+tensor-core path is bf16 operands / fp32 accumulate by construction); `--data_path synthetic[:N]` yields N random
+batches per epoch so the entry point can be exercised without a dataset.  TensorBoard logging is not part of the hot
+path (SURVEY.md §8 out of scope): `--log_dir` is accepted and ignored.
+"""
+from __future__ import annotations
+
+import argparse
+import datetime
+import glob
+import json
+import math
+import os
+import signal
+import sys
+import time
+from pathlib import Path
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+
+def get_args_parser():
+    parser = argparse.ArgumentParser('MAE pre-training', add_help=False)
+    parser.add_argument('--batch_size', default=64, type=int,
+                        help='Batch size per GPU (effective batch size is batch_size * accum_iter * # gpus')
+    parser.add_argument('--epochs', default=400, type=int)
+    parser.add_argument('--accum_iter', '--acum_iter', dest='accum_iter', default=1, type=int)
+    parser.add_argument('--model', default='mae_vit_large_patch16', type=str, metavar='MODEL')
+    parser.add_argument('--input_size', default=224, type=int)
+    parser.add_argument('--mask_ratio', default=0.75, type=float)
+    parser.add_argument('--norm_pix_loss', action='store_true')
+    parser.set_defaults(norm_pix_loss=False)
+    parser.add_argument('--weight_decay', type=float, default=0.05)
+    parser.add_argument('--lr', type=float, default=None, metavar='LR')
+    parser.add_argument('--blr', type=float, default=1e-3, metavar='LR')
+    parser.add_argument('--min_lr', type=float, default=0., metavar='LR')
+    parser.add_argument('--warmup_epochs', type=int, default=40, metavar='N')
+    parser.add_argument('--data_path', default='/datasets01/imagenet_full_size/061417/', type=str)
+    parser.add_argument('--no_train_dir', action='store_true')
+    parser.add_argument('--output_dir', default=str(Path('checkpoints') / 'mae' / 'pretrain'))
+    parser.add_argument('--log_dir', default=str(Path('outputs') / 'mae' / 'pretrain'))
+    parser.add_argument('--device', default='cuda')
+    parser.add_argument('--seed', default=0, type=int)
+    parser.add_argument('--resume', default='')
+    parser.add_argument('--save-freq-epochs', type=int, default=20)
+    parser.add_argument('--save-freq-mins', type=int, default=0)
+    parser.add_argument('--keep-last', type=int, default=5)
+    parser.add_argument('--keep-every-n-epochs', type=int, default=50)
+    parser.add_argument('--start_epoch', default=0, type=int, metavar='N')
+    parser.add_argument('--num_workers', default=10, type=int)
+    parser.add_argument('--pin_mem', action='store_true')
+    parser.add_argument('--no_pin_mem', action='store_false', dest='pin_mem')
+    parser.set_defaults(pin_mem=True)
+    parser.add_argument('--world_size', default=1, type=int)
+    parser.add_argument('--local_rank', default=-1, type=int)
+    parser.add_argument('--dist_on_itp', action='store_true')
+    parser.add_argument('--dist_url', default='env://')
+    parser.add_argument('--precision', choices=['amp', 'fp32'], default='amp')
+    return parser
+
+
+class _SyntheticBatches:
+    """`--data_path synthetic[:N]`: N batches per epoch of ImageNet-normalised-looking noise (no dataset on the box)."""
+
+    def __init__(self, n, batch, size, seed):
+        self.n, self.batch, self.size, self.seed = n, batch, size, seed
+        self.sampler = None
+
+    def __len__(self):
+        return self.n
+
+    def __iter__(self):
+        g = torch.Generator().manual_seed(self.seed)
+        for _ in range(self.n):
+            yield torch.randn(self.batch, 3, self.size, self.size, generator=g).pin_memory(), None
+
+
+def _init_distributed(args):
+    """util/misc.py init_distributed_mode for the torchrun environment (RANK / WORLD_SIZE / LOCAL_RANK)."""
+    if 'RANK' in os.environ and 'WORLD_SIZE' in os.environ:
+        args.rank, args.world_size = int(os.environ['RANK']), int(os.environ['WORLD_SIZE'])
+        args.gpu = int(os.environ.get('LOCAL_RANK', 0))
+        args.distributed = args.world_size > 1
+    else:
+        args.rank, args.world_size, args.gpu, args.distributed = 0, 1, 0, False
+    torch.cuda.set_device(args.gpu)
+    if args.distributed:
+        from .dp import configure_overlap
+        configure_overlap(int(os.environ.get("SSL4P_DP_SMS", "0")))
+        dist.init_process_group('nccl', init_method=args.dist_url, device_id=torch.device('cuda', args.gpu))
+        dist.barrier()
+
+
+def _build_loader(args):
+    if args.data_path.startswith('synthetic'):
+        n = int(args.data_path.split(':')[1]) if ':' in args.data_path else 8
+        return _SyntheticBatches(n, args.batch_size, args.input_size, args.seed + args.rank)
+    from torchvision import datasets, transforms
+    transform_train = transforms.Compose([
+        transforms.RandomResizedCrop(args.input_size, scale=(0.2, 1.0), interpolation=3),  # 3 is bicubic
+        transforms.RandomHorizontalFlip(),
+        transforms.ToTensor(),
+        transforms.Normalize(mean=[0.485, 0.456, 0.406], std=[0.229, 0.224, 0.225])])
+    data_dir = args.data_path if args.no_train_dir else os.path.join(args.data_path, 'train')
+    dataset_train = datasets.ImageFolder(data_dir, transform=transform_train)
+    print(dataset_train)
+    sampler = torch.utils.data.DistributedSampler(dataset_train, num_replicas=args.world_size, rank=args.rank,
+                                                  shuffle=True, seed=args.seed)
+    return torch.utils.data.DataLoader(dataset_train, sampler=sampler, batch_size=args.batch_size,
+                                       num_workers=args.num_workers, pin_memory=args.pin_mem, drop_last=True)
+
+
+def train_one_epoch(engine, data_loader, device, epoch, args, save_ckpt_fn=None, last_time_save=None, time_save_sec=None):
+    """One epoch of engine_pretrain.train_one_epoch (:22-100) on `PretrainEngine`."""
+    from .engine import cosine_lr
+    accum_iter = args.accum_iter
+    n_iter = len(data_loader)
+    loss_sum, loss_cnt, lr = 0.0, 0, args.lr
+    t0 = time.time()
+    for it, (samples, _) in enumerate(data_loader):
+        if it % accum_iter == 0:                       # per-iteration (not per-epoch) lr schedule
+            lr = cosine_lr(it / n_iter + epoch, args.lr, args.min_lr, args.warmup_epochs, args.epochs)
+        samples = samples.to(device, non_blocking=True)
+        loss = engine.step(samples, lr=lr, accum_iter=accum_iter, micro_index=it % accum_iter)
+        loss_value = loss.item()                       # the reference syncs here too (engine_pretrain.py:55)
+        if not math.isfinite(loss_value):
+            print("Loss is {}, stopping training".format(loss_value))
+            sys.exit(1)
+        if args.distributed:                           # util/misc.py all_reduce_mean
+            t = torch.tensor([loss_value], device=device)
+            dist.all_reduce(t)
+            loss_value = (t / args.world_size).item()
+        loss_sum += loss_value
+        loss_cnt += 1
+        if it % 20 == 0 or it == n_iter - 1:
+            print(f"Epoch: [{epoch}]  [{it:4d}/{n_iter}]  lr: {lr:.6f}  loss: {loss_value:.4f} ({loss_sum / loss_cnt:.4f})  "
+                  f"time: {(time.time() - t0) / (it + 1):.4f}")
+        if save_ckpt_fn is not None and last_time_save is not None and time_save_sec:
+            if (time.time() - last_time_save[0]) >= time_save_sec:
+                save_ckpt_fn(epoch)
+                last_time_save[0] = time.time()
+    bad = engine.nonfinite_count()
+    if bad:
+        print(f"[warn] {bad} optimiser blocks saw a non-finite gradient so far")
+    return {"loss": loss_sum / max(loss_cnt, 1), "lr": lr}
+
+
+def main(args):
+    from . import models_mae
+    from .engine import PretrainEngine
+    if args.precision == 'fp32':
+        raise SystemExit("--precision fp32: the B200 path computes with bf16 tensor-core operands and fp32 accumulation only")
+    _init_distributed(args)
+    print("{}".format(args).replace(', ', ',\n'))
+    device = torch.device('cuda', args.gpu)
+    seed = args.seed + args.rank
+    torch.manual_seed(seed)
+    np.random.seed(seed)
+
+    data_loader_train = _build_loader(args)
+    model = models_mae.__dict__[args.model](norm_pix_loss=args.norm_pix_loss)
+    model.to(device)
+    eff_batch_size = args.batch_size * args.accum_iter * args.world_size
+    if args.lr is None:
+        args.lr = args.blr * eff_batch_size / 256
+    print("base lr: %.2e" % (args.lr * 256 / eff_batch_size))
+    print("actual lr: %.2e" % args.lr)
+    print("accumulate grad iterations: %d" % args.accum_iter)
+    print("effective batch size: %d" % eff_batch_size)
+    engine = PretrainEngine(model, lr=args.lr, weight_decay=args.weight_decay, betas=(0.9, 0.95), mask_ratio=args.mask_ratio)
+
+    if args.resume:                                    # util/misc.py load_model
+        checkpoint = torch.load(args.resume, map_location='cpu', weights_only=False)
+        model.load_state_dict(checkpoint['model'])
+        model._store.mark_dirty()
+        print("Resume checkpoint %s" % args.resume)
+        if 'optimizer' in checkpoint and 'epoch' in checkpoint:
+            engine.load_optimizer_state_dict(checkpoint['optimizer'])
+            args.start_epoch = checkpoint['epoch'] + 1
+            print("With optim & sched!")
+
+    print(f"Start training for {args.epochs} epochs")
+    last_time_save = [time.time()]
+    time_save_sec = args.save_freq_mins * 60
+    ckpt_dir = os.path.join(args.output_dir, "ckpts") if args.output_dir else None
+    if ckpt_dir:
+        os.makedirs(ckpt_dir, exist_ok=True)
+    main_process = args.rank == 0
+
+    def _is_milestone(ep):
+        n = args.keep_every_n_epochs
+        return n > 0 and ((ep + 1) % n == 0 or (ep + 1) == args.epochs)
+
+    def _cleanup_checkpoints():
+        paths = sorted(glob.glob(os.path.join(ckpt_dir, "checkpoint-*.pth")))
+        survivors = set(paths[-args.keep_last:]) if args.keep_last > 0 else set()
+        for p in paths:
+            try:
+                ep = int(os.path.basename(p).split('-')[1].split('.')[0])
+            except Exception:
+                ep = -1
+            if p in survivors or _is_milestone(ep):
+                continue
+            try:
+                os.remove(p)
+            except OSError:
+                pass
+
+    def _save_checkpoint(ep):
+        if not (ckpt_dir and main_process):
+            return
+        path = Path(ckpt_dir) / f"checkpoint-{ep}.pth"
+        to_save = {"model": model.state_dict(), "optimizer": engine.optimizer_state_dict(), "epoch": ep, "scaler": {}, "args": args}
+        torch.save(to_save, path)
+        last = Path(ckpt_dir) / "last.pth"
+        try:
+            if last.is_symlink() or last.exists():
+                last.unlink()
+            last.symlink_to(path.name)
+        except OSError:
+            pass
+        _cleanup_checkpoints()
+
+    epoch = args.start_epoch
+
+    def _term_handler(signum, frame):
+        try:
+            _save_checkpoint(epoch)
+        finally:
+            os._exit(0)
+
+    for sig in (signal.SIGTERM, signal.SIGINT):
+        signal.signal(sig, _term_handler)
+
+    start_time = time.time()
+    for epoch in range(args.start_epoch, args.epochs):
+        if args.distributed and getattr(data_loader_train, "sampler", None) is not None:
+            data_loader_train.sampler.set_epoch(args.seed + epoch)
+        train_stats = train_one_epoch(engine, data_loader_train, device, epoch, args, save_ckpt_fn=_save_checkpoint,
+                                      last_time_save=last_time_save, time_save_sec=time_save_sec)
+        do_epoch_save = (args.save_freq_epochs > 0 and ((epoch + 1) % args.save_freq_epochs == 0)) or ((epoch + 1) == args.epochs)
+        if args.output_dir and do_epoch_save:
+            _save_checkpoint(epoch)
+            last_time_save[0] = time.time()
+        log_stats = {**{f'train_{k}': v for k, v in train_stats.items()}, 'epoch': epoch}
+        if args.output_dir and main_process:
+            with open(os.path.join(args.output_dir, "log.txt"), mode="a", encoding="utf-8") as f:
+                f.write(json.dumps(log_stats) + "\n")
+    total_time_str = str(datetime.timedelta(seconds=int(time.time() - start_time)))
+    print('Training time {}'.format(total_time_str))
+    if args.distributed:
+        torch.cuda.synchronize()
+        dist.barrier()
+
+
+if __name__ == '__main__':
+    args = get_args_parser()
+    args = args.parse_args()
+    if args.output_dir:
+        Path(args.output_dir).mkdir(parents=True, exist_ok=True)
+    main(args)

@@ -250,3 +250,22 @@ def test_bucket_reducer_world_size_2_gloo(tmp_path):
         out, err = p.communicate(timeout=180)
         assert p.returncode == 0, err[-2000:]
         assert "ok" in out
+
+
+def test_main_pretrain_parser_matches_the_reference_flag_for_flag():
+    """Same flags and defaults as /root/reference/.../mae/main_pretrain.py:47-135 (parsed out of the reference source when
+    the reference tree is present; the frozen expectation below otherwise)."""
+    import argparse
+    from pathlib import Path
+    from ssl4polyp_b200 import main_pretrain as MP
+    ours = vars(MP.get_args_parser().parse_args([]))
+    ref_path = "/root/reference/src/ssl4polyp/models/mae/main_pretrain.py"
+    if os.path.exists(ref_path):
+        src = open(ref_path).read()
+        ns = {"argparse": argparse, "Path": Path}
+        exec(src[src.index("def get_args_parser"):src.index("def main(")], ns)
+        assert vars(ns["get_args_parser"]().parse_args([])) == ours
+    assert ours["batch_size"] == 64 and ours["model"] == "mae_vit_large_patch16" and ours["mask_ratio"] == 0.75
+    assert ours["blr"] == 1e-3 and ours["warmup_epochs"] == 40 and ours["weight_decay"] == 0.05 and ours["precision"] == "amp"
+    a = MP.get_args_parser().parse_args(["--acum_iter", "4", "--no_train_dir", "--save-freq-mins", "30", "--keep-last", "2"])
+    assert a.accum_iter == 4 and a.no_train_dir and a.save_freq_mins == 30 and a.keep_last == 2

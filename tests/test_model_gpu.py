@@ -3,6 +3,7 @@
   (2) the CPU oracle (oracle/mae_oracle.py) run on the same weights, images and noise.
 Tolerances are BASELINE.json's: masking indices / ids_restore / mask bit-exact; loss rel 1e-2; gradient cosine > 0.999.
 """
+import math
 import os
 
 import pytest
@@ -337,3 +338,26 @@ def test_engine_step_matches_oracle_adamw_step():
             delta, delta_o = torch.cat([delta[:n], delta[2 * n:]]), torch.cat([delta_o[:n], delta_o[2 * n:]])
         if delta_o.abs().max() > 0:
             assert cos(delta, delta_o) > 0.98, k
+
+
+def test_main_pretrain_cli_synthetic_run_and_resume(tmp_path):
+    """The reference's command line (main_pretrain.py:47-135) end to end on synthetic batches: 2 epochs, checkpoint
+    dict layout of util/misc.py:306-318, `last.pth`, log.txt, then --resume continues from the saved epoch."""
+    import json
+    from ssl4polyp_b200 import main_pretrain as MP
+    out = tmp_path / "run"
+    argv = ["--model", "mae_vit_base_patch16", "--norm_pix_loss", "--batch_size", "4", "--epochs", "2", "--warmup_epochs", "1",
+            "--blr", "1.5e-4", "--data_path", "synthetic:3", "--output_dir", str(out), "--save-freq-epochs", "1"]
+    args = MP.get_args_parser().parse_args(argv)
+    out.mkdir(parents=True)
+    MP.main(args)
+    ck = torch.load(out / "ckpts" / "checkpoint-1.pth", map_location="cpu", weights_only=False)
+    assert set(ck) == {"model", "optimizer", "epoch", "scaler", "args"} and ck["epoch"] == 1
+    assert "decoder_blocks.7.mlp.fc2.weight" in ck["model"] and ck["model"]["patch_embed.proj.weight"].shape == (768, 3, 16, 16)
+    assert (out / "ckpts" / "last.pth").is_symlink()
+    logs = [json.loads(l) for l in open(out / "log.txt")]
+    assert [l["epoch"] for l in logs] == [0, 1] and all(math.isfinite(l["train_loss"]) for l in logs)
+    args2 = MP.get_args_parser().parse_args(argv[:argv.index("--epochs")] + ["--epochs", "3"] + argv[argv.index("--epochs") + 2:] +
+                                            ["--resume", str(out / "ckpts" / "checkpoint-1.pth")])
+    MP.main(args2)
+    assert args2.start_epoch == 2 and (out / "ckpts" / "checkpoint-2.pth").exists()
