@@ -288,7 +288,7 @@ def b200_arm(args):
     achieved = g_flops / (g_ms / 1e3) / 1e12 if g_ms > 0 else 0.0
     step_tflops = F_STEP_GFLOP_PER_IMG[args.model] * 1e9 * B / (ms_per_step / 1e3) / 1e12
     roofline = {"bound": "tensor", "kernel": "gemm_tcgen05_kernel", "achieved": achieved, "peak": pk["tflops_sustained"],
-                "unit": "TFLOP/s", "frac": achieved / pk["tflops_sustained"], "traffic": None,
+                "unit": "TFLOP/s", "frac": achieved / pk["tflops_sustained"], "traffic": gemm_traffic(args.model, B),
                 "peak_source": f"{pk['source']} (bf16 sustained; burst {pk['tflops_burst']})",
                 "gemm_launches_per_step": len(prof), "gemm_ms_per_step": g_ms, "gemm_share_of_step": g_ms / ms_per_step,
                 "step_tflops_per_gpu": step_tflops, "step_frac_of_peak": step_tflops / pk["tflops_sustained"]}
@@ -325,6 +325,16 @@ def b200_arm(args):
         sys.stdout.flush()
         sys.stderr.flush()
         os._exit(0)
+
+
+def gemm_traffic(model: str, batch: int):
+    """DRAM bytes per gemm_tcgen05_kernel launch (read + write, average over the launches of one step) from the committed
+    ncu capture of this workload (profiles/r01g_gemm_traffic.{csv,json}); null for a workload that was not captured."""
+    path = os.path.join(ROOT, "profiles", "r01g_gemm_traffic.json")
+    if model != "base" or batch != 256 or not os.path.exists(path):
+        return None
+    with open(path) as f:
+        return json.load(f)["traffic_per_launch"]
 
 
 def main():
