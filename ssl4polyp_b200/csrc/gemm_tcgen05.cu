@@ -23,8 +23,16 @@ namespace ssl4p {
 constexpr int BM = 128;          // tile rows (UMMA M, cta_group::1)
 constexpr int BK = 64;           // K per stage: 64 bf16 = 128 B = one SWIZZLE_128B row
 constexpr int UMMA_K = 16;
-constexpr int kGemmThreads = 320;
-constexpr int kEpiWarps = 8;
+// Epilogue warps: 16 for the GELU / dGELU epilogues, 8 otherwise.  At K = 512..768 every part of those two epilogues
+// (tcgen05.ld, transpose, erf math or the gelu' operand load, stores) adds to a per-warp chain longer than the main loop of
+// the tile (scripts/gemm_dbg_sweep.sh); splitting it over twice the warps gives 144 -> 130 us and 140 -> 119 us at the
+// decoder shape.  The price is 64 KB of transpose patches (4 KB per warp), i.e. one pipeline stage less, which costs the
+// plain bf16 epilogues at K >= 1536 more than they gain - they stay at 8 warps.
+__host__ __device__ constexpr bool epi_out_f32(int epi) {
+    return epi == SSL4P_EPI_BIAS_RESIDUAL_F32 || epi == SSL4P_EPI_BIAS_F32 || epi == SSL4P_EPI_PARTIAL_F32;
+}
+__host__ __device__ constexpr int epi_warps(int epi) { return (epi == SSL4P_EPI_BIAS_GELU_BF16 || epi == SSL4P_EPI_DGELU_BF16) ? 16 : 8; }
+__host__ __device__ constexpr int gemm_threads(int epi) { return 64 + 32 * epi_warps(epi); }
 
 struct GemmParams {
     int M, N, K;                 // C[M,N] = sum_k A[m,k] B[n,k]
@@ -38,16 +46,16 @@ struct GemmParams {
     long long split_stride;      // elements between split-K partial planes of C
 };
 
-template <int BN, bool A_MN, bool B_MN>
+template <int BN, bool A_MN, bool B_MN, int EPI>
 struct SmemLayout {
     static constexpr int kABytes = BM * BK * 2;
     static constexpr int kBBytes = BN * BK * 2;
     static constexpr int kStageBytes = kABytes + kBBytes;
-    static constexpr int kBudget = 192 * 1024;
+    static constexpr int kEpiBytes = epi_warps(EPI) * 32 * 32 * 4;     // per-warp transpose patches of the epilogue
+    static constexpr int kBudget = 224 * 1024 - kEpiBytes;
     static constexpr int kStagesRaw = kBudget / kStageBytes;
     static constexpr int kStages = kStagesRaw > 8 ? 8 : kStagesRaw;
     static constexpr int kBarBytes = 1024;
-    static constexpr int kEpiBytes = kEpiWarps * 32 * 32 * 4;          // per-warp transpose patches of the epilogue
     static constexpr int kTotal = kStages * kStageBytes + kBarBytes + kEpiBytes + 1024 /*align slack*/;
 };
 
@@ -66,9 +74,9 @@ __device__ __forceinline__ float4 shfl_f4(float4 v, int src) {
 }
 // The bias of the <= 4 column chunks a warp handles in one tile (4 x 32 floats), one float4 per lane: lane 8k + j holds
 // columns [n0 + chunk0 + 64 k + 4 j, +4).  Loaded BEFORE the wait for the accumulator, so its latency is never exposed.
-__device__ __forceinline__ float4 load_bias_lane(const GemmParams& p, int n0, int chunk0) {
+__device__ __forceinline__ float4 load_bias_lane(const GemmParams& p, int n0, int chunk0, int chunk_step) {
     const int lane = (int)lane_id();
-    const int col = n0 + chunk0 + (lane >> 3) * 64 + (lane & 7) * 4;
+    const int col = n0 + chunk0 + (lane >> 3) * chunk_step + (lane & 7) * 4;
     if (p.bias == nullptr || col >= p.N) return make_float4(0.f, 0.f, 0.f, 0.f);
     return __ldg(reinterpret_cast<const float4*>(p.bias + col));
 }
@@ -206,10 +214,12 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, uint32_t stg
 
 // ---- the kernel ---------------------------------------------------------------------------------
 template <int BN, bool A_MN, bool B_MN, int EPI>
-__global__ void __launch_bounds__(kGemmThreads, 1)
+__global__ void __launch_bounds__(gemm_threads(EPI), 1)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmParams p) {
-    using L = SmemLayout<BN, A_MN, B_MN>;
+    using L = SmemLayout<BN, A_MN, B_MN, EPI>;
     constexpr int kStages = L::kStages;
+    constexpr int kEpiWarps = epi_warps(EPI);
+    constexpr int kChunkStep = (kEpiWarps / 4) * 32;          // columns between two chunks of the same warp
     constexpr uint32_t kTmemCols = 512;                      // 2 accumulators x up to 256 columns
     constexpr uint32_t kAccStride = 256;
 
@@ -342,17 +352,17 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             constexpr bool kBias = EPI == SSL4P_EPI_BIAS_BF16 || EPI == SSL4P_EPI_BIAS_GELU_BF16 || EPI == SSL4P_EPI_BIAS_RESIDUAL_F32 ||
                                    EPI == SSL4P_EPI_BIAS_F32;
             float4 bias_lane = make_float4(0.f, 0.f, 0.f, 0.f);
-            if constexpr (kBias) bias_lane = load_bias_lane(p, n0, chunk0);
+            if constexpr (kBias) bias_lane = load_bias_lane(p, n0, chunk0, kChunkStep);
             mbar_wait(&tmem_full[acc], acc_phase);
             tc_fence_after();
             const uint32_t stg = smem_u32(epi_stage) + (warp - 2) * kStageBytesPerWarp;
             const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + acc * kAccStride;
             const bool empty_split = split * p.k_per_split >= p.K;   // empty split-K range: the accumulator was never written
 #pragma unroll 1
-            for (int c = chunk0; c < BN; c += 64) {
+            for (int c = chunk0; c < BN; c += kChunkStep) {
                 const int col0 = n0 + c;
                 if (col0 >= p.N) break;
-                if constexpr (kAux) if (c + 64 < BN) load_aux<EPI>(p, row_base, col0 + 64, aux_nxt);
+                if constexpr (kAux) if (c + kChunkStep < BN) load_aux<EPI>(p, row_base, col0 + kChunkStep, aux_nxt);
                 uint32_t r[32];
                 tmem_ld_32x32(taddr + c, r);
                 tmem_ld_wait();
@@ -360,7 +370,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 #pragma unroll
                     for (int j = 0; j < 32; ++j) r[j] = 0u;
                 }
-                if (row_base < p.M) epilogue_chunk<EPI>(p, stg, row_base, col0, split, r, aux_cur, bias_lane, (c - chunk0) >> 6);
+                if (row_base < p.M) epilogue_chunk<EPI>(p, stg, row_base, col0, split, r, aux_cur, bias_lane, (c - chunk0) / kChunkStep);
                 if constexpr (kAux) aux_cur = aux_nxt;
             }
             tc_fence_before();
@@ -425,7 +435,7 @@ static int make_tmap(CUtensorMap* out, const void* ptr, long long inner, long lo
 
 template <int BN, bool A_MN, bool B_MN, int EPI>
 static int launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p, cudaStream_t stream) {
-    using L = SmemLayout<BN, A_MN, B_MN>;
+    using L = SmemLayout<BN, A_MN, B_MN, EPI>;
     auto kern = gemm_tcgen05_kernel<BN, A_MN, B_MN, EPI>;
     static bool attr_set = false;
     if (!attr_set) {
@@ -435,7 +445,7 @@ static int launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmPara
     const int mt = (p.M + BM - 1) / BM, nt = (p.N + BN - 1) / BN;
     const int total = mt * nt * p.splits;
     const int grid = total < num_sms() ? total : num_sms();
-    kern<<<grid, kGemmThreads, L::kTotal, stream>>>(tmA, tmB, p);
+    kern<<<grid, gemm_threads(EPI), L::kTotal, stream>>>(tmA, tmB, p);
     return check_launch("gemm_tcgen05_kernel");
 }
 
