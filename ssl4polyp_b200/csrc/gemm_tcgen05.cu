@@ -348,7 +348,22 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             const int row_base = m0 + q * 32;
             constexpr bool kAux = EPI == SSL4P_EPI_BIAS_RESIDUAL_F32 || EPI == SSL4P_EPI_DGELU_BF16;
             AuxRegs aux_cur, aux_nxt;
-            if constexpr (kAux) load_aux<EPI>(p, row_base, n0 + chunk0, aux_cur);      // in flight while the MMAs of the tile finish
+            // Second epilogue operand.  dGELU (16 warps: at most kNC = 2 chunks per warp and tile): ALL of the tile's gelu'
+            // values of this warp are requested before the accumulator wait - with one chunk of look-ahead the load latency
+            // was the critical chain of the kernel (117 us with everything else switched off).  Residual (8 warps, 4 chunks,
+            // 32 registers per chunk): one chunk ahead.
+            constexpr bool kAuxAll = EPI == SSL4P_EPI_DGELU_BF16;
+            constexpr int kNC = (BN + kChunkStep - 1) / kChunkStep;
+            AuxRegs aux_all[kAuxAll ? kNC : 1];
+            if constexpr (kAuxAll) {
+#pragma unroll
+                for (int ci = 0; ci < kNC; ++ci) {
+                    const int c = chunk0 + ci * kChunkStep;
+                    if (c < BN && n0 + c < p.N) load_aux<EPI>(p, row_base, n0 + c, aux_all[ci]);
+                }
+            } else if constexpr (kAux) {
+                load_aux<EPI>(p, row_base, n0 + chunk0, aux_cur);      // in flight while the MMAs of the tile finish
+            }
             constexpr bool kBias = EPI == SSL4P_EPI_BIAS_BF16 || EPI == SSL4P_EPI_BIAS_GELU_BF16 || EPI == SSL4P_EPI_BIAS_RESIDUAL_F32 ||
                                    EPI == SSL4P_EPI_BIAS_F32;
             float4 bias_lane = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -358,6 +373,19 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             const uint32_t stg = smem_u32(epi_stage) + (warp - 2) * kStageBytesPerWarp;
             const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + acc * kAccStride;
             const bool empty_split = split * p.k_per_split >= p.K;   // empty split-K range: the accumulator was never written
+            if constexpr (kAuxAll) {
+#pragma unroll
+                for (int ci = 0; ci < kNC; ++ci) {
+                    const int c = chunk0 + ci * kChunkStep;
+                    const int col0 = n0 + c;
+                    if (c < BN && col0 < p.N) {
+                        uint32_t r[32];
+                        tmem_ld_32x32(taddr + c, r);
+                        tmem_ld_wait();
+                        if (row_base < p.M) epilogue_chunk<EPI>(p, stg, row_base, col0, split, r, aux_all[ci], bias_lane, ci);
+                    }
+                }
+            } else
 #pragma unroll 1
             for (int c = chunk0; c < BN; c += kChunkStep) {
                 const int col0 = n0 + c;
