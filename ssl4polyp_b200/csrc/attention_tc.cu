@@ -666,10 +666,11 @@ attention_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_
                     }
                     pend_kt = kt; pend_kt_hh = hh; pend_b = b; pend_sl = sl;
                 }
-                pend_dq_hh = hh;
-                if (hh == HP - 1) { write_dvk(); write_dq(); }   // last head of the item: nothing left to hide behind
+                pend_dq_hh = hh;                                 // read out inside the next half block (of the next item, if any)
             }
         }
+        if (pend_kt >= 0) write_dvk();                            // the CTA's last item: nothing left to hide behind
+        if (pend_dq_hh >= 0) write_dq();
     }
 
     tc_fence_before();
