@@ -374,16 +374,17 @@ attention_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_
     float* sL = reinterpret_cast<float*>(smem + 12 * kTileBytes);   // [HP][256] lse * log2e (+inf for q >= T)
     float* sD = sL + HP * 256;                                      // [HP][256] D * scale
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 12 * kTileBytes + 4096);
-    uint64_t* in_full = bars;
-    uint64_t* in_empty = bars + 1;
-    uint64_t* st_full = bars + 2;                                // [2] scores of half block j in TMEM buffer j & 1
-    uint64_t* pt_full = bars + 4;                                // [2] P^T / dS^T of half block j in shared memory, buffer drained
-    uint64_t* blk_done = bars + 6;                               // all tensor reads of a block's P^T / dS^T retired
-    uint64_t* dvk_full = bars + 7;
-    uint64_t* dvk_empty = bars + 8;
-    uint64_t* dq_full = bars + 9;
-    uint64_t* dq_empty = bars + 10;
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 11);
+    uint64_t* in_full = bars;                                    // [2] operand stages: one-tile sequences (T <= 128) use the two
+    uint64_t* in_empty = bars + 2;                               // [2] tiles of every operand buffer as a 2-deep ring of items
+    uint64_t* st_full = bars + 4;                                // [2] scores of half block j in TMEM buffer j & 1
+    uint64_t* pt_full = bars + 6;                                // [2] P^T / dS^T of half block j in shared memory, buffer drained
+    uint64_t* blk_done = bars + 8;                               // all tensor reads of a block's P^T / dS^T retired
+    uint64_t* dvk_full = bars + 9;
+    uint64_t* dvk_empty = bars + 10;
+    uint64_t* dq_full = bars + 11;
+    uint64_t* dq_empty = bars + 12;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 13);
+    const bool ring = p.NB == 1;                                 // item il lives in stage il & 1, otherwise always stage 0
 
     const int warp = threadIdx.x >> 5;
     const int lane = lane_id();
@@ -393,7 +394,7 @@ attention_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_
     if (warp == 8 && lane == 0) { tma_prefetch_desc(&tmQKV); tma_prefetch_desc(&tmDO); }
     if (warp == 9) {
         if (lane == 0) {
-            mbar_init(in_full, 1); mbar_init(in_empty, 1);
+            for (int i = 0; i < 2; ++i) { mbar_init(&in_full[i], 1); mbar_init(&in_empty[i], 1); }
             for (int i = 0; i < 2; ++i) { mbar_init(&st_full[i], 1); mbar_init(&pt_full[i], 256); }
             mbar_init(blk_done, 1);
             mbar_init(dvk_full, 1); mbar_init(dvk_empty, 256);
@@ -415,17 +416,19 @@ attention_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_
             for (int il = 0; il < my_items; ++il) {
                 const int item = blockIdx.x + il * gridDim.x;
                 const int b = item / p.slices_per_img, sl = item % p.slices_per_img;
-                mbar_wait(in_empty, (il & 1) ^ 1);
-                mbar_expect_tx(in_full, (uint32_t)(4 * p.NB) * kTileBytes);
+                const int stage = ring ? (il & 1) : 0, use = ring ? (il >> 1) : il;
+                mbar_wait(&in_empty[stage], (use & 1) ^ 1);
+                mbar_expect_tx(&in_full[stage], (uint32_t)(4 * p.NB) * kTileBytes);
                 for (int i = 0; i < p.NB; ++i) {
-                    tma_load_3d(sQ + i * kTileBytes, &tmQKV, in_full, sl * 64, i * 128, b);
-                    tma_load_3d(sK + i * kTileBytes, &tmQKV, in_full, HHD + sl * 64, i * 128, b);
-                    tma_load_3d(sV + i * kTileBytes, &tmQKV, in_full, 2 * HHD + sl * 64, i * 128, b);
-                    tma_load_3d(sDO + i * kTileBytes, &tmDO, in_full, sl * 64, i * 128, b);
+                    const int slot = (stage + i) * kTileBytes;
+                    tma_load_3d(sQ + slot, &tmQKV, &in_full[stage], sl * 64, i * 128, b);
+                    tma_load_3d(sK + slot, &tmQKV, &in_full[stage], HHD + sl * 64, i * 128, b);
+                    tma_load_3d(sV + slot, &tmQKV, &in_full[stage], 2 * HHD + sl * 64, i * 128, b);
+                    tma_load_3d(sDO + slot, &tmDO, &in_full[stage], sl * 64, i * 128, b);
                 }
                 // the operands are single buffered: pull the next item's boxes into L2 now, so that the loads issued
                 // after this item's last MMA pay L2 latency instead of HBM latency
-                if (il + 1 < my_items) {
+                if (!ring && il + 1 < my_items) {
                     const int item2 = item + gridDim.x;
                     const int b2 = item2 / p.slices_per_img, sl2_ = item2 % p.slices_per_img;
                     for (int i = 0; i < p.NB; ++i) {
@@ -441,7 +444,8 @@ attention_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_
     } else if (warp == 9) {
         // ===================== MMA issuer =====================
         if (lane == 0) {
-            const uint32_t sQa = smem_u32(sQ), sKa = smem_u32(sK), sVa = smem_u32(sV), sDOa = smem_u32(sDO);
+            uint32_t sQa = smem_u32(sQ), sKa = smem_u32(sK), sVa = smem_u32(sV), sDOa = smem_u32(sDO);   // + stage offset per item
+            const uint32_t sQ0 = sQa, sK0 = sKa, sV0 = sVa, sDO0 = sDOa;
             const uint32_t sPTa = smem_u32(sPT), sDSa = smem_u32(sDS);
             const uint32_t idesc_acc = idesc_rt(128, 64, false, true);     // A K-major (P^T / dS^T rows = keys), B MN-major
             const uint32_t idesc_dq = idesc_rt(128, 64, true, true);       // A MN-major (dS^T read as [keys][queries]), B MN-major
@@ -463,8 +467,10 @@ attention_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_
                 umma_commit(&st_full[jj & 1]);
             };
             for (int il = 0; il < my_items; ++il) {
-                mbar_wait(in_full, il & 1);
+                const int stage = ring ? (il & 1) : 0, use = ring ? (il >> 1) : il;
+                mbar_wait(&in_full[stage], use & 1);
                 tc_fence_after();
+                sQa = sQ0 + stage * kTileBytes; sKa = sK0 + stage * kTileBytes; sVa = sV0 + stage * kTileBytes; sDOa = sDO0 + stage * kTileBytes;
                 HalfBlk ahead{0, 0, 0, 0};                        // next half block whose scores have not been issued
                 int ja = j;
                 for (int i = 0; i < 2 && ahead.hh < HP; ++i) { issue_scores(ahead, ja++); ahead.next(p.Npad, p.NB); }
@@ -500,7 +506,7 @@ attention_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_
                     }
                     if (ahead.hh < HP) { issue_scores(ahead, ja++); ahead.next(p.Npad, p.NB); }   // refill the buffer just drained
                 }
-                umma_commit(in_empty);
+                umma_commit(&in_empty[stage]);
             }
         }
         __syncwarp();
