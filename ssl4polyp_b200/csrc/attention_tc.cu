@@ -61,11 +61,14 @@ attention_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnFwd
     uint64_t* qk_empty = bars + 1;                               // all S MMAs of the item retired: Q/K may be overwritten
     uint64_t* v_full = bars + 10;                                // V of the item landed
     uint64_t* v_empty = bars + 11;                               // all P V MMAs of the item retired
+    // one-tile sequences (T <= 128): the two tiles of each operand buffer form a 2-deep ring of items; stage 1 barriers:
+    uint64_t* qk_full1 = bars + 12; uint64_t* qk_empty1 = bars + 13; uint64_t* v_full1 = bars + 14; uint64_t* v_empty1 = bars + 15;
+    const bool ring = p.NB == 1 && p.NKB == 1;
     uint64_t* s_full = bars + 2;                                 // [2]
     uint64_t* p_full = bars + 4;                                 // [2]
     uint64_t* o_full = bars + 6;                                 // [2]
     uint64_t* s_empty = bars + 8;                                // [2]
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 12);
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 16);
 
     const int warp = threadIdx.x >> 5;
     const int lane = lane_id();
@@ -78,6 +81,8 @@ attention_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnFwd
         if (lane == 0) {
             mbar_init(qk_full, 1); mbar_init(qk_empty, NT);
             mbar_init(v_full, 1); mbar_init(v_empty, NT);
+            mbar_init(qk_full1, 1); mbar_init(qk_empty1, NT);
+            mbar_init(v_full1, 1); mbar_init(v_empty1, NT);
             for (int i = 0; i < 2; ++i) {
                 mbar_init(&s_full[i], 1); mbar_init(&p_full[i], 128); mbar_init(&o_full[i], 1); mbar_init(&s_empty[i], 128);
             }
@@ -101,14 +106,18 @@ attention_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnFwd
                 const int b = item / p.slices_per_img, sl = item % p.slices_per_img;
                 // Q/K are dead once the item's S MMAs have retired (about half way through the item), V after its last
                 // P V: two barrier pairs, so the next item's Q/K arrive while this item is still in its softmax
-                mbar_wait(qk_empty, (il & 1) ^ 1);
-                mbar_expect_tx(qk_full, (uint32_t)(p.NB + p.NKB) * kTileBytes);
-                for (int i = 0; i < p.NB; ++i) tma_load_3d(sQ + i * kTileBytes, &tmQKV, qk_full, sl * 64, i * 128, b);
-                for (int i = 0; i < p.NKB; ++i) tma_load_3d(sK + i * kTileBytes, &tmQKV, qk_full, HHD + sl * 64, i * 128, b);
-                mbar_wait(v_empty, (il & 1) ^ 1);
-                mbar_expect_tx(v_full, (uint32_t)p.NKB * kTileBytes);
-                for (int i = 0; i < p.NKB; ++i) tma_load_3d(sV + i * kTileBytes, &tmQKV, v_full, 2 * HHD + sl * 64, i * 128, b);
-                if (il + 1 < my_items) {                          // single-buffered operands: warm L2 with the next item's boxes
+                const int stage = ring ? (il & 1) : 0, use = ring ? (il >> 1) : il;
+                uint64_t* qf = stage ? qk_full1 : qk_full; uint64_t* qe = stage ? qk_empty1 : qk_empty;
+                uint64_t* vf = stage ? v_full1 : v_full;   uint64_t* ve = stage ? v_empty1 : v_empty;
+                const int so = stage * kTileBytes;
+                mbar_wait(qe, (use & 1) ^ 1);
+                mbar_expect_tx(qf, (uint32_t)(p.NB + p.NKB) * kTileBytes);
+                for (int i = 0; i < p.NB; ++i) tma_load_3d(sQ + so + i * kTileBytes, &tmQKV, qf, sl * 64, i * 128, b);
+                for (int i = 0; i < p.NKB; ++i) tma_load_3d(sK + so + i * kTileBytes, &tmQKV, qf, HHD + sl * 64, i * 128, b);
+                mbar_wait(ve, (use & 1) ^ 1);
+                mbar_expect_tx(vf, (uint32_t)p.NKB * kTileBytes);
+                for (int i = 0; i < p.NKB; ++i) tma_load_3d(sV + so + i * kTileBytes, &tmQKV, vf, 2 * HHD + sl * 64, i * 128, b);
+                if (!ring && il + 1 < my_items) {                 // single-buffered operands: warm L2 with the next item's boxes
                     const int item2 = item + gridDim.x;
                     const int b2 = item2 / p.slices_per_img, s2 = item2 % p.slices_per_img;
                     for (int i = 0; i < p.NKB; ++i) {
@@ -137,18 +146,22 @@ attention_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnFwd
                 const int u = s_done[w], g = 2 * u + w;
                 if (g >= total) return false;
                 const int il = g / NT, t = g - il * NT;
-                if (loaded <= il && mbar_test_wait(qk_full, loaded & 1)) ++loaded;    // the barrier is at most one phase ahead
+                if (loaded <= il) {                                                   // items land in order; a barrier is at most one phase ahead
+                    const bool ok = ring ? mbar_test_wait((loaded & 1) ? qk_full1 : qk_full, (loaded >> 1) & 1) : mbar_test_wait(qk_full, loaded & 1);
+                    if (ok) ++loaded;
+                }
                 if (loaded <= il) return false;
                 if (!sep && !mbar_test_wait(&s_empty[w], (u & 1) ^ 1)) return false;  // alias plan: O of the previous tile read out
                 tc_fence_after();
                 const int hh = t / p.NB, mb = t - hh * p.NB;
-                const uint32_t a0 = sQa + mb * kTileBytes + hh * (HD * 2);
-                const uint32_t b0 = sKa + hh * (HD * 2);
+                const uint32_t so = ring ? (uint32_t)(il & 1) * kTileBytes : 0u;
+                const uint32_t a0 = sQa + so + mb * kTileBytes + hh * (HD * 2);
+                const uint32_t b0 = sKa + so + hh * (HD * 2);
 #pragma unroll
                 for (int kk = 0; kk < HD / 16; ++kk)
                     umma_bf16(tmem_base + s_col[w], umma_smem_desc(a0 + kk * 32, 16, 1024), umma_smem_desc(b0 + kk * 32, 16, 1024), idesc_s, kk > 0);
                 umma_commit(&s_full[w]);
-                umma_commit(qk_empty);
+                umma_commit((ring && (il & 1)) ? qk_empty1 : qk_empty);
                 ++s_done[w];
                 return true;
             };
@@ -163,17 +176,21 @@ attention_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnFwd
                     tc_fence_after();
                     // sep plan: P(g) complete means S(g) has been consumed -> the chain's next S goes first, then P V
                     if (sep && s_done[w] == u + 1) try_issue_s(w);
-                    if (loaded_v <= il && mbar_test_wait(v_full, loaded_v & 1)) ++loaded_v;
+                    if (loaded_v <= il) {
+                        const bool ok = ring ? mbar_test_wait((loaded_v & 1) ? v_full1 : v_full, (loaded_v >> 1) & 1) : mbar_test_wait(v_full, loaded_v & 1);
+                        if (ok) ++loaded_v;
+                    }
                     if (loaded_v <= il) continue;                 // V not there yet: come back (p_full stays complete)
                     tc_fence_after();
                     const uint32_t pa = sPa + (uint32_t)w * 4u * kTileBytes;
                     const int ksteps = p.Npad >> 4;
+                    const uint32_t vso = ring ? (uint32_t)(il & 1) * kTileBytes : 0u;
                     const uint32_t voff = (HD == 32) ? (uint32_t)(t / p.NB) * 64u : 0u;   // head of the pair: +64 B inside the 128 B row
                     for (int ks = 0; ks < ksteps; ++ks)
                         umma_bf16(tmem_base + o_col[w], umma_smem_desc(pa + (ks >> 2) * kTileBytes + (ks & 3) * 32, 16, 1024),
-                                  umma_smem_desc(sVa + ks * 2048 + voff, kTileBytes, 1024), idesc_o, ks > 0);
+                                  umma_smem_desc(sVa + vso + ks * 2048 + voff, kTileBytes, 1024), idesc_o, ks > 0);
                     umma_commit(&o_full[w]);
-                    umma_commit(v_empty);
+                    umma_commit((ring && (il & 1)) ? v_empty1 : v_empty);
                     nxt[w] = g + 2;
                 }
             }
