@@ -135,6 +135,11 @@ def test_mae_small_config_against_oracle():
                       decoder_num_heads=2, norm_pix_loss=True)
     _check_against_oracle(m, cfg, B=3, seed=4, mr=0.75, size=64)
     _check_against_oracle(m, cfg, B=5, seed=6, mr=0.5, size=64)
+    # edges of random_masking (models_mae.py:123-148): a single image; nothing masked away from the encoder except one patch
+    # (len_keep = L - 1); almost everything masked (len_keep = 1: the encoder sees the cls token and one patch)
+    _check_against_oracle(m, cfg, B=1, seed=8, mr=0.75, size=64)
+    _check_against_oracle(m, cfg, B=2, seed=9, mr=0.05, size=64)
+    _check_against_oracle(m, cfg, B=4, seed=10, mr=0.9, size=64)
 
 
 def test_forward_draws_the_reference_noise():
