@@ -212,10 +212,49 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, uint32_t stg
     }
 }
 
+// TMA store of one [32 rows x 32 bf16] box from shared memory (SWIZZLE_64B layout) to the output; rows / columns
+// beyond the tensor are clipped by the hardware
+__device__ __forceinline__ void tma_store_2d(const CUtensorMap* m, uint32_t smem_src, int c0, int c1) {
+    asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
+                 ::"l"(reinterpret_cast<uint64_t>(m)), "r"(smem_src), "r"(c0), "r"(c1) : "memory");
+    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+}
+__device__ __forceinline__ void tma_store_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void tma_store_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+
+// EPI_BIAS_BF16 through TMA: the lane keeps its row (the tcgen05.ld layout), adds the bias, packs to bf16 and writes 64
+// bytes into the [32 x 64 B] patch (16-byte chunk c of row r at c ^ ((r >> 1) & 3) = SWIZZLE_64B); one lane hands the
+// box to the TMA unit.  No read-back, no per-thread global stores.
+__device__ __forceinline__ void epilogue_chunk_tma(const CUtensorMap* tmC, const GemmParams& p, uint32_t stg, int row_base, int col0,
+                                                   uint32_t (&acc)[32], const float4 bias_lane, const int kchunk) {
+    const int lane = (int)lane_id();
+    uint32_t w[16];
+    if (p.bias != nullptr) {
+#pragma unroll
+        for (int j4 = 0; j4 < 8; ++j4) {
+            const float4 b = shfl_f4(bias_lane, kchunk * 8 + j4);
+            w[2 * j4] = pack_bf16(__uint_as_float(acc[4 * j4]) + b.x, __uint_as_float(acc[4 * j4 + 1]) + b.y);
+            w[2 * j4 + 1] = pack_bf16(__uint_as_float(acc[4 * j4 + 2]) + b.z, __uint_as_float(acc[4 * j4 + 3]) + b.w);
+        }
+    } else {
+#pragma unroll
+        for (int j = 0; j < 16; ++j) w[j] = pack_bf16(__uint_as_float(acc[2 * j]), __uint_as_float(acc[2 * j + 1]));
+    }
+    if (lane == 0) tma_store_wait_read();                          // the previous box of this patch has left shared memory
+    __syncwarp();
+#pragma unroll
+    for (int c = 0; c < 4; ++c)
+        sts_v4(stg + lane * 64 + ((c ^ ((lane >> 1) & 3)) << 4), w[4 * c], w[4 * c + 1], w[4 * c + 2], w[4 * c + 3]);
+    fence_proxy_async();
+    __syncwarp();
+    if (lane == 0) tma_store_2d(tmC, stg, col0, row_base);
+}
+
 // ---- the kernel ---------------------------------------------------------------------------------
 template <int BN, bool A_MN, bool B_MN, int EPI>
 __global__ void __launch_bounds__(gemm_threads(EPI), 1)
-gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmParams p) {
+gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                    const __grid_constant__ CUtensorMap tmC, const GemmParams p) {
     using L = SmemLayout<BN, A_MN, B_MN, EPI>;
     constexpr int kStages = L::kStages;
     constexpr int kEpiWarps = epi_warps(EPI);
@@ -398,6 +437,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 #pragma unroll
                     for (int j = 0; j < 32; ++j) r[j] = 0u;
                 }
+                if constexpr (EPI == SSL4P_EPI_BIAS_BF16) {
+                    if (row_base < p.M) epilogue_chunk_tma(&tmC, p, stg, row_base, col0, r, bias_lane, (c - chunk0) / kChunkStep);
+                } else
                 if (row_base < p.M) epilogue_chunk<EPI>(p, stg, row_base, col0, split, r, aux_cur, bias_lane, (c - chunk0) / kChunkStep);
                 if constexpr (kAux) aux_cur = aux_nxt;
             }
@@ -408,6 +450,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         }
     }
 
+    if constexpr (EPI == SSL4P_EPI_BIAS_BF16) {
+        if (warp >= 2 && lane_id() == 0) tma_store_wait_all();     // shared memory must outlive the bulk stores
+    }
     tc_fence_before();
     __syncthreads();
     if (warp == 1) {
@@ -461,8 +506,22 @@ static int make_tmap(CUtensorMap* out, const void* ptr, long long inner, long lo
     return SSL4P_OK;
 }
 
+// bf16 output as a 2-D tensor map for TMA stores: box = 32 columns x 32 rows (one epilogue chunk), SWIZZLE_64B
+static int make_tmap_out(CUtensorMap* out, void* ptr, long long cols, long long rows, long long ld) {
+    EncodeTiledFn enc = get_encode_fn();
+    if (!enc) { set_error("cuTensorMapEncodeTiled entry point unavailable (no CUDA driver?)"); return SSL4P_ERR_CUDA; }
+    cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+    cuuint64_t strides[1] = {(cuuint64_t)ld * 2};
+    cuuint32_t box[2] = {32u, 32u};
+    cuuint32_t estr[2] = {1u, 1u};
+    CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, ptr, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                     CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled (output) failed (CUresult %d) cols=%lld rows=%lld ld=%lld", (int)r, cols, rows, ld); return SSL4P_ERR_CUDA; }
+    return SSL4P_OK;
+}
+
 template <int BN, bool A_MN, bool B_MN, int EPI>
-static int launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p, cudaStream_t stream) {
+static int launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC, const GemmParams& p, cudaStream_t stream) {
     using L = SmemLayout<BN, A_MN, B_MN, EPI>;
     auto kern = gemm_tcgen05_kernel<BN, A_MN, B_MN, EPI>;
     static bool attr_set = false;
@@ -473,28 +532,28 @@ static int launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmPara
     const int mt = (p.M + BM - 1) / BM, nt = (p.N + BN - 1) / BN;
     const int total = mt * nt * p.splits;
     const int grid = total < num_sms() ? total : num_sms();
-    kern<<<grid, gemm_threads(EPI), L::kTotal, stream>>>(tmA, tmB, p);
+    kern<<<grid, gemm_threads(EPI), L::kTotal, stream>>>(tmA, tmB, tmC, p);
     return check_launch("gemm_tcgen05_kernel");
 }
 
 // Only the (layout, epilogue) pairs the model uses are instantiated.
 template <int BN>
-static int dispatch(int layout, int epi, const CUtensorMap& a, const CUtensorMap& b, const GemmParams& p, cudaStream_t s) {
+static int dispatch(int layout, int epi, const CUtensorMap& a, const CUtensorMap& b, const CUtensorMap& c, const GemmParams& p, cudaStream_t s) {
     if (layout == SSL4P_GEMM_NT) {
         switch (epi) {
-            case SSL4P_EPI_BIAS_BF16: return launch<BN, false, false, SSL4P_EPI_BIAS_BF16>(a, b, p, s);
-            case SSL4P_EPI_BIAS_GELU_BF16: return launch<BN, false, false, SSL4P_EPI_BIAS_GELU_BF16>(a, b, p, s);
-            case SSL4P_EPI_BIAS_RESIDUAL_F32: return launch<BN, false, false, SSL4P_EPI_BIAS_RESIDUAL_F32>(a, b, p, s);
-            case SSL4P_EPI_BIAS_F32: return launch<BN, false, false, SSL4P_EPI_BIAS_F32>(a, b, p, s);
+            case SSL4P_EPI_BIAS_BF16: return launch<BN, false, false, SSL4P_EPI_BIAS_BF16>(a, b, c, p, s);
+            case SSL4P_EPI_BIAS_GELU_BF16: return launch<BN, false, false, SSL4P_EPI_BIAS_GELU_BF16>(a, b, c, p, s);
+            case SSL4P_EPI_BIAS_RESIDUAL_F32: return launch<BN, false, false, SSL4P_EPI_BIAS_RESIDUAL_F32>(a, b, c, p, s);
+            case SSL4P_EPI_BIAS_F32: return launch<BN, false, false, SSL4P_EPI_BIAS_F32>(a, b, c, p, s);
         }
     } else if (layout == SSL4P_GEMM_NN) {
         switch (epi) {
-            case SSL4P_EPI_BIAS_BF16: return launch<BN, false, true, SSL4P_EPI_BIAS_BF16>(a, b, p, s);
-            case SSL4P_EPI_DGELU_BF16: return launch<BN, false, true, SSL4P_EPI_DGELU_BF16>(a, b, p, s);
+            case SSL4P_EPI_BIAS_BF16: return launch<BN, false, true, SSL4P_EPI_BIAS_BF16>(a, b, c, p, s);
+            case SSL4P_EPI_DGELU_BF16: return launch<BN, false, true, SSL4P_EPI_DGELU_BF16>(a, b, c, p, s);
         }
     } else {
         switch (epi) {
-            case SSL4P_EPI_PARTIAL_F32: return launch<BN, true, true, SSL4P_EPI_PARTIAL_F32>(a, b, p, s);
+            case SSL4P_EPI_PARTIAL_F32: return launch<BN, true, true, SSL4P_EPI_PARTIAL_F32>(a, b, c, p, s);
         }
     }
     set_error("gemm: epilogue %d is not available for layout %d", epi, layout);
@@ -584,10 +643,12 @@ extern "C" int ssl4p_gemm_bf16(const void* A, const void* B, void* C, void* C2, 
     else       rc = make_tmap(&tmB, B, N, K, ldb, BK);            // B stored [K,N], N contiguous
     if (rc) return rc;
 
-    if (bn == 256) return dispatch<256>(layout, epilogue, tmA, tmB, p, stream);
-    if (bn == 192) return dispatch<192>(layout, epilogue, tmA, tmB, p, stream);
-    if (bn == 128) return dispatch<128>(layout, epilogue, tmA, tmB, p, stream);
-    if (bn == 64) return dispatch<64>(layout, epilogue, tmA, tmB, p, stream);
+    CUtensorMap tmC = tmA;                                         // placeholder unless the epilogue stores through TMA
+    if (epilogue == SSL4P_EPI_BIAS_BF16) { rc = make_tmap_out(&tmC, C, N, M, ldc); if (rc) return rc; }
+    if (bn == 256) return dispatch<256>(layout, epilogue, tmA, tmB, tmC, p, stream);
+    if (bn == 192) return dispatch<192>(layout, epilogue, tmA, tmB, tmC, p, stream);
+    if (bn == 128) return dispatch<128>(layout, epilogue, tmA, tmB, tmC, p, stream);
+    if (bn == 64) return dispatch<64>(layout, epilogue, tmA, tmB, tmC, p, stream);
     set_error("gemm: dispatch fell through");
     return SSL4P_ERR_ARG;
 }
