@@ -213,7 +213,10 @@ class ClassifierEngine(TrainEngine):
     """Fine-tune step (train_classification.py:4525-4546): logits -> BCE-with-logits on logit1-logit0 (2 classes,
     :3347-3374) or cross-entropy -> backward -> AdamW.  The loss over B x ncls scalars stays in torch."""
 
-    def __init__(self, model, lr, weight_decay=0.05, betas=(0.9, 0.999), pos_weight=None, **kw):
+    def __init__(self, model, lr, weight_decay=0.0, betas=(0.9, 0.999), pos_weight=None, **kw):
+        # train_classification.py:5751-5768: plain torch.optim.AdamW over head + backbone groups with ONE weight decay for
+        # every parameter (biases and LayerNorm included; default 0.0) - not timm's no-decay rule of the pretraining script
+        kw.setdefault("no_decay_rule", lambda name, p: False)
         super().__init__(model, lr, weight_decay, betas, **kw)
         self.pos_weight = pos_weight
 
@@ -238,3 +241,35 @@ def cosine_lr(it_epoch: float, lr: float, min_lr: float, warmup_epochs: float, e
     if it_epoch < warmup_epochs:
         return lr * it_epoch / warmup_epochs
     return min_lr + (lr - min_lr) * 0.5 * (1. + math.cos(math.pi * (it_epoch - warmup_epochs) / (epochs - warmup_epochs)))
+
+
+def finetune_cosine_factor(epoch: int, total_epochs: int, warmup_epochs: int = 0) -> float:
+    """Per-EPOCH lr multiplier of the fine-tune script's `--scheduler cosine` (train_classification.py:3943-3958, a
+    LambdaLR): linear warm-up (epoch+1)/warmup, then half cosine over the remaining epochs."""
+    if warmup_epochs > 0 and epoch < warmup_epochs:
+        return float(epoch + 1) / float(max(1, warmup_epochs))
+    progress = (epoch - warmup_epochs) / float(max(1, total_epochs - warmup_epochs))
+    progress = min(max(progress, 0.0), 1.0)
+    return 0.5 * (1.0 + math.cos(math.pi * progress))
+
+
+class PlateauLR:
+    """`--scheduler plateau` (train_classification.py:3959-3970): torch's ReduceLROnPlateau(mode="max", factor, patience,
+    min_lr) restated on a plain float, since the engine owns the learning rate (device scalar), not a torch optimizer.
+    `lr = sched.step(metric)` once per epoch; pass the result to `engine.step(..., lr=lr)`."""
+
+    def __init__(self, lr: float, factor: float = 0.5, patience: int = 2, min_lr: float = 1e-6, threshold: float = 1e-4, eps: float = 1e-8):
+        self.lr, self.factor, self.patience, self.min_lr, self.threshold, self.eps = lr, factor, patience, min_lr, threshold, eps
+        self.best, self.num_bad = -math.inf, 0
+
+    def step(self, metric: float) -> float:
+        if metric > self.best * (1.0 + self.threshold) if self.best > -math.inf else True:     # mode="max", threshold_mode="rel"
+            self.best, self.num_bad = metric, 0
+        else:
+            self.num_bad += 1
+        if self.num_bad > self.patience:
+            new_lr = max(self.lr * self.factor, self.min_lr)
+            if self.lr - new_lr > self.eps:
+                self.lr = new_lr
+            self.num_bad = 0
+        return self.lr

@@ -269,3 +269,32 @@ def test_main_pretrain_parser_matches_the_reference_flag_for_flag():
     assert ours["blr"] == 1e-3 and ours["warmup_epochs"] == 40 and ours["weight_decay"] == 0.05 and ours["precision"] == "amp"
     a = MP.get_args_parser().parse_args(["--acum_iter", "4", "--no_train_dir", "--save-freq-mins", "30", "--keep-last", "2"])
     assert a.accum_iter == 4 and a.no_train_dir and a.save_freq_mins == 30 and a.keep_last == 2
+
+
+def test_finetune_schedulers_match_torch():
+    """train_classification.py:3943-3971 `create_scheduler`: cosine LambdaLR and ReduceLROnPlateau(mode="max") on floats."""
+    from ssl4polyp_b200.engine import PlateauLR, finetune_cosine_factor
+    w = torch.nn.Parameter(torch.zeros(1))
+    opt = torch.optim.AdamW([w], lr=1e-3)
+    sch = torch.optim.lr_scheduler.LambdaLR(opt, lambda e: finetune_cosine_factor(e, 20, 3))
+    for e in range(20):
+        assert abs(opt.param_groups[0]["lr"] - 1e-3 * finetune_cosine_factor(e, 20, 3)) < 1e-12
+        opt.step(); sch.step()
+    assert finetune_cosine_factor(0, 20, 3) == 1 / 3 and finetune_cosine_factor(3, 20, 3) == 1.0 and finetune_cosine_factor(25, 20, 3) == 0.0
+    opt = torch.optim.AdamW([w], lr=1e-3)
+    ref = torch.optim.lr_scheduler.ReduceLROnPlateau(opt, mode="max", factor=0.5, patience=2, min_lr=1e-6)
+    ours = PlateauLR(1e-3, factor=0.5, patience=2, min_lr=1e-6)
+    metrics = [0.5, 0.6, 0.6, 0.59, 0.6, 0.61, 0.6, 0.6, 0.6, 0.6, 0.6, 0.6, 0.62, 0.1, 0.1, 0.1, 0.1, 0.1, 0.1, 0.1, 0.1, 0.1, 0.1]
+    for m in metrics:
+        ref.step(m)
+        assert abs(ours.step(m) - opt.param_groups[0]["lr"]) < 1e-15, m
+
+
+def test_classifier_engine_decays_every_parameter_like_the_reference():
+    """train_classification.py:5751-5768 builds torch.optim.AdamW with one weight decay for all parameters; the pretraining
+    script uses timm's rule (no decay for 1-D tensors and biases, main_pretrain.py:216-218)."""
+    import inspect
+    from ssl4polyp_b200 import engine
+    src = inspect.getsource(engine.ClassifierEngine.__init__)
+    assert "no_decay_rule" in src and "lambda name, p: False" in src
+    assert inspect.signature(engine.ClassifierEngine.__init__).parameters["weight_decay"].default == 0.0
