@@ -184,6 +184,10 @@ def b200_arm(args):
     dev = torch.device("cuda", local)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        # NCCL logs (its version banner included) go to stdout by default; stdout carries exactly ONE JSON line
+        if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
+            os.environ["NCCL_DEBUG"] = "WARN"
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         from ssl4polyp_b200.dp import configure_overlap
         configure_overlap(int(os.environ.get("SSL4P_DP_SMS", "0")))
         dist.init_process_group("nccl", device_id=dev)
