@@ -249,8 +249,13 @@ attention_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnFwd
                         tmem_ld_wait();
                         if (c + 32 < p.Npad) tmem_ld_32x32(taddr + c + 32, rb);
                         if (c + 32 <= p.T) {
+                            float m0 = mx, m1 = mx, m2 = mx, m3 = mx;
 #pragma unroll
-                            for (int jj = 0; jj < 32; ++jj) mx = fmaxf(mx, __uint_as_float(ra[jj]));
+                            for (int jj = 0; jj < 32; jj += 4) {
+                                m0 = fmaxf(m0, __uint_as_float(ra[jj])); m1 = fmaxf(m1, __uint_as_float(ra[jj + 1]));
+                                m2 = fmaxf(m2, __uint_as_float(ra[jj + 2])); m3 = fmaxf(m3, __uint_as_float(ra[jj + 3]));
+                            }
+                            mx = fmaxf(fmaxf(m0, m1), fmaxf(m2, m3));
                         } else {
 #pragma unroll
                             for (int jj = 0; jj < 32; ++jj) if (c + jj < p.T) mx = fmaxf(mx, __uint_as_float(ra[jj]));
@@ -259,8 +264,13 @@ attention_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnFwd
                         tmem_ld_wait();
                         if (c + 64 < p.Npad) tmem_ld_32x32(taddr + c + 64, ra);
                         if (c + 64 <= p.T) {
+                            float m0 = mx, m1 = mx, m2 = mx, m3 = mx;
 #pragma unroll
-                            for (int jj = 0; jj < 32; ++jj) mx = fmaxf(mx, __uint_as_float(rb[jj]));
+                            for (int jj = 0; jj < 32; jj += 4) {
+                                m0 = fmaxf(m0, __uint_as_float(rb[jj])); m1 = fmaxf(m1, __uint_as_float(rb[jj + 1]));
+                                m2 = fmaxf(m2, __uint_as_float(rb[jj + 2])); m3 = fmaxf(m3, __uint_as_float(rb[jj + 3]));
+                            }
+                            mx = fmaxf(fmaxf(m0, m1), fmaxf(m2, m3));
                         } else {
 #pragma unroll
                             for (int jj = 0; jj < 32; ++jj) if (c + 32 + jj < p.T) mx = fmaxf(mx, __uint_as_float(rb[jj]));
@@ -284,8 +294,12 @@ attention_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnFwd
 #pragma unroll
                         for (int jj = 0; jj < 32; ++jj) e[jj] = (c + jj < p.T) ? fast_exp2(fmaf(__uint_as_float(r[jj]), sl2, -msl)) : 0.f;
                     }
+                    {                                             // four independent chains (a single one costs 32 x 4 dependent cycles)
+                        float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
 #pragma unroll
-                    for (int jj = 0; jj < 32; ++jj) sum += e[jj];
+                        for (int jj = 0; jj < 32; jj += 4) { s0 += e[jj]; s1 += e[jj + 1]; s2 += e[jj + 2]; s3 += e[jj + 3]; }
+                        sum += (s0 + s1) + (s2 + s3);
+                    }
                     const uint32_t tile = pw + (c >> 6) * kTileBytes;
                     const int sub = (c & 63) >> 3;
 #pragma unroll

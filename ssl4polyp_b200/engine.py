@@ -213,12 +213,13 @@ class ClassifierEngine(TrainEngine):
     """Fine-tune step (train_classification.py:4525-4546): logits -> BCE-with-logits on logit1-logit0 (2 classes,
     :3347-3374) or cross-entropy -> backward -> AdamW.  The loss over B x ncls scalars stays in torch."""
 
-    def __init__(self, model, lr, weight_decay=0.0, betas=(0.9, 0.999), pos_weight=None, **kw):
+    def __init__(self, model, lr, weight_decay=0.0, betas=(0.9, 0.999), pos_weight=None, class_weights=None, **kw):
         # train_classification.py:5751-5768: plain torch.optim.AdamW over head + backbone groups with ONE weight decay for
         # every parameter (biases and LayerNorm included; default 0.0) - not timm's no-decay rule of the pretraining script
         kw.setdefault("no_decay_rule", lambda name, p: False)
         super().__init__(model, lr, weight_decay, betas, **kw)
         self.pos_weight = pos_weight
+        self.class_weights = class_weights      # CrossEntropyLoss(weight=...) for > 2 classes (:6103)
 
     def step(self, imgs, target, lr=None, graph: bool = False):
         if graph:
@@ -230,7 +231,7 @@ class ClassifierEngine(TrainEngine):
             z = lg[:, 1] - lg[:, 0]
             loss = torch.nn.functional.binary_cross_entropy_with_logits(z, target.float(), pos_weight=self.pos_weight)
         else:
-            loss = torch.nn.functional.cross_entropy(lg, target)
+            loss = torch.nn.functional.cross_entropy(lg, target, weight=self.class_weights)
         (dlogits,) = torch.autograd.grad(loss, lg)
         self.backward_and_step(lambda sink: vit_core.classifier_bwd(self.store, sink, m._dims, sv, dlogits.contiguous()), lr=lr)
         return loss.detach()

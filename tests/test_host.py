@@ -2,11 +2,13 @@
 the host-side mirror of the reference interface, and the data-parallel bucket logic over gloo (world_size 2).
 No CUDA compute is called here."""
 import ctypes
+import math
 import os
 import re
 import subprocess
 import sys
 
+import numpy as np
 import pytest
 import torch
 
@@ -298,3 +300,135 @@ def test_classifier_engine_decays_every_parameter_like_the_reference():
     src = inspect.getsource(engine.ClassifierEngine.__init__)
     assert "no_decay_rule" in src and "lambda name, p: False" in src
     assert inspect.signature(engine.ClassifierEngine.__init__).parameters["weight_decay"].default == 0.0
+
+
+def test_train_classification_parser_matches_the_reference_flag_for_flag():
+    """Every flag, dest and default of reference get_args (train_classification.py:7706-7982), checked by executing the
+    reference's own parser-building lines when the tree is present; the frozen expectation below otherwise."""
+    import argparse
+    from pathlib import Path
+    from ssl4polyp_b200 import train_classification as TC
+    ours = vars(TC.get_args(["--pretraining", "random"]))
+    ref_path = "/root/reference/src/ssl4polyp/classification/train_classification.py"
+    if os.path.exists(ref_path):
+        src = open(ref_path).read()
+        body = src[src.index("def get_args():"):src.index("    seed_flag_present = any(")]
+        ns = {"argparse": argparse, "Path": Path, "data_packs_root": lambda: Path("data_packs")}
+        exec(body + "    return parser\n", ns)
+        ref = vars(ns["get_args"]().parse_args(["--pretraining", "random"]))
+        extra = {"synthetic_samples", "num_classes", "_seed_explicit"}
+        assert set(ours) - extra == set(ref)
+        assert {k: v for k, v in ours.items() if k not in extra} == ref
+    assert ours["lr"] == 1e-4 and ours["batch_size"] == 16 and ours["epochs"] == 50 and ours["weight_decay"] == 0.05
+    assert ours["finetune_mode"] == "full" and ours["scheduler"] == "none" and ours["early_stop_monitor"] == "val_loss"
+    assert ours["seed"] == 42 and ours["pin_memory"] is True and ours["perturbation_splits"] == ["test"]
+    a = TC.get_args(["--seeds", "7", "9"]);            assert TC._active_seed(a) == 7
+    a = TC.get_args(["--seeds", "7", "--seed", "3"]);  assert TC._active_seed(a) == 3
+
+
+def test_finetune_modes_select_the_reference_parameter_sets():
+    """finetune.py:49-92: full / none / head+1 / head+2; nn.Sequential blocks are skipped by the isinstance test."""
+    from ssl4polyp_b200 import train_classification as TC
+
+    class Toy(torch.nn.Module):
+        def __init__(self, seq):
+            super().__init__()
+            blocks = [torch.nn.Linear(2, 2) for _ in range(3)]
+            self.blocks = torch.nn.Sequential(*blocks) if seq else torch.nn.ModuleList(blocks)
+            self.norm = torch.nn.LayerNorm(2)
+            self.lin_head = torch.nn.Linear(2, 2)
+            self.head = True          # ViT_from_MAE.head is a bool, not a module (models.py:163)
+            self.frozen = False
+
+    def trainable(m):
+        return sorted(n for n, p in m.named_parameters() if p.requires_grad)
+
+    m = Toy(False)
+    TC.configure_finetune_parameters(m, "none");   assert trainable(m) == ["lin_head.bias", "lin_head.weight"] and m.frozen
+    TC.configure_finetune_parameters(m, "head+1"); assert trainable(m) == ["blocks.2.bias", "blocks.2.weight", "lin_head.bias", "lin_head.weight"]
+    TC.configure_finetune_parameters(m, "HEAD+2"); assert len(trainable(m)) == 6 and "blocks.1.weight" in trainable(m) and not m.frozen
+    TC.configure_finetune_parameters(m, "full");   assert len(trainable(m)) == len(list(m.parameters()))
+    s = Toy(True)
+    TC.configure_finetune_parameters(s, "head+2"); assert trainable(s) == ["lin_head.bias", "lin_head.weight"]
+    with pytest.raises(ValueError):
+        TC.normalise_finetune_mode("head+3")
+    ref_path = "/root/reference/src/ssl4polyp/classification/finetune.py"
+    if os.path.exists(ref_path):
+        import importlib.util
+        spec = importlib.util.spec_from_file_location("_ref_finetune", ref_path)
+        ref = importlib.util.module_from_spec(spec); spec.loader.exec_module(ref)
+        for seq in (False, True):
+            for mode in ("none", "full", "head+1", "head+2"):
+                a, b = Toy(seq), Toy(seq)
+                TC.configure_finetune_parameters(a, mode); ref.configure_finetune_parameters(b, mode)
+                assert trainable(a) == trainable(b) and a.frozen == b.frozen, (seq, mode)
+
+
+def test_monitor_early_stop_and_selection_tag_helpers():
+    """train_classification.py:3297-3345, :3878-3915."""
+    from ssl4polyp_b200 import train_classification as TC
+    assert TC.resolve_monitor_mode("val_loss", "auto") == "min" and TC.resolve_monitor_mode("val_auroc", None) == "max"
+    assert TC.resolve_monitor_mode("val_auroc", "MIN") == "min"
+    assert TC.resolve_monitor_key("val_auroc") == "auroc" and TC.resolve_monitor_key(None) == "loss"
+    assert TC.improved(0.4, None, mode="min", min_delta=0) and TC.improved(0.4, 0.5, mode="min", min_delta=0.05)
+    assert not TC.improved(0.46, 0.5, mode="min", min_delta=0.05) and not TC.improved(float("nan"), 0.5, mode="max", min_delta=0)
+    assert TC.should_stop(3, 3, 5, 0) and not TC.should_stop(3, 0, 5, 0) and not TC.should_stop(3, 3, 5, 6)
+    assert [TC.selection_tag(m) for m in ("val_loss", "val_auroc", "loss", "", "val_f1_score")] == ["valLoss", "valAUROC", "loss", "best", "valF1Score"]
+    ref_path = "/root/reference/src/ssl4polyp/classification/train_classification.py"
+    if os.path.exists(ref_path):
+        import re
+        src = open(ref_path).read()
+        ns = {"re": re, "Optional": __import__("typing").Optional}
+        exec(src[src.index("def _format_selection_tag"):src.index("def _should_trigger_early_stop")], ns)
+        for m in ("val_loss", "val_auroc", "loss", "", None, "val_f1_score", "AUC-test", "val__auprc"):
+            assert TC.selection_tag(m) == ns["_format_selection_tag"](m), m
+
+
+def test_metrics_match_sklearn_on_seeded_inputs_with_ties():
+    """classification/metrics/performance.py + thresholds.py call scikit-learn; ssl4polyp_b200.metrics restates them."""
+    sk = pytest.importorskip("sklearn.metrics")
+    from ssl4polyp_b200 import metrics as M
+    rng = np.random.default_rng(0)
+    for n in (5, 64, 501):
+        for ties in (False, True):
+            y = rng.integers(0, 2, n); y[0], y[1] = 0, 1
+            s = rng.random(n)
+            s = np.round(s, 1) if ties else s
+            p = np.stack([1 - s, s], 1)
+            assert abs(M.auroc(p, y, 2) - sk.roc_auc_score(y, s)) < 1e-12
+            assert abs(M.auprc(p, y, 2) - sk.average_precision_score(y, s)) < 1e-12
+            assert abs(M.balanced_accuracy(p, y, 2) - sk.balanced_accuracy_score(y, p.argmax(1))) < 1e-12
+            assert abs(M.mcc(p, y) - sk.matthews_corrcoef(y, p.argmax(1))) < 1e-12
+            fpr, tpr, th = sk.roc_curve(y, s)
+            tau = th[np.argmax(tpr - fpr)]
+            tau = np.nextafter(s.max(), 1.0) if np.isinf(tau) else tau
+            assert M.youden_j_threshold(p, y) == tau
+            lab = (s >= tau).astype(int)
+            assert abs(M.mean_f1(p, y, 2, tau) - sk.f1_score(y, lab, average="macro")) < 1e-6
+            assert abs(M.mean_recall(p, y, 2, tau) - sk.recall_score(y, lab, average="macro")) < 1e-6
+    y = rng.integers(0, 3, 300); p = rng.random((300, 3)); p /= p.sum(1, keepdims=True)
+    assert abs(M.auroc(p, y, 3) - sk.roc_auc_score(y, p, multi_class="ovr", average="macro")) < 1e-12
+    assert abs(M.auprc(p, y, 3) - sk.average_precision_score(np.eye(3)[y], p, average="macro")) < 1e-12
+    assert math.isnan(M.auroc(np.array([[.5, .5]] * 3), np.zeros(3, int), 2))
+    sep = np.array([0.1, 0.2, 0.8, 0.9]); yy = np.array([0, 0, 1, 1])           # perfectly separable: argmax lands on a real score
+    assert M.youden_j_threshold(np.stack([1 - sep, sep], 1), yy) == 0.8
+
+
+def test_synthetic_frames_shard_and_class_weights():
+    from ssl4polyp_b200 import train_classification as TC
+    full = TC.SyntheticFrames(37, 8, 2, image_size=16, seed=3)
+    assert len(full) == 5 and [b[0].shape[0] for b in full] == [8, 8, 8, 8, 5]
+    r0 = TC.SyntheticFrames(37, 8, 2, image_size=16, seed=3, shard=(0, 2)); r1 = TC.SyntheticFrames(37, 8, 2, image_size=16, seed=3, shard=(1, 2))
+    assert len(r0) == 3 and len(r1) == 2
+    got = torch.cat([b[1] for b in r0] + [b[1] for b in r1]).sort().values
+    assert torch.equal(got, full.labels.sort().values)
+    a, b = next(iter(full)), next(iter(TC.SyntheticFrames(37, 8, 2, image_size=16, seed=3)))
+    assert torch.equal(a[0], b[0]) and a[0].dtype == torch.float32
+    args = TC.get_args([])
+    w, c = TC._class_weights(args, [0, 0, 0, 1], 2)
+    assert c == [3, 1] and w == [4 / 6, 2.0] and TC._pos_weight(w, c) == 3.0          # :5617-5622, :6089-6094
+    args.class_weights = "1,5"
+    assert TC._class_weights(args, [0, 0, 0, 1], 2)[0] == [1.0, 5.0]
+    args.class_weights = "1,2,3"
+    with pytest.raises(ValueError):
+        TC._class_weights(args, [0, 1], 2)

@@ -366,3 +366,47 @@ def test_main_pretrain_cli_synthetic_run_and_resume(tmp_path):
                                             ["--resume", str(out / "ckpts" / "checkpoint-1.pth")])
     MP.main(args2)
     assert args2.start_epoch == 2 and (out / "ckpts" / "checkpoint-2.pth").exists()
+
+
+def test_train_classification_cli_synthetic_run(tmp_path):
+    """The fine-tune command line (train_classification.py:7706-7982) end to end on synthetic frames: MAE checkpoint ->
+    ViT_from_MAE, head+1 regime, BCE on logit1-logit0, cosine schedule, Youden tau on val, best/last checkpoints with the
+    reference's payload keys and pointer files; frozen tensors stay bit-identical, trainable ones move."""
+    import json
+    from ssl4polyp_b200 import models_mae, utils
+    from ssl4polyp_b200 import train_classification as TC
+    torch.manual_seed(0)
+    ck = tmp_path / "mae.pth"
+    torch.save({"model": models_mae.mae_vit_base_patch16(norm_pix_loss=True).state_dict()}, ck)
+    out = tmp_path / "cls"
+    args = TC.get_args(["--pretraining", "Hyperkvasir", "--ss-framework", "mae", "--checkpoint", str(ck), "--finetune-mode", "head+1",
+                        "--dataset", "synthetic", "--synthetic-samples", "48", "--batch-size", "16", "--epochs", "3", "--learning-rate", "1e-3",
+                        "--scheduler", "cosine", "--early-stop-monitor", "val_auroc", "--log-interval", "1", "--output-dir", str(out), "--seed", "5"])
+    lines = []
+    summary = TC.run(args, log=lines.append)
+    assert summary["epochs_completed"] == 3 and summary["global_step"] == 9 and summary["monitor_metric"] == "val_auroc"
+    assert 0.0 <= summary["val"]["auroc"] <= 1.0 and math.isfinite(summary["train_loss"]) and summary["val"]["tau"] is not None
+    stem = out / "Hyperkvasir_synthetic_headp1_s5"
+    best = torch.load(str(stem) + ".pth", map_location="cpu", weights_only=False)
+    need = {"epoch", "model_state_dict", "optimizer_state_dict", "scaler_state_dict", "loss", "val_perf", "val_loss", "val_auroc", "test_perf",
+            "test_loss", "test_auroc", "monitor_value", "monitor_metric", "test_monitor_value", "py_state", "np_state", "torch_state"}
+    assert need <= set(best) and best["monitor_metric"] == "val_auroc" and best["epoch"] == summary["best_epoch"]
+    assert os.path.islink(str(stem) + ".pth") and os.path.exists(str(stem) + "_last.pth")
+    last = torch.load(str(stem) + "_last.pth", map_location="cpu", weights_only=False)
+    assert last["epoch"] == 3
+    assert json.loads(open(str(stem) + ".metrics.json").read())["best_epoch"] == summary["best_epoch"]
+    assert any("Train Epoch: 1" in l for l in lines) and os.path.getsize(str(stem) + ".log") > 0
+    # head+1: lin_head and blocks.11 moved, everything else is the checkpoint bit for bit
+    ref = utils.get_MAE_backbone(str(ck), True, 2, False, None).state_dict()
+    sd = last["model_state_dict"]
+    moved = {k for k in sd if not torch.equal(sd[k].cpu(), ref[k].cpu())}
+    assert moved and all(k.startswith("lin_head.") or k.startswith("blocks.11.") for k in moved), sorted(moved)[:5]
+    assert "blocks.11.mlp.fc1.weight" in moved and "blocks.10.mlp.fc1.weight" not in moved and "patch_embed.proj.weight" not in moved
+    # the saved weights reproduce the logged validation loss through the module API (eval mode, no_grad)
+    model = utils.get_MAE_backbone(str(ck), True, 2, False, None)
+    model.load_state_dict(sd)
+    model = model.cuda()
+    val = TC.evaluate(model, TC.SyntheticFrames(12, 16, 2, 224, 6), torch.device("cuda"), 2,
+                      pos_weight=torch.tensor(TC._pos_weight(*TC._class_weights(args, TC.SyntheticFrames(48, 16, 2, 224, 5).labels_list, 2)), device="cuda"))
+    assert abs(val["loss"] - last["val_loss"]) <= 2e-3 * max(1.0, abs(last["val_loss"]))
+    assert abs(val["auroc"] - last["val_auroc"]) < 1e-6
