@@ -62,6 +62,26 @@ int ssl4p_reduce_rows_f32(const float* part, int G, int N, float* out, int accum
 int ssl4p_splitk_reduce(const float* parts, int splits, long long stride, float* out, long long n, int accumulate, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
+ * Pretraining input transform (main_pretrain.py:156-160: RandomResizedCrop(224, scale=(0.2,1), bicubic) ->
+ * RandomHorizontalFlip -> ToTensor -> Normalize, a torchvision Compose run per image on DataLoader workers).
+ * Replaces the Pillow resample (libImaging/Resample.c, 8-bit path) + torchvision to_tensor/normalize with two
+ * kernels, bit-exact in the uint8 resample and in the fp32 result.  The crop boxes and flips are drawn by the
+ * caller (host RNG, torchvision's get_params sequence).
+ *   frames  device uint8: RGB frames, HWC, packed anywhere in one buffer
+ *   desc    device int64 [N,8] per image: byte offset of the frame in `frames`, row pitch in bytes, crop top, left,
+ *           height, width (pixels, inside the frame), flip (0/1), 0
+ *   out     device fp32 [N,3,S,S]
+ *   max_crop  the largest crop height or width in the batch (sizes the filter windows: at most
+ *             SSL4P_RESAMPLE_MAX_TAPS taps per output, i.e. crops up to ~15 S)
+ *   mean3 / std3  HOST pointers to 3 floats
+ * ------------------------------------------------------------------------------------------------ */
+#define SSL4P_RESAMPLE_MAX_TAPS 64
+size_t ssl4p_crop_resize_workspace_bytes(int N, int S);
+int ssl4p_crop_resize_normalize_u8(const void* frames, const long long* desc, int N, int S, int max_crop,
+                                   const float* mean3, const float* std3, float* out,
+                                   void* workspace, size_t workspace_bytes, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
  * random_masking (models_mae.py:123-148) as a function of the noise the caller drew with torch.rand.
  *   ids_restore[n,i] = rank of noise[n,i] in its row (stable ascending: ties -> lower index first)  int64
  *   mask[n,i]        = ids_restore[n,i] >= len_keep ? 1 : 0                                          fp32

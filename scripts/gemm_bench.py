@@ -44,23 +44,24 @@ for name, layout, epi, M, N, K in cases:
     out = torch.empty(M, N, device=dev, dtype=torch.float32 if out32 else torch.bfloat16)
     out2 = torch.empty(M, N, device=dev, dtype=torch.bfloat16) if epi == EPI_BIAS_GELU_BF16 else None
     splits = ops.pick_splits(M, N, K) if layout == GEMM_TN else 1
-    ts = []
-    for _ in range(reps):
-        flush.zero_()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        if layout == GEMM_TN:
-            ops.gemm(a, b, layout, epi, out=out, splits=splits)
-        else:
-            ops.gemm(a, b, layout, epi, bias=bias, aux=aux, out=out, out2=out2)
-        e1.record()
-        torch.cuda.synchronize()
-        ts.append(e0.elapsed_time(e1) * 1e3)
-    t = min(ts)
-    byt = a.numel() * 2 + b.numel() * 2 + out.numel() * out.element_size() + (out2.numel() * 2 if out2 is not None else 0) + \
-        (aux.numel() * aux.element_size() if aux is not None else 0)
-    n_per_step = 12 if name.startswith("enc") else 8
-    if "pred" in name: n_per_step = 1
-    tot += t * n_per_step
-    print(f"{name:18s} M={M:6d} N={N:5d} K={K:6d} s={splits:2d}  {t:8.1f} us  {2.0 * M * N * K / t / 1e6:7.1f} TF/s  {byt / t / 1e3:6.0f} GB/s   x{n_per_step}")
+    for force_bn in [int(x) for x in os.environ.get("GEMM_BN", "0").split(",")]:      # GEMM_BN=0,256,192,128,64 sweeps the N tile
+        ts = []
+        for _ in range(reps):
+            flush.zero_()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            if layout == GEMM_TN:
+                ops.gemm(a, b, layout, epi, out=out, splits=splits, force_bn=force_bn)
+            else:
+                ops.gemm(a, b, layout, epi, bias=bias, aux=aux, out=out, out2=out2, force_bn=force_bn)
+            e1.record()
+            torch.cuda.synchronize()
+            ts.append(e0.elapsed_time(e1) * 1e3)
+        t = min(ts)
+        byt = a.numel() * 2 + b.numel() * 2 + out.numel() * out.element_size() + (out2.numel() * 2 if out2 is not None else 0) + \
+            (aux.numel() * aux.element_size() if aux is not None else 0)
+        n_per_step = 12 if name.startswith("enc") else 8
+        if "pred" in name: n_per_step = 1
+        tot += t * n_per_step
+        print(f"{name:18s} bn={force_bn:3d} M={M:6d} N={N:5d} K={K:6d} s={splits:2d}  {t:8.1f} us  {2.0 * M * N * K / t / 1e6:7.1f} TF/s  {byt / t / 1e3:6.0f} GB/s   x{n_per_step}")
 print(f"sum over the step's block GEMMs: {tot / 1e3:.2f} ms")

@@ -1,0 +1,126 @@
+"""The pretraining input transform with the pixel work on the device.
+
+Reference (models/mae/main_pretrain.py:156-160), per image on DataLoader workers:
+
+    transforms.Compose([RandomResizedCrop(input_size, scale=(0.2, 1.0), interpolation=3),   # PIL bicubic
+                        RandomHorizontalFlip(), ToTensor(), Normalize(IMAGENET_MEAN, IMAGENET_STD)])
+
+Here the workers only decode to uint8 HWC; `TrainTransform` draws the crop box and flip of every image on the host
+with the SAME torch RNG calls in the same order as the Compose (so a seeded run crops identically), copies only the
+crop rectangle of each frame into one pinned staging buffer (one H2D per batch, 3 bytes per source pixel of the
+crop - the CPU cost left on the host is a memcpy, not a bicubic resample), and `ops.crop_resize_normalize` produces the fp32 [N,3,224,224] batch - bit-identical to the Compose
+(Pillow's fixed-point bicubic resample included; csrc/input_pipeline.cu).
+"""
+from __future__ import annotations
+
+import math
+
+import numpy as np
+import torch
+
+from . import ops
+
+IMAGENET_MEAN = (0.485, 0.456, 0.406)
+IMAGENET_STD = (0.229, 0.224, 0.225)
+
+
+def random_resized_crop_params(height: int, width: int, scale=(0.2, 1.0), ratio=(3.0 / 4.0, 4.0 / 3.0)):
+    """(top, left, h, w) drawn as torchvision's RandomResizedCrop.get_params draws them: up to ten tries of
+    area ~ U(scale) * H * W and aspect ~ exp(U(log ratio)), offsets by torch.randint; centre crop clamped to the
+    ratio range when no try fits."""
+    lo, hi = torch.log(torch.tensor(ratio)).tolist()
+    full = height * width
+    for _attempt in range(10):
+        area = full * torch.empty(1).uniform_(scale[0], scale[1]).item()
+        aspect = torch.exp(torch.empty(1).uniform_(lo, hi)).item()
+        w, h = int(round(math.sqrt(area * aspect))), int(round(math.sqrt(area / aspect)))
+        if 0 < w <= width and 0 < h <= height:
+            top = torch.randint(0, height - h + 1, size=(1,)).item()
+            left = torch.randint(0, width - w + 1, size=(1,)).item()
+            return top, left, h, w
+    shape = float(width) / float(height)
+    if shape < min(ratio):
+        w, h = width, int(round(width / min(ratio)))
+    elif shape > max(ratio):
+        h, w = height, int(round(height * max(ratio)))
+    else:
+        w, h = width, height
+    return (height - h) // 2, (width - w) // 2, h, w
+
+
+class TrainTransform:
+    """`batch = TrainTransform(224)(frames)`; frames: sequence of uint8 HWC RGB arrays / CPU tensors of any sizes.
+    Returns fp32 [N,3,size,size] on `device`.  `last_params` holds the drawn (top, left, h, w, flip) per image."""
+
+    def __init__(self, size: int = 224, scale=(0.2, 1.0), ratio=(3.0 / 4.0, 4.0 / 3.0), flip_p: float = 0.5,
+                 mean=IMAGENET_MEAN, std=IMAGENET_STD, device=None, pack_threads=None):
+        if not torch.cuda.is_available():
+            raise RuntimeError("ssl4polyp_b200.input_pipeline needs a CUDA device (sm_100a); there is no CPU fallback")
+        self.size, self.scale, self.ratio, self.flip_p, self.mean, self.std = size, scale, ratio, flip_p, mean, std
+        self.device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+        self._stage = [None, None]          # two pinned staging buffers: batch i+1 is packed while batch i's copy drains
+        self._events = [None, None]
+        self._turn = 0
+        import os
+        from concurrent.futures import ThreadPoolExecutor
+        nt = 1 if pack_threads is None else int(pack_threads)      # measured: one thread is fastest (scripts/input_bench.py)
+        self._pool = ThreadPoolExecutor(max_workers=nt) if nt > 1 else None
+        self.last_params = []
+        self.h2d_bytes = 0
+
+    def draw(self, height: int, width: int):
+        top, left, h, w = random_resized_crop_params(height, width, self.scale, self.ratio)
+        flip = bool(torch.rand(1) < self.flip_p)          # RandomHorizontalFlip.forward
+        return top, left, h, w, flip
+
+    def _staging(self, nbytes: int):
+        k = self._turn
+        self._turn ^= 1
+        if self._events[k] is not None:
+            self._events[k].synchronize()                 # the copy that last used this buffer has left the host
+        buf = self._stage[k]
+        if buf is None or buf.numel() < nbytes:
+            buf = torch.empty(max(nbytes, 1 << 22), dtype=torch.uint8).pin_memory()
+            self._stage[k] = buf
+        return k, buf
+
+    def __call__(self, frames, params=None, out=None):
+        frames = [f.numpy() if isinstance(f, torch.Tensor) else np.asarray(f) for f in frames]
+        for f in frames:
+            if f.dtype != np.uint8 or f.ndim != 3 or f.shape[2] != 3:
+                raise RuntimeError(f"TrainTransform: frames must be uint8 [H, W, 3], got {f.dtype} {f.shape}")
+        if params is None:
+            params = [self.draw(f.shape[0], f.shape[1]) for f in frames]
+        self.last_params = list(params)
+        n = len(frames)
+        rows = np.zeros((n, 8), np.int64)
+        total = 0
+        for i, (f, (top, left, h, w, flip)) in enumerate(zip(frames, params)):
+            if not (0 <= top and 0 <= left and h > 0 and w > 0 and top + h <= f.shape[0] and left + w <= f.shape[1]):
+                raise RuntimeError(f"TrainTransform: crop {(top, left, h, w)} outside a {f.shape[0]}x{f.shape[1]} frame")
+            rows[i] = (total, w * 3, 0, 0, h, w, int(flip), 0)       # only the crop rectangle travels: it becomes the frame
+            total += h * w * 3
+        desc = torch.from_numpy(rows)
+        k, stage = self._staging(max(total, 1))
+
+        def pack(i):
+            top, left, h, w, _flip = params[i]
+            o = int(rows[i, 0])
+            stage[o:o + h * w * 3].view(h, w, 3).copy_(torch.from_numpy(frames[i])[top:top + h, left:left + w])
+
+        if self._pool is not None and n > 1:
+            list(self._pool.map(pack, range(n)))          # strided memcpys: the GIL is released inside copy_
+        else:
+            for i in range(n):
+                pack(i)
+        dev = torch.empty(max(total, 1), dtype=torch.uint8, device=self.device)
+        dev.copy_(stage[:max(total, 1)], non_blocking=True)
+        desc_dev = desc.pin_memory().to(self.device, non_blocking=True)
+        ev = torch.cuda.Event()
+        ev.record()
+        self._events[k] = ev
+        self.h2d_bytes = total + desc.numel() * 8
+        if n == 0:
+            return torch.empty(0, 3, self.size, self.size, dtype=torch.float32, device=self.device)
+        max_crop = max(max(p[2], p[3]) for p in params)
+        return ops.crop_resize_normalize(dev, desc_dev, self.size, max_crop, self.mean, self.std, out=out)

@@ -74,6 +74,9 @@ def get_args_parser():
     parser.add_argument('--dist_on_itp', action='store_true')
     parser.add_argument('--dist_url', default='env://')
     parser.add_argument('--precision', choices=['amp', 'fp32'], default='amp')
+    # not in the reference: run the Compose's pixel work (crop, bicubic resize, flip, normalise) on the GPU
+    parser.add_argument('--device_transform', action='store_true',
+                        help='DataLoader workers only decode; RandomResizedCrop/flip/ToTensor/Normalize run on the device (bit-identical)')
     return parser
 
 
@@ -120,12 +123,25 @@ def _build_loader(args):
         transforms.ToTensor(),
         transforms.Normalize(mean=[0.485, 0.456, 0.406], std=[0.229, 0.224, 0.225])])
     data_dir = args.data_path if args.no_train_dir else os.path.join(args.data_path, 'train')
-    dataset_train = datasets.ImageFolder(data_dir, transform=transform_train)
+    on_device = getattr(args, 'device_transform', False)
+    # --device_transform: the workers only decode (uint8 HWC); crop / bicubic resize / flip / normalise run on the GPU,
+    # bit-identical to the Compose above (input_pipeline.TrainTransform), in train_one_epoch
+    dataset_train = datasets.ImageFolder(data_dir, transform=_decode_rgb_u8 if on_device else transform_train)
     print(dataset_train)
     sampler = torch.utils.data.DistributedSampler(dataset_train, num_replicas=args.world_size, rank=args.rank,
                                                   shuffle=True, seed=args.seed)
     return torch.utils.data.DataLoader(dataset_train, sampler=sampler, batch_size=args.batch_size,
-                                       num_workers=args.num_workers, pin_memory=args.pin_mem, drop_last=True)
+                                       num_workers=args.num_workers, pin_memory=args.pin_mem and not on_device, drop_last=True,
+                                       collate_fn=_collate_frames if on_device else None)
+
+
+def _decode_rgb_u8(img):
+    import numpy as np
+    return torch.from_numpy(np.asarray(img.convert('RGB')).copy())
+
+
+def _collate_frames(batch):
+    return [b[0] for b in batch], torch.tensor([b[1] for b in batch])
 
 
 def train_one_epoch(engine, data_loader, device, epoch, args, save_ckpt_fn=None, last_time_save=None, time_save_sec=None):
@@ -138,7 +154,13 @@ def train_one_epoch(engine, data_loader, device, epoch, args, save_ckpt_fn=None,
     for it, (samples, _) in enumerate(data_loader):
         if it % accum_iter == 0:                       # per-iteration (not per-epoch) lr schedule
             lr = cosine_lr(it / n_iter + epoch, args.lr, args.min_lr, args.warmup_epochs, args.epochs)
-        samples = samples.to(device, non_blocking=True)
+        if isinstance(samples, list):                  # --device_transform: uint8 frames of any size
+            if getattr(engine, '_device_tf', None) is None:          # kept off `args`: args is pickled into checkpoints
+                from .input_pipeline import TrainTransform
+                engine._device_tf = TrainTransform(args.input_size, device=device)
+            samples = engine._device_tf(samples)
+        else:
+            samples = samples.to(device, non_blocking=True)
         loss = engine.step(samples, lr=lr, accum_iter=accum_iter, micro_index=it % accum_iter)
         loss_value = loss.item()                       # the reference syncs here too (engine_pretrain.py:55)
         if not math.isfinite(loss_value):

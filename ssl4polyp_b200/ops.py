@@ -166,6 +166,32 @@ def reduce_rows_f32(x, out=None, accumulate=False):
     return out
 
 
+def crop_resize_normalize(frames, desc, size, max_crop, mean, std, out=None):
+    """uint8 HWC frames (one packed device buffer) -> crop / PIL-bicubic resize / flip / to_tensor / normalize ->
+    fp32 [N,3,size,size] (main_pretrain.py:156-160).  desc int64 [N,8] on the device: byte offset, row pitch, top,
+    left, height, width, flip, 0.  max_crop = largest crop extent in the batch (host int)."""
+    import ctypes
+    lib = _lib.load()
+    _req(frames, torch.uint8, "crop_resize frames")
+    _req(desc, torch.int64, "crop_resize desc")
+    if desc.dim() != 2 or desc.shape[1] != 8:
+        raise RuntimeError("crop_resize: desc must be int64 [N, 8]")
+    N = desc.shape[0]
+    if out is None:
+        out = torch.empty(N, 3, size, size, dtype=f32, device=frames.device)
+    _req(out, f32, "crop_resize out")
+    assert out.shape == (N, 3, size, size)
+    if N == 0:
+        return out
+    nb = lib.ssl4p_crop_resize_workspace_bytes(N, size)
+    ws = workspace(nb, frames.device, "crop_resize")
+    m3 = (ctypes.c_float * 3)(*[float(v) for v in mean])
+    s3 = (ctypes.c_float * 3)(*[float(v) for v in std])
+    _lib.check(lib.ssl4p_crop_resize_normalize_u8(frames.data_ptr(), desc.data_ptr(), N, size, int(max_crop), ctypes.addressof(m3),
+                                                  ctypes.addressof(s3), out.data_ptr(), ws.data_ptr(), ws.numel(), _stream()), "crop_resize")
+    return out
+
+
 def cast_bf16(src, dst=None):
     lib = _lib.load()
     _req(src, f32, "cast src")

@@ -266,7 +266,9 @@ def test_main_pretrain_parser_matches_the_reference_flag_for_flag():
         src = open(ref_path).read()
         ns = {"argparse": argparse, "Path": Path}
         exec(src[src.index("def get_args_parser"):src.index("def main(")], ns)
-        assert vars(ns["get_args_parser"]().parse_args([])) == ours
+        extra = {"device_transform"}                     # this implementation's own switch (input_pipeline.TrainTransform)
+        assert vars(ns["get_args_parser"]().parse_args([])) == {k: v for k, v in ours.items() if k not in extra}
+        assert ours["device_transform"] is False
     assert ours["batch_size"] == 64 and ours["model"] == "mae_vit_large_patch16" and ours["mask_ratio"] == 0.75
     assert ours["blr"] == 1e-3 and ours["warmup_epochs"] == 40 and ours["weight_decay"] == 0.05 and ours["precision"] == "amp"
     a = MP.get_args_parser().parse_args(["--acum_iter", "4", "--no_train_dir", "--save-freq-mins", "30", "--keep-last", "2"])
@@ -432,3 +434,32 @@ def test_synthetic_frames_shard_and_class_weights():
     args.class_weights = "1,2,3"
     with pytest.raises(ValueError):
         TC._class_weights(args, [0, 1], 2)
+
+
+def test_input_oracle_matches_pillow_torchvision_golden():
+    """oracle/input_oracle.py against tests/golden/input_golden.npz (made by oracle/make_input_golden.py from the
+    installed Pillow + torchvision): uint8 after the bicubic resample and fp32 after ToTensor+Normalize, bit for bit;
+    the crop boxes drawn by the product's host code follow torchvision's RNG sequence."""
+    import hashlib
+    from oracle import input_oracle as IO
+    from ssl4polyp_b200 import input_pipeline as P
+    g = np.load(os.path.join(ROOT, "tests", "golden", "input_golden.npz"))
+    for case in range(8):
+        H, W, i, j, h, w, flip = (int(v) for v in g[f"params{case}"])
+        if H * W > 800 * 800:
+            continue                                   # the two large frames take the numpy oracle ~10 s: GPU test covers them
+        frame = IO.synthetic_frame(case, H, W)
+        u8 = IO.crop_resize_u8(frame, i, j, h, w)
+        assert np.array_equal(u8, g[f"u8_{case}"]), case
+        t = IO.to_tensor_normalize(u8, bool(flip))
+        assert hashlib.sha256(np.ascontiguousarray(t).tobytes()).digest() == g[f"tensor_sha256_{case}"].tobytes(), case
+        if case not in (3, 5):                         # those two boxes were forced (skipped passes), not drawn
+            torch.manual_seed(case)
+            assert P.random_resized_crop_params(H, W) == (i, j, h, w)
+            assert bool(torch.rand(1) < 0.5) == bool(flip)
+    for s in range(30):
+        torch.manual_seed(s); a = P.random_resized_crop_params(40 + 37 * s, 2000 - 61 * s)
+        torch.manual_seed(s); b = IO.random_resized_crop_params(40 + 37 * s, 2000 - 61 * s)
+        assert a == b, s
+    ks, b, k = IO.precompute_coeffs(1155, 0.0, 1155.0, 224)
+    assert ks == 23 and int(b[:, 1].max()) <= ks and abs(int(k[100].sum()) - (1 << 22)) <= ks

@@ -410,3 +410,28 @@ def test_train_classification_cli_synthetic_run(tmp_path):
                       pos_weight=torch.tensor(TC._pos_weight(*TC._class_weights(args, TC.SyntheticFrames(48, 16, 2, 224, 5).labels_list, 2)), device="cuda"))
     assert abs(val["loss"] - last["val_loss"]) <= 2e-3 * max(1.0, abs(last["val_loss"]))
     assert abs(val["auroc"] - last["val_auroc"]) < 1e-6
+
+
+def test_main_pretrain_image_folder_with_device_transform(tmp_path):
+    """`--device_transform`: ImageFolder workers decode to uint8 only, the crop / bicubic resize / flip / normalise of
+    main_pretrain.py:156-160 runs on the GPU inside the loop; one epoch over PNG frames of mixed sizes, checkpoint written."""
+    import numpy as np
+    from PIL import Image
+    from oracle import input_oracle as IO
+    from ssl4polyp_b200 import main_pretrain as MP
+    root = tmp_path / "data"
+    for cls in ("a", "b"):
+        (root / cls).mkdir(parents=True)
+        for k in range(4):
+            Image.fromarray(IO.synthetic_frame(k + (10 if cls == "b" else 0), 240 + 40 * k, 320 + 30 * k)).save(root / cls / f"{k}.png")
+    out = tmp_path / "run"
+    out.mkdir()
+    args = MP.get_args_parser().parse_args(["--model", "mae_vit_base_patch16", "--norm_pix_loss", "--batch_size", "4", "--epochs", "1",
+                                            "--warmup_epochs", "0", "--blr", "1.5e-4", "--data_path", str(root), "--no_train_dir",
+                                            "--num_workers", "2", "--device_transform", "--output_dir", str(out), "--save-freq-epochs", "1"])
+    MP.main(args)
+    ck = torch.load(out / "ckpts" / "checkpoint-0.pth", map_location="cpu", weights_only=False)
+    assert ck["epoch"] == 0 and ck["args"].device_transform is True
+    log = [l for l in open(out / "log.txt").read().splitlines() if l.strip()]
+    import json
+    assert math.isfinite(json.loads(log[-1])["train_loss"])

@@ -1,5 +1,6 @@
 """GPU parity tests of the individual C-ABI kernels against plain fp32 torch / the oracle (tests only)."""
 import math
+import os
 
 import pytest
 import torch
@@ -319,3 +320,94 @@ def test_pool_head():
         dxn = ops.pool_head_bwd(xn.to(dev()), W.to(dev()), dl.to(dev()), dW, db, N, T, D, spatial)
         assert rel_err(dxn.cpu().reshape(N, T, D), xf.grad) < 1e-2
         assert rel_err(dW.cpu(), Wr.grad) < 1e-4 and rel_err(db.cpu(), br.grad) < 1e-5
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# input transform (main_pretrain.py:156-160): bit-exact against Pillow/torchvision goldens and the oracle
+def _input_golden():
+    import numpy as np
+    return np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "input_golden.npz"))
+
+
+def _run_crop(frames, params, size=224):
+    import numpy as np
+    from ssl4polyp_b200 import ops
+    desc, chunks, off = [], [], 0
+    for f, (i, j, h, w, flip) in zip(frames, params):
+        desc.append([off, f.shape[1] * 3, i, j, h, w, int(flip), 0])
+        chunks.append(np.ascontiguousarray(f).reshape(-1))
+        off += f.size
+    buf = torch.from_numpy(np.concatenate(chunks)).cuda()
+    out = ops.crop_resize_normalize(buf, torch.tensor(desc, dtype=torch.int64).cuda(), size,
+                                    max(max(p[2], p[3]) for p in params), (0.485, 0.456, 0.406), (0.229, 0.224, 0.225))
+    torch.cuda.synchronize()
+    return out.cpu().numpy()
+
+
+def test_crop_resize_normalize_bit_exact_against_pillow_golden():
+    """All eight golden cases in ONE launch (mixed frame sizes, 37x41 up-scaling to 1072x1920 down-scaling, both
+    skipped-pass cases, flips): fp32 output sha256 == what torchvision produced; uint8 resample recovered exactly."""
+    import hashlib
+    import numpy as np
+    from oracle import input_oracle as IO
+    g = _input_golden()
+    frames, params = [], []
+    for case in range(8):
+        H, W, i, j, h, w, flip = (int(v) for v in g[f"params{case}"])
+        frames.append(IO.synthetic_frame(case, H, W)); params.append((i, j, h, w, bool(flip)))
+    out = _run_crop(frames, params)
+    mean = np.asarray(IO.IMAGENET_MEAN, np.float32)[:, None, None]; std = np.asarray(IO.IMAGENET_STD, np.float32)[:, None, None]
+    for case in range(8):
+        t = out[case]
+        want = IO.to_tensor_normalize(g[f"u8_{case}"], params[case][4])
+        assert np.array_equal(t.view(np.uint32), want.view(np.uint32)), (case, float(np.abs(t - want).max()))
+        assert hashlib.sha256(np.ascontiguousarray(t).tobytes()).digest() == g[f"tensor_sha256_{case}"].tobytes(), case
+
+
+@pytest.mark.parametrize("H,W,box", [(300, 300, (0, 0, 300, 300)), (225, 223, (0, 0, 225, 223)), (64, 3000, (0, 0, 64, 3000)),
+                                      (3000, 64, (10, 1, 2990, 63)), (1, 1, (0, 0, 1, 1)), (500, 700, (499, 0, 1, 700))])
+def test_crop_resize_edge_geometries_match_the_oracle(H, W, box):
+    """Extreme aspect ratios, one-pixel crops, crops touching the frame border, scale 13 (55 taps)."""
+    import numpy as np
+    from oracle import input_oracle as IO
+    frame = IO.synthetic_frame(11, H, W)
+    i, j, h, w = box
+    for flip in (False, True):
+        got = _run_crop([frame], [(i, j, h, w, flip)])[0]
+        want = IO.to_tensor_normalize(IO.crop_resize_u8(frame, i, j, h, w), flip)
+        assert np.array_equal(got.view(np.uint32), want.view(np.uint32)), float(np.abs(got - want).max())
+
+
+def test_crop_resize_rejects_oversized_crops_and_handles_empty_batches():
+    from ssl4polyp_b200 import ops
+    buf = torch.zeros(16, dtype=torch.uint8, device="cuda")
+    desc = torch.zeros(1, 8, dtype=torch.int64, device="cuda")
+    with pytest.raises(RuntimeError, match="taps"):
+        ops.crop_resize_normalize(buf, desc, 224, 224 * 16, (0, 0, 0), (1, 1, 1))
+    out = ops.crop_resize_normalize(buf, torch.zeros(0, 8, dtype=torch.int64, device="cuda"), 224, 10, (0, 0, 0), (1, 1, 1))
+    assert out.shape == (0, 3, 224, 224)
+
+
+def test_train_transform_reproduces_the_compose_under_one_seed():
+    """TrainTransform (host RNG draw + packed uint8 H2D + kernels) == the reference Compose restated by the oracle, image
+    for image under one torch seed; only the crop rows travel to the device."""
+    import numpy as np
+    from oracle import input_oracle as IO
+    from ssl4polyp_b200.input_pipeline import TrainTransform
+    frames = [IO.synthetic_frame(20 + k, 240 + 53 * k, 320 + 71 * k) for k in range(6)]
+    tf = TrainTransform(224)
+    for rep in range(2):                                   # second call reuses the other staging buffer
+        torch.manual_seed(77 + rep)
+        got = tf(frames).cpu().numpy()
+        torch.manual_seed(77 + rep)
+        for k, f in enumerate(frames):
+            want, p = IO.transform_train(f)
+            assert tuple(tf.last_params[k]) == p
+            assert np.array_equal(got[k].view(np.uint32), want.view(np.uint32)), (rep, k)
+    assert tf.h2d_bytes < sum(f.size for f in frames) and tf.h2d_bytes * 1.0 > 0
+    # the batch feeds the model as the DataLoader's batch would
+    from ssl4polyp_b200 import models_mae
+    torch.manual_seed(0)
+    m = models_mae.mae_vit_base_patch16(norm_pix_loss=True).cuda()
+    loss, pred, mask = m(tf(frames), mask_ratio=0.75)
+    assert torch.isfinite(loss) and pred.shape == (6, 196, 768)
