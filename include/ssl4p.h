@@ -76,8 +76,11 @@ int ssl4p_splitk_reduce(const float* parts, int splits, long long stride, float*
  *   mean3 / std3  HOST pointers to 3 floats
  * ------------------------------------------------------------------------------------------------ */
 #define SSL4P_RESAMPLE_MAX_TAPS 64
+#define SSL4P_RESAMPLE_BICUBIC 0   /* PIL Image.BICUBIC, a = -0.5, support 2: RandomResizedCrop(interpolation=3)              */
+#define SSL4P_RESAMPLE_BILINEAR 1  /* PIL Image.BILINEAR, support 1: T.Resize((S,S)) of the fine-tune / eval transforms
+                                      (classification/data/transforms.py:233-235; box = the whole frame, flip = 0)       */
 size_t ssl4p_crop_resize_workspace_bytes(int N, int S);
-int ssl4p_crop_resize_normalize_u8(const void* frames, const long long* desc, int N, int S, int max_crop,
+int ssl4p_crop_resize_normalize_u8(const void* frames, const long long* desc, int N, int S, int max_crop, int filter,
                                    const float* mean3, const float* std3, float* out,
                                    void* workspace, size_t workspace_bytes, void* stream);
 

@@ -42,12 +42,20 @@ def bicubic_filter(x: float) -> float:
     return 0.0
 
 
-def precompute_coeffs(in_size: int, in0: float, in1: float, out_size: int):
+def bilinear_filter(x: float) -> float:
+    """Resample.c bilinear_filter (support 1.0)."""
+    if x < 0.0:
+        x = -x
+    return 1.0 - x if x < 1.0 else 0.0
+
+
+def precompute_coeffs(in_size: int, in0: float, in1: float, out_size: int, filt: str = "bicubic"):
     """Resample.c precompute_coeffs + normalize_coeffs_8bpc -> (ksize, bounds[out,2] = (xmin, count), kk[out,ksize] int32)."""
     scale = filterscale = (in1 - in0) / out_size
     if filterscale < 1.0:
         filterscale = 1.0
-    support = 2.0 * filterscale
+    fn, base = (bicubic_filter, 2.0) if filt == "bicubic" else (bilinear_filter, 1.0)
+    support = base * filterscale
     ksize = int(math.ceil(support)) * 2 + 1
     bounds = np.zeros((out_size, 2), np.int32)
     kk = np.zeros((out_size, ksize), np.int32)
@@ -61,7 +69,7 @@ def precompute_coeffs(in_size: int, in0: float, in1: float, out_size: int):
         if xmax > in_size:
             xmax = in_size
         xmax -= xmin
-        k = [bicubic_filter((x + xmin - center + 0.5) * ss) for x in range(xmax)]
+        k = [fn((x + xmin - center + 0.5) * ss) for x in range(xmax)]
         ww = 0.0
         for w in k:
             ww += w
@@ -95,15 +103,15 @@ def _pass(img: np.ndarray, bounds, kk, axis: int) -> np.ndarray:
     return out
 
 
-def crop_resize_u8(frame: np.ndarray, top: int, left: int, height: int, width: int, size: int = 224) -> np.ndarray:
+def crop_resize_u8(frame: np.ndarray, top: int, left: int, height: int, width: int, size: int = 224, filt: str = "bicubic") -> np.ndarray:
     """`F.resized_crop(img, top, left, height, width, (size, size), BICUBIC)` on a PIL RGB image: crop, then
     ImagingResample with the box = the whole crop; a pass is skipped when that axis already has the target size."""
     crop = np.ascontiguousarray(frame[top:top + height, left:left + width, :])
     if width != size:
-        _, b, k = precompute_coeffs(width, 0.0, float(width), size)
+        _, b, k = precompute_coeffs(width, 0.0, float(width), size, filt)
         crop = _pass(crop, b, k, 1)
     if height != size:
-        _, b, k = precompute_coeffs(height, 0.0, float(height), size)
+        _, b, k = precompute_coeffs(height, 0.0, float(height), size, filt)
         crop = _pass(crop, b, k, 0)
     return crop
 
@@ -158,3 +166,9 @@ def synthetic_frame(seed: int, H: int, W: int) -> np.ndarray:
     rng = np.random.default_rng(seed)
     base = rng.integers(0, 256, (H // 8 + 2, W // 8 + 2, 3), dtype=np.uint8)
     return np.kron(base, np.ones((8, 8, 1), np.uint8))[:H, :W] ^ rng.integers(0, 32, (H, W, 3), dtype=np.uint8)
+
+
+def transform_eval(frame: np.ndarray, size: int = 224) -> np.ndarray:
+    """classification/data/transforms.py:233-258 without augmentations (val / test stages): T.Resize((size, size)) - PIL
+    BILINEAR over the whole frame - then ToTensor and Normalize."""
+    return to_tensor_normalize(crop_resize_u8(frame, 0, 0, frame.shape[0], frame.shape[1], size, "bilinear"), False)

@@ -57,6 +57,14 @@ mine = [IO.transform_train(frames[s])[0] for s in (0, 1, 4)]
 for a, b in zip(ref, mine):
     assert np.array_equal(a.view(np.uint32), b.view(np.uint32))
 print("Compose under one seed: bit-identical")
+# the fine-tune eval transform: T.Resize((224, 224)) (PIL bilinear) -> ToTensor -> Normalize
+ev = T.Compose([T.Resize((224, 224)), T.ToTensor(), T.Normalize(mean=IO.IMAGENET_MEAN, std=IO.IMAGENET_STD)])
+for seed in (0, 1, 4, 6, 7):
+    t = ev(Image.fromarray(frames[seed])).numpy()
+    o = IO.transform_eval(frames[seed])
+    assert np.array_equal(o.view(np.uint32), t.view(np.uint32)), seed
+    out[f"eval_sha256_{seed}"] = np.frombuffer(hashlib.sha256(np.ascontiguousarray(t).tobytes()).digest(), np.uint8)
+print("eval transform (bilinear Resize): bit-identical")
 dst = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests", "golden", "input_golden.npz")
 np.savez_compressed(dst, **out)
 print("wrote", dst, os.path.getsize(dst) // 1024, "KiB")

@@ -47,7 +47,16 @@ __device__ __forceinline__ double bicubic_weight(double x) {        // Resample.
 // taps == 0 marks a skipped pass) followed by int32 weights[kMaxTaps][S] (tap-major: lanes = adjacent outputs).
 __device__ __forceinline__ size_t axis_words(int S) { return (size_t)S * (kMaxTaps + 2); }
 
-__global__ void resample_coeffs_kernel(const long long* __restrict__ desc, int S, int* __restrict__ ws) {
+__device__ __forceinline__ double bilinear_weight(double x) {       // Resample.c bilinear_filter (support 1)
+    if (x < 0.0) x = -x;
+    return x < 1.0 ? __dadd_rn(1.0, -x) : 0.0;
+}
+
+__device__ __forceinline__ double filter_weight(int filter, double x) {
+    return filter == SSL4P_RESAMPLE_BILINEAR ? bilinear_weight(x) : bicubic_weight(x);
+}
+
+__global__ void resample_coeffs_kernel(const long long* __restrict__ desc, int S, int filter, int* __restrict__ ws) {
     const int n = blockIdx.x, axis = blockIdx.y;
     const long long* d = desc + (size_t)n * kDescStride;
     const int in_size = (int)(axis == 0 ? d[5] : d[4]);
@@ -61,7 +70,7 @@ __global__ void resample_coeffs_kernel(const long long* __restrict__ desc, int S
         }
         const double scale = __ddiv_rn((double)in_size, (double)S);  // (in1 - in0) / outSize, box = the whole crop
         const double filterscale = scale < 1.0 ? 1.0 : scale;
-        const double support = __dmul_rn(2.0, filterscale);
+        const double support = __dmul_rn(filter == SSL4P_RESAMPLE_BILINEAR ? 1.0 : 2.0, filterscale);
         const double ss = __ddiv_rn(1.0, filterscale);
         const double center = __dmul_rn((double)xx + 0.5, scale);    // in0 (= 0.0) + (xx + 0.5) * scale
         int xmin = __double2int_rz(__dadd_rn(__dadd_rn(center, -support), 0.5));
@@ -72,9 +81,9 @@ __global__ void resample_coeffs_kernel(const long long* __restrict__ desc, int S
         if (xmax > kMaxTaps) xmax = kMaxTaps;                        // unreachable: the host checks the largest crop
         double ww = 0.0;
         for (int x = 0; x < xmax; ++x)
-            ww = __dadd_rn(ww, bicubic_weight(__dmul_rn(__dadd_rn(__dadd_rn((double)(x + xmin), -center), 0.5), ss)));
+            ww = __dadd_rn(ww, filter_weight(filter, __dmul_rn(__dadd_rn(__dadd_rn((double)(x + xmin), -center), 0.5), ss)));
         for (int x = 0; x < xmax; ++x) {
-            double w = bicubic_weight(__dmul_rn(__dadd_rn(__dadd_rn((double)(x + xmin), -center), 0.5), ss));
+            double w = filter_weight(filter, __dmul_rn(__dadd_rn(__dadd_rn((double)(x + xmin), -center), 0.5), ss));
             if (ww != 0.0) w = __ddiv_rn(w, ww);
             const double f = __dmul_rn(w, (double)(1 << kPrecBits));
             weights[(size_t)x * S + xx] = w < 0.0 ? __double2int_rz(__dadd_rn(-0.5, f)) : __double2int_rz(__dadd_rn(0.5, f));
@@ -178,13 +187,14 @@ extern "C" size_t ssl4p_crop_resize_workspace_bytes(int N, int S) {
     return (size_t)N * 2 * (size_t)S * (kMaxTaps + 2) * sizeof(int);
 }
 
-extern "C" int ssl4p_crop_resize_normalize_u8(const void* frames, const long long* desc, int N, int S, int max_crop,
+extern "C" int ssl4p_crop_resize_normalize_u8(const void* frames, const long long* desc, int N, int S, int max_crop, int filter,
                                               const float* mean3, const float* std3, float* out,
                                               void* workspace, size_t workspace_bytes, void* stream) {
     SSL4P_REQUIRE(frames && desc && out && mean3 && std3, "crop_resize: null argument");
     SSL4P_REQUIRE(N >= 0 && S > 0 && S <= 1024 && max_crop > 0, "crop_resize: bad shape N=%d S=%d max_crop=%d", N, S, max_crop);
+    SSL4P_REQUIRE(filter == SSL4P_RESAMPLE_BICUBIC || filter == SSL4P_RESAMPLE_BILINEAR, "crop_resize: unknown filter %d", filter);
     const double scale = max_crop > S ? (double)max_crop / S : 1.0;
-    const int ksize = (int)ceil(2.0 * scale) * 2 + 1;                // Resample.c: ksize = ceil(support) * 2 + 1
+    const int ksize = (int)ceil((filter == SSL4P_RESAMPLE_BILINEAR ? 1.0 : 2.0) * scale) * 2 + 1;   // Resample.c: ceil(support) * 2 + 1
     SSL4P_REQUIRE(ksize <= kMaxTaps, "crop_resize: a %d-pixel crop to %d needs %d taps per output (limit %d)", max_crop, S, ksize, kMaxTaps);
     SSL4P_REQUIRE(workspace && workspace_bytes >= ssl4p_crop_resize_workspace_bytes(N, S), "crop_resize: workspace too small");
     if (N == 0) return SSL4P_OK;
@@ -199,7 +209,7 @@ extern "C" int ssl4p_crop_resize_normalize_u8(const void* frames, const long lon
     SSL4P_REQUIRE(smem <= 227 * 1024, "crop_resize: crop %d -> %d does not fit shared memory", max_crop, S);
     const int tile_rows = band_tile_rows(band, max_crop, S);
     SSL4P_CUDA(cudaFuncSetAttribute(crop_resize_normalize_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    resample_coeffs_kernel<<<dim3(N, 2), 256, 0, STREAM>>>(desc, S, (int*)workspace);
+    resample_coeffs_kernel<<<dim3(N, 2), 256, 0, STREAM>>>(desc, S, filter, (int*)workspace);
     int rc = check_launch("resample_coeffs_kernel");
     if (rc) return rc;
     crop_resize_normalize_kernel<<<dim3((S + band - 1) / band, N), 256, smem, STREAM>>>(

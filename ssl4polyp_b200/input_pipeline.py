@@ -61,6 +61,7 @@ class TrainTransform:
         self._stage = [None, None]          # two pinned staging buffers: batch i+1 is packed while batch i's copy drains
         self._events = [None, None]
         self._turn = 0
+        self.filter = "bicubic"                          # RandomResizedCrop(interpolation=3)
         import os
         from concurrent.futures import ThreadPoolExecutor
         nt = 1 if pack_threads is None else int(pack_threads)      # measured: one thread is fastest (scripts/input_bench.py)
@@ -123,4 +124,16 @@ class TrainTransform:
         if n == 0:
             return torch.empty(0, 3, self.size, self.size, dtype=torch.float32, device=self.device)
         max_crop = max(max(p[2], p[3]) for p in params)
-        return ops.crop_resize_normalize(dev, desc_dev, self.size, max_crop, self.mean, self.std, out=out)
+        return ops.crop_resize_normalize(dev, desc_dev, self.size, max_crop, self.mean, self.std, out=out, filter=self.filter)
+
+
+class EvalTransform(TrainTransform):
+    """The fine-tune script's val / test transform (classification/data/transforms.py:233-258 with augmentations off):
+    T.Resize((size, size)) - PIL BILINEAR over the whole frame - then ToTensor and Normalize; no randomness."""
+
+    def __init__(self, size: int = 224, mean=IMAGENET_MEAN, std=IMAGENET_STD, device=None):
+        super().__init__(size, mean=mean, std=std, device=device)
+        self.filter = "bilinear"
+
+    def draw(self, height: int, width: int):
+        return 0, 0, height, width, False

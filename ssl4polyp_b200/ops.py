@@ -166,10 +166,11 @@ def reduce_rows_f32(x, out=None, accumulate=False):
     return out
 
 
-def crop_resize_normalize(frames, desc, size, max_crop, mean, std, out=None):
+def crop_resize_normalize(frames, desc, size, max_crop, mean, std, out=None, filter="bicubic"):
     """uint8 HWC frames (one packed device buffer) -> crop / PIL-bicubic resize / flip / to_tensor / normalize ->
     fp32 [N,3,size,size] (main_pretrain.py:156-160).  desc int64 [N,8] on the device: byte offset, row pitch, top,
-    left, height, width, flip, 0.  max_crop = largest crop extent in the batch (host int)."""
+    left, height, width, flip, 0.  max_crop = largest crop extent in the batch (host int).  filter: "bicubic"
+    (RandomResizedCrop(interpolation=3)) or "bilinear" (T.Resize of classification/data/transforms.py:233-235)."""
     import ctypes
     lib = _lib.load()
     _req(frames, torch.uint8, "crop_resize frames")
@@ -187,7 +188,8 @@ def crop_resize_normalize(frames, desc, size, max_crop, mean, std, out=None):
     ws = workspace(nb, frames.device, "crop_resize")
     m3 = (ctypes.c_float * 3)(*[float(v) for v in mean])
     s3 = (ctypes.c_float * 3)(*[float(v) for v in std])
-    _lib.check(lib.ssl4p_crop_resize_normalize_u8(frames.data_ptr(), desc.data_ptr(), N, size, int(max_crop), ctypes.addressof(m3),
+    _lib.check(lib.ssl4p_crop_resize_normalize_u8(frames.data_ptr(), desc.data_ptr(), N, size, int(max_crop),
+                                                  {"bicubic": 0, "bilinear": 1}[filter], ctypes.addressof(m3),
                                                   ctypes.addressof(s3), out.data_ptr(), ws.data_ptr(), ws.numel(), _stream()), "crop_resize")
     return out
 

@@ -461,5 +461,9 @@ def test_input_oracle_matches_pillow_torchvision_golden():
         torch.manual_seed(s); a = P.random_resized_crop_params(40 + 37 * s, 2000 - 61 * s)
         torch.manual_seed(s); b = IO.random_resized_crop_params(40 + 37 * s, 2000 - 61 * s)
         assert a == b, s
+    for sd in (0, 4, 6):
+        H, W = (int(v) for v in g[f"params{sd}"][:2])
+        t = IO.transform_eval(IO.synthetic_frame(sd, H, W))
+        assert hashlib.sha256(np.ascontiguousarray(t).tobytes()).digest() == g[f"eval_sha256_{sd}"].tobytes(), sd
     ks, b, k = IO.precompute_coeffs(1155, 0.0, 1155.0, 224)
     assert ks == 23 and int(b[:, 1].max()) <= ks and abs(int(k[100].sum()) - (1 << 22)) <= ks

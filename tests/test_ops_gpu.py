@@ -411,3 +411,23 @@ def test_train_transform_reproduces_the_compose_under_one_seed():
     m = models_mae.mae_vit_base_patch16(norm_pix_loss=True).cuda()
     loss, pred, mask = m(tf(frames), mask_ratio=0.75)
     assert torch.isfinite(loss) and pred.shape == (6, 196, 768)
+
+
+def test_eval_transform_bilinear_resize_bit_exact_against_pillow_golden():
+    """classification/data/transforms.py:233-258 (val / test): T.Resize((224,224)) PIL bilinear -> ToTensor -> Normalize."""
+    import hashlib
+    import numpy as np
+    from oracle import input_oracle as IO
+    from ssl4polyp_b200.input_pipeline import EvalTransform
+    g = _input_golden()
+    seeds = (0, 1, 4, 6, 7)
+    frames = []
+    for sd in seeds:
+        H, W = (int(v) for v in g[f"params{sd}"][:2])
+        frames.append(IO.synthetic_frame(sd, H, W))
+    got = EvalTransform(224)(frames).cpu().numpy()
+    for k, sd in enumerate(seeds):
+        assert hashlib.sha256(np.ascontiguousarray(got[k]).tobytes()).digest() == g[f"eval_sha256_{sd}"].tobytes(), sd
+    small = IO.synthetic_frame(3, 224, 224)
+    want = IO.transform_eval(small)
+    assert np.array_equal(EvalTransform(224)([small]).cpu().numpy()[0].view(np.uint32), want.view(np.uint32))
