@@ -98,11 +98,14 @@ __device__ __forceinline__ int clip8(int acc) {
     return acc < 0 ? 0 : (acc > 255 ? 255 : acc);
 }
 
+// kS > 0: the output size is a compile-time constant (224: the index divisions become multiplies); kS == 0: runtime S
+template <int kS>
 __global__ void __launch_bounds__(256)
 crop_resize_normalize_kernel(const uint8_t* __restrict__ frames, const long long* __restrict__ desc, const int* __restrict__ ws,
-                             int S, int band, int tile_rows, float m0, float m1, float m2, float s0, float s1, float s2,
+                             int S_rt, int band, int tile_rows, float m0, float m1, float m2, float s0, float s1, float s2,
                              float* __restrict__ out) {
     extern __shared__ uint8_t tile[];                                // [tile_rows][3 S] uint8: rows of the horizontally resized crop
+    const int S = kS > 0 ? kS : S_rt;
     const int n = blockIdx.y;
     const int r0 = blockIdx.x * band;
     const int rows = min(band, S - r0);
@@ -135,8 +138,10 @@ crop_resize_normalize_kernel(const uint8_t* __restrict__ frames, const long long
             const int xmin = bx[2 * xx], taps = bx[2 * xx + 1];
             const uint8_t* p = row + xmin * 3;
             int a0 = 1 << (kPrecBits - 1), a1 = a0, a2 = a0;
-            for (int x = 0; x < taps; ++x, p += 3) {
-                const int k = wx[x * S + xx];
+            const int* kp = wx + xx;
+#pragma unroll 4
+            for (int x = 0; x < taps; ++x, p += 3, kp += S) {
+                const int k = __ldg(kp);
                 a0 += (int)p[0] * k;
                 a1 += (int)p[1] * k;
                 a2 += (int)p[2] * k;
@@ -159,7 +164,9 @@ crop_resize_normalize_kernel(const uint8_t* __restrict__ frames, const long long
             const int ymin = by[2 * rr], taps = by[2 * rr + 1];
             const uint8_t* p = tile + (ymin - ylo) * row_bytes + xx * 3 + c;
             int acc = 1 << (kPrecBits - 1);
-            for (int t = 0; t < taps; ++t, p += row_bytes) acc += (int)(*p) * wy[t * S + rr];
+            const int* kp = wy + rr;
+#pragma unroll 4
+            for (int t = 0; t < taps; ++t, p += row_bytes, kp += S) acc += (int)(*p) * __ldg(kp);
             v = clip8(acc);
         } else {
             v = tile[(rr - r0) * row_bytes + xx * 3 + c];
@@ -198,21 +205,23 @@ extern "C" int ssl4p_crop_resize_normalize_u8(const void* frames, const long lon
     SSL4P_REQUIRE(ksize <= kMaxTaps, "crop_resize: a %d-pixel crop to %d needs %d taps per output (limit %d)", max_crop, S, ksize, kMaxTaps);
     SSL4P_REQUIRE(workspace && workspace_bytes >= ssl4p_crop_resize_workspace_bytes(N, S), "crop_resize: workspace too small");
     if (N == 0) return SSL4P_OK;
-    // the tallest band whose tile fits 96 KB (two CTAs per SM); a 1-row band always has to fit the 227 KB limit
+    // the tallest band whose tile fits the budget (56 KB: four CTAs per SM hide the byte-load latency of the horizontal pass)
+    static const int g_tile_kb = getenv("SSL4P_RESIZE_TILE_KB") ? atoi(getenv("SSL4P_RESIZE_TILE_KB")) : 56;   // measured: 96 -> 0.81 / 2.39 ms, 56 -> 0.70 / 2.17 ms (576x720 / 1072x1920 sources)
     int band = 1;
     const int cands[6] = {32, 16, 8, 4, 2, 1};
     size_t smem = 0;
     for (int i = 0; i < 6; ++i) {
         smem = (size_t)band_tile_rows(cands[i], max_crop, S) * 3 * S;
-        if (smem <= 96 * 1024 || cands[i] == 1) { band = cands[i]; break; }
+        if (smem <= (size_t)g_tile_kb * 1024 || cands[i] == 1) { band = cands[i]; break; }
     }
     SSL4P_REQUIRE(smem <= 227 * 1024, "crop_resize: crop %d -> %d does not fit shared memory", max_crop, S);
     const int tile_rows = band_tile_rows(band, max_crop, S);
-    SSL4P_CUDA(cudaFuncSetAttribute(crop_resize_normalize_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    auto kernel = S == 224 ? crop_resize_normalize_kernel<224> : crop_resize_normalize_kernel<0>;
+    SSL4P_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     resample_coeffs_kernel<<<dim3(N, 2), 256, 0, STREAM>>>(desc, S, filter, (int*)workspace);
     int rc = check_launch("resample_coeffs_kernel");
     if (rc) return rc;
-    crop_resize_normalize_kernel<<<dim3((S + band - 1) / band, N), 256, smem, STREAM>>>(
+    kernel<<<dim3((S + band - 1) / band, N), 256, smem, STREAM>>>(
         (const uint8_t*)frames, desc, (const int*)workspace, S, band, tile_rows,
         mean3[0], mean3[1], mean3[2], std3[0], std3[1], std3[2], out);
     return check_launch("crop_resize_normalize_kernel");

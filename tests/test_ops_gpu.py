@@ -431,3 +431,14 @@ def test_eval_transform_bilinear_resize_bit_exact_against_pillow_golden():
     small = IO.synthetic_frame(3, 224, 224)
     want = IO.transform_eval(small)
     assert np.array_equal(EvalTransform(224)([small]).cpu().numpy()[0].view(np.uint32), want.view(np.uint32))
+
+
+@pytest.mark.parametrize("size", [96, 225])
+def test_crop_resize_other_output_sizes_match_the_oracle(size):
+    """`--input_size` other than 224 takes the runtime-size instantiation of the kernel."""
+    import numpy as np
+    from oracle import input_oracle as IO
+    frame = IO.synthetic_frame(31, 333, 411)
+    got = _run_crop([frame], [(7, 9, 300, 380, True)], size=size)[0]
+    want = IO.to_tensor_normalize(IO.crop_resize_u8(frame, 7, 9, 300, 380, size), True)
+    assert got.shape == (3, size, size) and np.array_equal(got.view(np.uint32), want.view(np.uint32))
