@@ -333,8 +333,8 @@ def b200_arm(args):
 
 def gemm_traffic(model: str, batch: int):
     """DRAM bytes per gemm_tcgen05_kernel launch (read + write, average over the launches of one step) from the committed
-    ncu capture of this workload (profiles/r01i_gemm_traffic.{csv,json}); null for a workload that was not captured."""
-    path = os.path.join(ROOT, "profiles", "r01i_gemm_traffic.json")
+    ncu capture of this workload (profiles/r01l_gemm_traffic.{csv,json}); null for a workload that was not captured."""
+    path = os.path.join(ROOT, "profiles", "r01l_gemm_traffic.json")
     if model != "base" or batch != 256 or not os.path.exists(path):
         return None
     with open(path) as f:
