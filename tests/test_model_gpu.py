@@ -435,3 +435,80 @@ def test_main_pretrain_image_folder_with_device_transform(tmp_path):
     log = [l for l in open(out / "log.txt").read().splitlines() if l.strip()]
     import json
     assert math.isfinite(json.loads(log[-1])["train_loss"])
+
+
+def test_full_size_batch_256_properties():
+    """BASELINE configs[1] (ViT-B/16, B=256, mask 0.75, norm_pix_loss) is too large for the CPU oracle in a test, so the
+    full size is checked through size-independent properties: masking is a permutation ranking (bit-exact against
+    argsort(argsort(noise)) with ties broken by index), 147 masked patches per image, the loss equals an fp32 torch
+    restatement of models_mae.py:198-214 applied to the kernel's own pred/mask (rel 1e-4), rows of the batch are
+    independent (the first 8 images alone give the same pred), the run is bit-reproducible, and the decoder_pred.bias
+    gradient equals the column sums of d loss / d pred from torch autograd (cosine > 0.9999)."""
+    torch.manual_seed(0)
+    m = build_base(0, True)
+    B = 256
+    imgs = torch.randn(B, 3, 224, 224, generator=torch.Generator().manual_seed(1000)).to(dev())
+    noise = torch.rand(B, 196, generator=torch.Generator().manual_seed(7)).to(dev())
+    noise[3, 10] = noise[3, 150]; noise[5, :] = 0.25                                   # ties: one pair, and a whole row
+    for p in m.parameters():
+        p.grad = None
+    loss, pred, mask, ids_restore = m.forward_with_noise(imgs, noise, 0.75)
+    loss.backward()
+    torch.cuda.synchronize()
+    # (1) masking: stable double argsort, permutation, counts
+    ids_shuffle = torch.argsort(noise, dim=1, stable=True)
+    want_restore = torch.argsort(ids_shuffle, dim=1, stable=True)
+    assert ids_restore.dtype == torch.int64 and torch.equal(ids_restore, want_restore)
+    assert torch.equal(ids_restore.sort(dim=1).values, torch.arange(196, device=dev()).expand(B, 196))
+    assert torch.equal(mask, (ids_restore >= 49).float()) and torch.equal(mask.sum(1), torch.full((B,), 147.0, device=dev()))
+    assert torch.equal(ids_restore[5], torch.arange(196, device=dev()))              # all-equal row keeps index order
+    # (2) loss from the kernel's own pred / mask, fp32 torch restatement
+    pred_f = pred.detach().float().requires_grad_(True)
+    x = imgs.reshape(B, 3, 14, 16, 14, 16)
+    target = torch.einsum('nchpwq->nhwpqc', x).reshape(B, 196, 768)
+    mean, var = target.mean(dim=-1, keepdim=True), target.var(dim=-1, keepdim=True)
+    target = (target - mean) / (var + 1.e-6) ** .5
+    l = (((pred_f - target) ** 2).mean(dim=-1) * mask).sum() / mask.sum()
+    assert abs(loss.item() - l.item()) <= 1e-4 * abs(l.item()), (loss.item(), l.item())
+    # (3) d loss / d pred -> decoder_pred.bias gradient (column sums over every token row)
+    l.backward()
+    want_db = pred_f.grad.sum(dim=(0, 1)).double()
+    got_db = m.decoder_pred.bias.grad.double()
+    cos = float(got_db @ want_db / (got_db.norm() * want_db.norm()))
+    assert cos > 0.9999 and abs(float(got_db.norm() / want_db.norm()) - 1.0) < 2e-2, (cos, float(got_db.norm()), float(want_db.norm()))
+    assert all(p.grad is not None and torch.isfinite(p.grad).all() for p in m.parameters() if p.requires_grad)
+    # (4) rows are independent: the first 8 images alone
+    with torch.no_grad():
+        l8, pred8, mask8, ids8 = m.forward_with_noise(imgs[:8].contiguous(), noise[:8].contiguous(), 0.75)
+        assert torch.equal(ids8, ids_restore[:8]) and torch.equal(mask8, mask[:8])
+        d = (pred8.float() - pred[:8].float()).abs().max().item()
+        assert d <= 2e-2 * pred[:8].float().abs().max().item(), d
+        # (5) bit-reproducible
+        l2, pred2, _, _ = m.forward_with_noise(imgs, noise, 0.75)
+        assert torch.equal(pred2, pred) and l2.item() == loss.item()
+
+
+def test_full_size_classifier_batch_128_properties():
+    """BASELINE configs[3] (ViT-B/16 classifier, B=128, T=197) through properties: rows independent (first 4 images alone),
+    bit-reproducible, the engine's fused step == the module's autograd path (same loss, same lin_head gradient direction:
+    `lin_head.bias.grad` equals the batch sum of d loss / d logits from torch), all gradients finite."""
+    from ssl4polyp_b200 import models
+    torch.manual_seed(2)
+    m = models.ViT_from_MAE(None, True, 2, False, None, embed_dim=768, depth=12, num_heads=12, out_token="cls").to(dev()).train()
+    B = 128
+    imgs = torch.randn(B, 3, 224, 224, generator=torch.Generator().manual_seed(1000)).to(dev())
+    target = torch.randint(0, 2, (B,), generator=torch.Generator().manual_seed(2000)).to(dev())
+    logits = m(imgs)
+    assert logits.shape == (B, 2) and torch.isfinite(logits).all()
+    lg = logits.detach().clone().requires_grad_(True)
+    O.binary_polyp_loss(lg, target).backward()
+    loss = O.binary_polyp_loss(logits, target)
+    loss.backward()
+    got, want = m.lin_head.bias.grad.double(), lg.grad.sum(0).double()
+    assert torch.allclose(got, want, rtol=1e-4, atol=1e-7), (got, want)
+    assert all(p.grad is not None and torch.isfinite(p.grad).all() for p in m.parameters() if p.requires_grad)
+    with torch.no_grad():
+        again = m(imgs)
+        assert torch.equal(again, logits)
+        first = m(imgs[:4].contiguous())
+        assert (first - logits[:4]).abs().max().item() <= 2e-2 * max(1.0, logits.abs().max().item())
