@@ -154,28 +154,35 @@ crop_resize_normalize_kernel(const uint8_t* __restrict__ frames, const long long
     }
     __syncthreads();
 
-    // vertical pass out of the tile, then hflip -> /255 -> (x - mean) / std (torchvision to_tensor + normalize, fp32)
-    for (int idx = threadIdx.x; idx < rows * row_bytes; idx += blockDim.x) {
-        const int xx = idx % S;
-        const int c = (idx / S) % 3;
-        const int rr = r0 + idx / row_bytes;
-        int v;
+    // vertical pass out of the tile (one thread = one output pixel, three channel accumulators sharing each weight
+    // load), then hflip -> /255 -> (x - mean) / std (torchvision to_tensor + normalize, fp32)
+    for (int idx = threadIdx.x; idx < rows * S; idx += blockDim.x) {
+        const int r = idx / S, xx = idx - r * S;
+        const int rr = r0 + r;
+        int v0, v1, v2;
         if (vpass) {
             const int ymin = by[2 * rr], taps = by[2 * rr + 1];
-            const uint8_t* p = tile + (ymin - ylo) * row_bytes + xx * 3 + c;
-            int acc = 1 << (kPrecBits - 1);
+            const uint8_t* p = tile + (ymin - ylo) * row_bytes + xx * 3;
             const int* kp = wy + rr;
+            int a0 = 1 << (kPrecBits - 1), a1 = a0, a2 = a0;
 #pragma unroll 4
-            for (int t = 0; t < taps; ++t, p += row_bytes, kp += S) acc += (int)(*p) * __ldg(kp);
-            v = clip8(acc);
+            for (int t = 0; t < taps; ++t, p += row_bytes, kp += S) {
+                const int k = __ldg(kp);
+                a0 += (int)p[0] * k;
+                a1 += (int)p[1] * k;
+                a2 += (int)p[2] * k;
+            }
+            v0 = clip8(a0); v1 = clip8(a1); v2 = clip8(a2);
         } else {
-            v = tile[(rr - r0) * row_bytes + xx * 3 + c];
+            const uint8_t* p = tile + r * row_bytes + xx * 3;
+            v0 = p[0]; v1 = p[1]; v2 = p[2];
         }
-        const float mean = c == 0 ? m0 : (c == 1 ? m1 : m2);
-        const float sd = c == 0 ? s0 : (c == 1 ? s1 : s2);
-        const float f = __fdiv_rn(__fsub_rn(__fdiv_rn((float)v, 255.0f), mean), sd);
         const int xo = flip ? S - 1 - xx : xx;
-        out[(((size_t)n * 3 + c) * S + rr) * S + xo] = f;
+        float* o = out + (((size_t)n * 3) * S + rr) * S + xo;
+        const size_t plane = (size_t)S * S;
+        o[0] = __fdiv_rn(__fsub_rn(__fdiv_rn((float)v0, 255.0f), m0), s0);
+        o[plane] = __fdiv_rn(__fsub_rn(__fdiv_rn((float)v1, 255.0f), m1), s1);
+        o[2 * plane] = __fdiv_rn(__fsub_rn(__fdiv_rn((float)v2, 255.0f), m2), s2);
     }
 }
 
