@@ -301,9 +301,11 @@ def _limit(value):
 
 
 @torch.no_grad()
-def evaluate(model, loader, device, n_class, *, pos_weight=None, class_weights=None, tau=None, limit=None):
+def evaluate(model, loader, device, n_class, *, pos_weight=None, class_weights=None, tau=None, limit=None, frame_transform=None):
     """One pass in eval mode (reference `test`, :4653-5494, minus exports/perturbations/morphology): every logit stays
-    on the device until the end of the split, then one D2H copy and the host metrics."""
+    on the device until the end of the split, then one D2H copy and the host metrics.  A batch whose first element is a list
+    of uint8 HWC frames goes through `input_pipeline.EvalTransform` (Resize bilinear -> ToTensor -> Normalize, bit-identical to
+    classification/data/transforms.py:233-258 with augmentations off)."""
     was_training = model.training
     model.eval()
     logits, targets = [], []
@@ -311,6 +313,11 @@ def evaluate(model, loader, device, n_class, *, pos_weight=None, class_weights=N
         if limit is not None and b >= limit:
             break
         data, target = batch[0], batch[1]
+        if isinstance(data, (list, tuple)):             # decoded uint8 HWC frames: the val / test transform runs on the device
+            if frame_transform is None:
+                from .input_pipeline import EvalTransform
+                frame_transform = EvalTransform(224, device=device)
+            data = frame_transform(data)
         logits.append(model(data.to(device, non_blocking=True)).float())
         targets.append(target.to(device, non_blocking=True))
     model.train(was_training)

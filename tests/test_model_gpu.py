@@ -512,3 +512,23 @@ def test_full_size_classifier_batch_128_properties():
         assert torch.equal(again, logits)
         first = m(imgs[:4].contiguous())
         assert (first - logits[:4]).abs().max().item() <= 2e-2 * max(1.0, logits.abs().max().item())
+
+
+def test_evaluate_accepts_uint8_frames_through_the_device_eval_transform():
+    """`evaluate` on batches of decoded uint8 frames == `evaluate` on the oracle-transformed fp32 tensors (the reference's
+    val / test transform, classification/data/transforms.py:233-258)."""
+    import numpy as np
+    from oracle import input_oracle as IO
+    from ssl4polyp_b200 import models
+    from ssl4polyp_b200 import train_classification as TC
+    torch.manual_seed(3)
+    m = models.ViT_from_MAE(None, True, 2, False, None, embed_dim=768, depth=12, num_heads=12, out_token="cls").to(dev())
+    frames = [IO.synthetic_frame(60 + k, 200 + 31 * k, 260 + 17 * k) for k in range(6)]
+    labels = torch.tensor([0, 1, 0, 1, 1, 0])
+    as_frames = [(frames[:4], labels[:4]), (frames[4:], labels[4:])]
+    tensors = torch.from_numpy(np.stack([IO.transform_eval(f) for f in frames]))
+    as_tensors = [(tensors[:4], labels[:4]), (tensors[4:], labels[4:])]
+    a = TC.evaluate(m, as_frames, dev(), 2)
+    b = TC.evaluate(m, as_tensors, dev(), 2)
+    assert a["count"] == 6 and a["loss"] == b["loss"] and a["auroc"] == b["auroc"]
+    assert torch.equal(a["_probabilities"], b["_probabilities"])
