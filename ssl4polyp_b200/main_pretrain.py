@@ -293,9 +293,13 @@ def main(args):
         dist.barrier()
 
 
-if __name__ == '__main__':
-    args = get_args_parser()
-    args = args.parse_args()
+def cli(argv=None):
+    """Console entry point (`ssl4polyp-pretrain`); the reference runs the file as a script (main_pretrain.py:325-330)."""
+    args = get_args_parser().parse_args(argv)
     if args.output_dir:
         Path(args.output_dir).mkdir(parents=True, exist_ok=True)
     main(args)
+
+
+if __name__ == '__main__':
+    cli()
