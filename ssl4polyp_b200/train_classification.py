@@ -504,7 +504,7 @@ def run(args, loaders=None, log=print):
         monitor_value = float(source.get(monitor_key, float("nan")))
         say(f"epoch {epoch}: train_loss={loss:.5f} lr={lr:.3e} steps={steps} "
             + (f"val_loss={val['loss']:.5f} val_auroc={val['auroc']:.4f} " if val else "")
-            + (f"test_auroc={test['auroc']:.4f} " if test else "") + f"{monitor_name}={monitor_value:.5f} ({time.time() - t0:.1f}s)")
+            + (f"test_auroc={test['auroc']:.4f} " if test else "") + f"monitor[{monitor_name}]={monitor_value:.5f} ({time.time() - t0:.1f}s)")
         last.update(epoch=epoch, loss=loss, val=val, test=test, monitor=monitor_value)
         if improved(monitor_value, best, mode=monitor_mode, min_delta=float(args.early_stop_min_delta)):
             best, best_epoch, no_improve = monitor_value, epoch, 0
