@@ -31,7 +31,6 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
-F_STEP_GFLOP_PER_IMG = {"base": 58.164, "large": 123.839}     # 3 x forward matmul FLOPs
 METRIC = "MAE ViT-B/16 pretrain img/s @1/2/4/8 B200; % bf16 tensor-core peak"
 
 
@@ -46,6 +45,8 @@ def parse():
     ap.add_argument("--cpu-batch", type=int, default=8, help="batch of the CPU baseline sample (BASELINE configs[0])")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--extra", default="all", choices=["all", "none"],
+                    help="also time the other BASELINE configurations (ViT-L pretraining, ViT-B classifier) and report them as extra_configs")
     ap.add_argument("--no-graph", action="store_true", help="enqueue every kernel from Python instead of replaying the captured step")
     return ap.parse_args()
 
@@ -169,11 +170,144 @@ def reference_arm(args):
     print(json.dumps(line), flush=True)
 
 
-def b200_arm(args):
+WORKLOADS = {
+    # name: (label, F_step GFLOP/img, BASELINE.json config)
+    "mae_b": ("MAE ViT-B/16 pretraining step (fwd+loss+bwd+allreduce+AdamW), mask_ratio 0.75, norm_pix_loss", 58.164, "configs[1]/[2]"),
+    "mae_l": ("MAE ViT-L/16 pretraining step (fwd+loss+bwd+allreduce+AdamW), mask_ratio 0.75, norm_pix_loss", 123.839, "configs[4]"),
+    "cls_b": ("ViT-B/16 classification full fine-tune step (ViT_from_MAE, random-init, 2-class BCE on logit1-logit0, AdamW)", 105.378, "configs[3]"),
+}
+
+
+def build_workload(name, B, world, rank, dev):
+    """-> (engine, host batches [(tensors...), (tensors...)] in pinned memory).  Weights: the reference init under
+    torch.manual_seed(0) on every rank; images randn(seed 1000 + rank), targets randint(seed 2000 + rank)."""
+    import torch
+    from ssl4polyp_b200 import models_mae, utils
+    from ssl4polyp_b200.engine import ClassifierEngine, PretrainEngine
+    torch.manual_seed(0)
+    if name in ("mae_b", "mae_l"):
+        ctor = models_mae.mae_vit_base_patch16 if name == "mae_b" else models_mae.mae_vit_large_patch16
+        model = ctor(norm_pix_loss=True).to(dev).train()
+        eng = PretrainEngine(model, lr=1.5e-4 * (B * world) / 256, weight_decay=0.05, betas=(0.9, 0.95), mask_ratio=0.75)   # main_pretrain.py:201-204
+    else:
+        model = utils.get_MAE_backbone(None, True, 2, False, None, out_token="cls").to(dev).train()
+        eng = ClassifierEngine(model, lr=1e-5, weight_decay=0.05)
+    torch.manual_seed(0 + rank)                                       # masking noise stream: seed + rank (main_pretrain.py:147)
+    g = torch.Generator().manual_seed(1000 + rank)
+    host = []
+    for i in range(2):                                                # 2 x 154 MB at B=256: each larger than the 126 MB L2
+        t = [torch.randn(B, 3, 224, 224, generator=g).pin_memory()]
+        if name == "cls_b":
+            t.append(torch.randint(0, 2, (B,), generator=torch.Generator().manual_seed(2000 + rank + i)).pin_memory())
+        host.append(tuple(t))
+    return eng, host
+
+
+def measure(eng, host, B, world, dev, steps, warmup, use_graph, rank, local, want_e2e=True, sample_clocks=True):
+    """Device-timed leg (inputs resident) and end-to-end leg (HostPipeline: H2D every step, loss D2H every step)."""
     import torch
     import torch.distributed as dist
-    from ssl4polyp_b200 import _lib, models_mae, ops
-    from ssl4polyp_b200.engine import PretrainEngine
+    from ssl4polyp_b200 import _lib
+    from ssl4polyp_b200.engine import HostPipeline
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(ms: float) -> float:
+        if world == 1:
+            return ms
+        t = torch.tensor([ms], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    resident = [tuple(t.to(dev) for t in h) for h in host]
+    l_before = _lib.launch_count()
+    eng.step(*resident[0], graph=use_graph)                           # eager (the captured step replays exactly this launch list)
+    launches_per_step = _lib.launch_count() - l_before
+    for i in range(max(warmup, 3)):
+        eng.step(*resident[i % 2], graph=use_graph)
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0 and sample_clocks:
+        sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(steps):
+        loss = eng.step(*resident[i % 2], graph=use_graph)
+    e1.record()
+    barrier()
+    clocks = sampler.stop() if (rank == 0 and sample_clocks) else None
+    ms = max_over_ranks(e0.elapsed_time(e1))
+    out = {"value": B * world * steps / (ms / 1e3), "ms_per_step": ms / steps, "launches_per_step": launches_per_step,
+           "clocks": clocks, "loss": float(loss.item()), "nonfinite": eng.nonfinite_count()}
+    if want_e2e:
+        pipe = HostPipeline(eng, graph=use_graph)                     # the public host-fed path main_pretrain.train_one_epoch uses
+        seen = []
+        for i in range(max(2, min(warmup, 3))):
+            seen += pipe.submit(*host[i % 2])
+        seen += pipe.drain()
+        barrier()
+        pipe.h2d_bytes = 0
+        n_read = 0
+        e0.record()
+        for i in range(steps):
+            n_read += len(pipe.submit(*host[i % 2]))                  # losses arrive on the host one step late, every step
+        n_read += len(pipe.drain())
+        e1.record()
+        barrier()
+        assert n_read == steps
+        ms2 = max_over_ranks(e0.elapsed_time(e1))
+        out["e2e"] = {"value": B * world * steps / (ms2 / 1e3), "unit": "images/s",
+                      "h2d_bytes_per_step": int(pipe.h2d_bytes // steps * world), "d2h_bytes_per_step": 4 * world,
+                      "ms_per_step": ms2 / steps,
+                      "path": "engine.HostPipeline: pinned host batch -> H2D on a copy stream (double-buffered) -> captured step; "
+                              "loss D2H into a pinned slot every step, read by the host one step late"}
+    return out
+
+
+def dp_check(eng, world, rank, dev):
+    """N > 1: (1) after the timed steps every rank must hold bit-identical parameters (CRC of the fp32 arena, all-gathered);
+    (2) the mean over ranks of the per-rank gradients that comes out of the bucketed all-reduce must equal the 1-GPU gradient
+    of the concatenated batch (same images, same noise; each image has the same number of masked patches, so the two are
+    the same quantity): minimum per-parameter cosine and the relative L2 error of the whole arena."""
+    import zlib
+    import torch
+    import torch.distributed as dist
+    torch.cuda.synchronize()
+    crc = zlib.crc32(eng.store.flat.detach().cpu().numpy().tobytes())
+    t = torch.tensor([crc], dtype=torch.int64, device=dev)
+    allc = [torch.zeros_like(t) for _ in range(world)]
+    dist.all_gather(allc, t)
+    crcs = [int(x.item()) for x in allc]
+    b = 8
+    g = torch.Generator().manual_seed(4242)
+    imgs = torch.randn(world * b, 3, 224, 224, generator=g).to(dev)
+    noise = torch.rand(world * b, 196, generator=g).to(dev)
+    _, g_dp = eng.gradients(imgs[rank * b:(rank + 1) * b].contiguous(), noise[rank * b:(rank + 1) * b].contiguous(), reduce=True)
+    _, g_one = eng.gradients(imgs, noise, reduce=False)
+    worst, worst_name = 1.0, None
+    for name, (a, cnt) in eng.store.offsets.items():
+        if not eng.store.params[name].requires_grad:
+            continue
+        x, y = g_dp[a:a + cnt].double(), g_one[a:a + cnt].double()
+        c = float(x @ y / (x.norm() * y.norm()).clamp_min(1e-300))
+        if c < worst:
+            worst, worst_name = c, name
+    rel = float((g_dp.double() - g_one.double()).norm() / g_one.double().norm())
+    wt = torch.tensor([worst], dtype=torch.float64, device=dev)
+    dist.all_reduce(wt, op=dist.ReduceOp.MIN)
+    return {"params_bit_equal_across_ranks": len(set(crcs)) == 1, "param_crc32": crcs[0], "ranks": world,
+            "grad_min_cosine_dp_vs_single_gpu": float(wt.item()), "grad_rel_l2_err": rel, "worst_param": worst_name,
+            "check_batch": f"{world} ranks x {b} images vs one rank x {world * b} images"}
+
+
+def b200_arm(args):
+    import gc
+    import torch
+    import torch.distributed as dist
+    from ssl4polyp_b200 import ops
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -194,130 +328,75 @@ def b200_arm(args):
     assert world == args.gpus or world == 1, f"--gpus {args.gpus} but WORLD_SIZE={world}"
 
     B = args.batch
-    torch.manual_seed(0)                                              # same init on every rank (DDP would broadcast)
-    ctor = models_mae.mae_vit_base_patch16 if args.model == "base" else models_mae.mae_vit_large_patch16
-    model = ctor(norm_pix_loss=True).to(dev).train()
-    lr = 1.5e-4 * (B * world) / 256                                   # main_pretrain.py:201-204
-    eng = PretrainEngine(model, lr=lr, weight_decay=0.05, betas=(0.9, 0.95), mask_ratio=0.75)
-    torch.manual_seed(0 + rank)                                       # masking noise stream: seed + rank (main_pretrain.py:147)
-
-    g = torch.Generator().manual_seed(1000 + rank)
-    host = [torch.randn(B, 3, 224, 224, generator=g).pin_memory() for _ in range(2)]
-    resident = [h.to(dev) for h in host]                              # 2 x 154 MB at B=256: each larger than the 126 MB L2
-
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    def max_over_ranks(ms: float) -> float:
-        if world == 1:
-            return ms
-        t = torch.tensor([ms], dtype=torch.float64, device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item())
-
-    # ---- leg 1: inputs resident in HBM -------------------------------------------------------------------
     use_graph = not args.no_graph
-    l_before = _lib.launch_count()
-    eng.step(resident[0], graph=use_graph)                            # eager (the captured step replays exactly this launch list)
-    launches_per_step = _lib.launch_count() - l_before
-    for i in range(max(args.warmup, 3)):
-        eng.step(resident[i % 2], graph=use_graph)
-    barrier()
-    sampler = ClockSampler(local)
-    if rank == 0:
-        sampler.start()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for i in range(args.steps):
-        loss = eng.step(resident[i % 2], graph=use_graph)
-    e1.record()
-    barrier()
-    launches = launches_per_step * args.steps                         # kernels of ours executed in the timed region
-    clocks = sampler.stop() if rank == 0 else None
-    ms = max_over_ranks(e0.elapsed_time(e1))
-    ms_per_step = ms / args.steps
-    value = B * world * args.steps / (ms / 1e3)
-    loss_val = float(loss.item())
-    nonfinite = eng.nonfinite_count()
-
-    # ---- leg 2: end to end — pinned host batch -> H2D every step, loss -> host every step --------------------
-    e2e = None
-    if not args.no_e2e:
-        copy_stream = torch.cuda.Stream(device=dev)
-        bufs = [torch.empty_like(resident[0]) for _ in range(2)]
-        ready = [torch.cuda.Event(), torch.cuda.Event()]
-        consumed = [torch.cuda.Event(), torch.cuda.Event()]
-
-        def prefetch(i):
-            with torch.cuda.stream(copy_stream):
-                copy_stream.wait_event(consumed[i % 2])
-                bufs[i % 2].copy_(host[i % 2], non_blocking=True)
-                ready[i % 2].record(copy_stream)
-
-        def e2e_loop(n):
-            for b in consumed:
-                b.record(torch.cuda.current_stream())
-            prefetch(0)
-            out = 0.0
-            for i in range(n):
-                if i + 1 < n:
-                    prefetch(i + 1)
-                torch.cuda.current_stream().wait_event(ready[i % 2])
-                l = eng.step(bufs[i % 2], graph=use_graph)
-                consumed[i % 2].record(torch.cuda.current_stream())
-                out = float(l.item())                                  # D2H read of the step's result, every step
-            return out
-
-        e2e_loop(max(2, min(args.warmup, 3)))
-        barrier()
-        e0.record()
-        e2e_loop(args.steps)
-        e1.record()
-        barrier()
-        ms2 = max_over_ranks(e0.elapsed_time(e1))
-        e2e = {"value": B * world * args.steps / (ms2 / 1e3), "unit": "images/s",
-               "h2d_bytes_per_step": int(host[0].numel() * 4 * world), "d2h_bytes_per_step": 4 * world,
-               "ms_per_step": ms2 / args.steps}
+    head = "mae_b" if args.model == "base" else "mae_l"
+    pk = peaks()
+    eng, host = build_workload(head, B, world, rank, dev)
+    r = measure(eng, host, B, world, dev, args.steps, args.warmup, use_graph, rank, local, want_e2e=not args.no_e2e)
+    value, ms_per_step = r["value"], r["ms_per_step"]
 
     # ---- roofline leg: every GEMM launch of one step timed with CUDA events on the launching stream ---------
-    pk = peaks()
+    resident0 = tuple(t.to(dev) for t in host[0])
     ops.GEMM_PROFILE = []
-    eng.step(resident[0])
+    eng.step(*resident0)
     torch.cuda.synchronize()
     prof, ops.GEMM_PROFILE = ops.GEMM_PROFILE, None
     g_ms = sum(a.elapsed_time(b) for a, b, _, _ in prof)
     g_flops = sum(f for _, _, f, _ in prof)
     achieved = g_flops / (g_ms / 1e3) / 1e12 if g_ms > 0 else 0.0
-    step_tflops = F_STEP_GFLOP_PER_IMG[args.model] * 1e9 * B / (ms_per_step / 1e3) / 1e12
+    f_step = WORKLOADS[head][1]
+    step_tflops = f_step * 1e9 * B / (ms_per_step / 1e3) / 1e12
     roofline = {"bound": "tensor", "kernel": "gemm_tcgen05_kernel", "achieved": achieved, "peak": pk["tflops_sustained"],
                 "unit": "TFLOP/s", "frac": achieved / pk["tflops_sustained"], "traffic": gemm_traffic(args.model, B),
+                "traffic_source": "profiles/*_gemm_traffic.json (committed ncu capture of this workload; not re-measured by this run)",
                 "peak_source": f"{pk['source']} (bf16 sustained; burst {pk['tflops_burst']})",
                 "gemm_launches_per_step": len(prof), "gemm_ms_per_step": g_ms, "gemm_share_of_step": g_ms / ms_per_step,
                 "step_tflops_per_gpu": step_tflops, "step_frac_of_peak": step_tflops / pk["tflops_sustained"]}
+    check = dp_check(eng, world, rank, dev) if world > 1 else None
+    del eng, host, resident0, prof
+    gc.collect(); torch.cuda.empty_cache()
+
+    # ---- the other BASELINE configurations, each to the same timing rules, reported inside the one line ------
+    extra = {}
+    if args.extra != "none":
+        plan = [("mae_l" if head == "mae_b" else "mae_b", B), ("cls_b", 128)]
+        if world > 1:
+            plan.append(("cls_b", max(128 // world, 1)))              # configs[3] with the reference's GLOBAL --batch-size 128
+        for name, b in plan:                                          # (train_classification.py:5504: per-rank = global // world)
+            try:
+                e2, h2 = build_workload(name, b, world, rank, dev)
+                m = measure(e2, h2, b, world, dev, max(4, args.steps // 2), 3, use_graph, rank, local, want_e2e=not args.no_e2e)
+            except Exception as ex:                                   # an extra workload must never cost the headline line
+                extra[f"{name}_b{b}"] = {"error": f"{type(ex).__name__}: {ex}"[:300]}
+                continue
+            label, f, cfg = WORKLOADS[name]
+            tf = f * 1e9 * b / (m["ms_per_step"] / 1e3) / 1e12
+            extra[f"{name}_b{b}"] = {"workload": f"{label}, batch {b}/GPU (global {b * world})", "baseline_config": cfg,
+                                     "value": m["value"], "unit": "images/s", "ms_per_step": m["ms_per_step"],
+                                     "e2e": m.get("e2e"), "step_tflops_per_gpu": tf, "step_frac_of_peak": tf / pk["tflops_sustained"],
+                                     "clocks": m["clocks"], "gpu_launches_per_step": m["launches_per_step"], "loss": m["loss"]}
+            del e2, h2
+            gc.collect(); torch.cuda.empty_cache()
 
     # ---- CPU baseline (rank 0, N=1 only): bounded sample of the same step on the host cores -----------------
     cpu = None
     if world == 1 and not args.no_cpu_baseline:
-        r = run_cpu(args.model, args.cpu_batch, steps=4, warmup=1, budget_s=25.0)
-        cpu = {"value": r["img_s"], "unit": "images/s", "cores": r["cores"], "kind": "port",
-               "sample": f"{r['steps']} steps, batch {args.cpu_batch}, fp32 fwd+loss+bwd+AdamW of the same model (oracle/mae_oracle.py), "
-                         f"{r['ms_per_step']:.0f} ms/step"}
+        c = run_cpu(args.model, args.cpu_batch, steps=4, warmup=1, budget_s=25.0)
+        cpu = {"value": c["img_s"], "unit": "images/s", "cores": c["cores"], "kind": "port",
+               "sample": f"{c['steps']} steps, batch {args.cpu_batch}, fp32 fwd+loss+bwd+AdamW of the same model (oracle/mae_oracle.py), "
+                         f"{c['ms_per_step']:.0f} ms/step"}
 
     if rank == 0:
-        name = "B" if args.model == "base" else "L"
         line = {
             "metric": METRIC, "value": value, "unit": "images/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "bf16", "data": "synthetic",
-            "config": {"workload": f"MAE ViT-{name}/16 pretraining step (fwd+loss+bwd+allreduce+AdamW), mask_ratio 0.75, norm_pix_loss, "
-                                   f"batch {B}/GPU, 224x224 fp32 images",
+            "config": {"workload": f"{WORKLOADS[head][0]}, batch {B}/GPU, 224x224 fp32 images",
                        "global_batch": B * world, "parallelism": f"dp{world}",
                        "l2_policy": "two alternating 154 MB input batches (> 126 MB L2); per-step activations ~14 GB",
                        "launch": "whole step replayed from one CUDA graph" if use_graph else "eager (one C-ABI call per kernel)"},
-            "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu,
-            "loss": loss_val, "nonfinite_grad_blocks": nonfinite,
+            "clocks": r["clocks"], "e2e": r.get("e2e"), "gpu_launches": int(r["launches_per_step"] * args.steps), "roofline": roofline,
+            "cpu_baseline": cpu, "loss": r["loss"], "nonfinite_grad_blocks": r["nonfinite"], "dp_check": check, "extra_configs": extra,
         }
         print(json.dumps(line), flush=True)
     if world > 1:
@@ -334,11 +413,14 @@ def b200_arm(args):
 def gemm_traffic(model: str, batch: int):
     """DRAM bytes per gemm_tcgen05_kernel launch (read + write, average over the launches of one step) from the committed
     ncu capture of this workload (profiles/r01l_gemm_traffic.{csv,json}); null for a workload that was not captured."""
-    path = os.path.join(ROOT, "profiles", "r01l_gemm_traffic.json")
-    if model != "base" or batch != 256 or not os.path.exists(path):
+    if model != "base" or batch != 256:
         return None
-    with open(path) as f:
-        return json.load(f)["traffic_per_launch"]
+    for name in ("r02_gemm_traffic.json", "r01l_gemm_traffic.json"):
+        path = os.path.join(ROOT, "profiles", name)
+        if os.path.exists(path):
+            with open(path) as f:
+                return json.load(f)["traffic_per_launch"]
+    return None
 
 
 def main():

@@ -235,12 +235,21 @@ def binary_polyp_loss(logits, target, pos_weight=None):
     return F.binary_cross_entropy_with_logits(z, target.float(), pos_weight=pos_weight)
 
 
+def multiclass_loss(logits, target, class_weights=None):
+    """train_classification.py:6103 + :3374: `nn.CrossEntropyLoss(weight=class_weights)(logits, targets)`."""
+    return F.cross_entropy(logits, target, weight=class_weights)
+
+
 # ----------------------------------------------------------------------------------------------
 # a1 — initialisation, restated (models_mae.py:65-93) so the oracle can build weights without
 # the reference tree (the GPU box has no /root/reference).
 # ----------------------------------------------------------------------------------------------
-def init_state_dict(cfg: MAEConfig = MAE_BASE, seed: int = 0) -> dict:
-    """Draw weights with the same RNG call ORDER and distributions as constructing
+def init_state_dict(cfg: MAEConfig = MAE_BASE, seed: int = 0, head_classes: int | None = None) -> dict:
+    """head_classes: also draw `lin_head = nn.Linear(D, head_classes)` AFTER the MAE constructor, which is where
+    `ViT_from_MAE.__init__` (models.py:178-180) draws it; the decoder tensors that constructor deletes (:171-175) are
+    dropped (`decoder_pos_embed` stays, as in the reference).  make_cls_golden.py pins this bit-for-bit.
+
+    Draw weights with the same RNG call ORDER and distributions as constructing
     `MaskedAutoencoderViT` under `torch.manual_seed(seed)`: module construction first (default
     torch inits consume the generator), then `initialize_weights`.  make_golden.py checks that
     this reproduces the reference constructor bit-for-bit."""
@@ -295,6 +304,26 @@ def init_state_dict(cfg: MAEConfig = MAE_BASE, seed: int = 0) -> dict:
         sd["cls_token"], sd["mask_token"] = cls, mask_tok
         sd["pos_embed"] = sincos_pos_embed(D, cfg.grid).unsqueeze(0)
         sd["decoder_pos_embed"] = sincos_pos_embed(Dd, cfg.grid).unsqueeze(0)
+        if head_classes is not None:
+            head = nn.Linear(D, head_classes)
+            gone = ("mask_token", "decoder_embed.", "decoder_blocks.", "decoder_norm.", "decoder_pred.")
+            sd = {k: v for k, v in sd.items() if not k.startswith(gone)}
+            sd["lin_head.weight"], sd["lin_head.bias"] = head.weight.data, head.bias.data
+    return sd
+
+
+def vit_any_state_dict(seed: int, num_classes: int = 2, embed_dim: int = 768, depth: int = 12, num_heads: int = 12):
+    """Weights of `VisionTransformer_from_Any(head=True, ...)` under `torch.manual_seed(seed)`, drawn through the timm
+    shim (construction order and trunc_normal init of timm 0.4.12) WITHOUT the reference tree, so the GPU box can
+    rebuild them; make_cls_golden.py checks this against the reference constructor (models.py:47-62) bit-for-bit."""
+    import torch.nn as nn
+    from oracle import timm_shim
+    with torch.random.fork_rng(devices=[]):
+        torch.manual_seed(seed)
+        vt = timm_shim.VisionTransformer(patch_size=16, embed_dim=embed_dim, depth=depth, num_heads=num_heads)
+        lin_head = nn.Linear(embed_dim, num_classes)
+    sd = {k: v.detach().clone() for k, v in vt.state_dict().items() if not k.startswith("head.")}
+    sd["lin_head.weight"], sd["lin_head.bias"] = lin_head.weight.detach().clone(), lin_head.bias.detach().clone()
     return sd
 
 

@@ -14,7 +14,7 @@ _lib = None
 
 vp, i32, i64, f32, sz = C.c_void_p, C.c_int, C.c_longlong, C.c_float, C.c_size_t
 
-# name -> (restype, argtypes); must list every symbol include/ssl4p.h declares (tests/test_abi.py checks this)
+# name -> (restype, argtypes); must list every symbol include/ssl4p.h declares (tests/test_host.py::test_abi_header_symbols_exported_and_bound checks this)
 SIGNATURES = {
     "ssl4p_abi_version": (i32, []),
     "ssl4p_reserve_sms": (i32, [i32]),

@@ -47,6 +47,15 @@ def plan_buckets(offsets: dict, trainable: list, limit_elems: int, align: int = 
     return buckets
 
 
+def broadcast_parameters(flat: torch.Tensor, group=None, src: int = 0) -> None:
+    """Every rank starts from rank `src`'s parameter arena - what `DistributedDataParallel.__init__` does in the reference
+    (main_pretrain.py:212-214): ranks are seeded `seed + rank` BEFORE the model is built (:146-148), so without this
+    broadcast each replica would start from a different initialisation and the averaged gradients would be applied to N
+    different models."""
+    if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
+        dist.broadcast(flat, src=src, group=group)
+
+
 def configure_overlap(n_sms: int) -> None:
     """Call BEFORE `init_process_group`: cap NCCL at `n_sms` CTAs (= SMs).  Together with `ssl4p_reserve_sms(n_sms)`
     (done by the engine) the all-reduce and our persistent kernels run on disjoint SM sets.  The gradient all-reduce

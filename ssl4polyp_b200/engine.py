@@ -24,7 +24,7 @@ import torch
 import torch.distributed as dist
 
 from . import ops, vit_core
-from .dp import BucketReducer, plan_buckets
+from .dp import BucketReducer, broadcast_parameters, plan_buckets
 from .param_store import ALIGN
 
 
@@ -47,6 +47,9 @@ class TrainEngine:
         store = model._store
         store.sync()
         self.store = store
+        broadcast_parameters(store.flat, process_group)       # DDP's constructor broadcast (main_pretrain.py:212-214)
+        store.mark_dirty()
+        store.sync()                                           # refresh the bf16 shadow from the broadcast weights
         self.lr, self.wd, self.betas, self.eps = lr, weight_decay, betas, eps
         dev = store.flat.device
         self.device = dev
@@ -93,10 +96,11 @@ class TrainEngine:
             self.reducer.ready(name)
 
     # ---- one optimisation step -------------------------------------------------------------------------------
-    def backward_and_step(self, run_backward, lr=None, accumulate: bool = False, do_step: bool = True):
+    def backward_and_step(self, run_backward, lr=None, accumulate: bool = False, do_step: bool = True, apply: bool = True):
         """run_backward(sink) enqueues the backward; gradients are reduced across ranks as buckets complete when
         `do_step` (the reference all-reduces on every micro-step, engine_pretrain.py:64-72; summing locally and
-        reducing once on the boundary gives the same mean with 1/accum of the traffic)."""
+        reducing once on the boundary gives the same mean with 1/accum of the traffic).  apply=False stops after the
+        reduction: the gradient arena then holds the SUM over ranks (checks: `PretrainEngine.gradients`)."""
         self.sink.accumulate = accumulate
         self._reduce_now = do_step
         self.reducer.reset()
@@ -104,6 +108,8 @@ class TrainEngine:
         if not do_step:
             return
         self.reducer.finish()
+        if not apply:
+            return
         b1, b2 = self.betas
         if not torch.cuda.is_current_stream_capturing():
             self._set_lr(self.lr if lr is None else lr)
@@ -153,31 +159,93 @@ class TrainEngine:
         return int(self.nonfinite.item())
 
     # ---- optimiser state in torch.optim.AdamW's layout (checkpoint hand-off, util/misc.py:306-352) -----------
+    def _group_plan(self):
+        """[(group extras, [parameter names])] in the order the reference builds its optimizer param_groups."""
+        named = [(n, self.store.params[n]) for n in self.store.offsets]
+        return timm_weight_decay_plan(named, self.wd)
+
     def optimizer_state_dict(self):
-        state = {}
-        names = [n for n in self.store.offsets if self.store.params[n].requires_grad]
+        """`torch.optim.AdamW.state_dict()` of the optimizer the reference would have built over this model: the same
+        param_groups (order, 'params' index lists, hyper-parameters) and per-parameter `step` / `exp_avg` / `exp_avg_sq`,
+        so the reference's `optimizer.load_state_dict` (util/misc.py:349) accepts our checkpoints.  `param_names`
+        (index -> state-dict name) and `t` are extra keys torch ignores."""
+        groups, names, state = [], [], {}
+        b1, b2 = self.betas
+        for extras, gnames in self._group_plan():
+            idx = list(range(len(names), len(names) + len(gnames)))
+            names += gnames
+            g = {"lr": self.lr, "betas": (b1, b2), "eps": self.eps, "weight_decay": self.wd, "amsgrad": False,
+                 "maximize": False, "foreach": None, "capturable": False, "differentiable": False, "fused": None,
+                 "decoupled_weight_decay": True}
+            g.update(extras)
+            g["params"] = idx
+            groups.append(g)
         for i, nme in enumerate(names):
+            if not self.store.params[nme].requires_grad or self.t == 0:
+                continue                                       # torch creates state lazily, on the first step with a gradient
             a, cnt = self.store.offsets[nme]
             shape = self.store.params[nme].shape
             state[i] = {"step": torch.tensor(float(self.t)),
                         "exp_avg": self.exp_avg[a:a + cnt].view(shape).clone(),
                         "exp_avg_sq": self.exp_avg_sq[a:a + cnt].view(shape).clone()}
-        return {"state": state, "param_names": names, "t": self.t,
-                "param_groups": [{"lr": self.lr, "betas": self.betas, "eps": self.eps, "weight_decay": self.wd}]}
+        return {"state": state, "param_groups": groups, "param_names": names, "t": self.t}
 
     def load_optimizer_state_dict(self, sd):
-        names = sd.get("param_names") or [n for n in self.store.offsets if self.store.params[n].requires_grad]
+        """Accepts our own checkpoints and the reference's (`torch.optim.AdamW.state_dict()` without `param_names`): the
+        index -> name map is then rebuilt from the reference's group construction order; every shape is checked."""
+        names = sd.get("param_names")
+        if names is None:
+            names = [n for _, g in self._group_plan() for n in g]
+            n_idx = sum(len(g["params"]) for g in sd["param_groups"])
+            if n_idx != len(names):
+                raise RuntimeError(f"optimizer state has {n_idx} parameters in {len(sd['param_groups'])} groups; this model's "
+                                   f"reference optimizer would have {len(names)} - not a checkpoint of this architecture")
         self.t = int(sd.get("t", 0))
-        for i, nme in enumerate(names):
-            st = sd["state"].get(i)
-            if st is None or nme not in self.store.offsets:
-                continue
+        steps = set()
+        for i, st in sd["state"].items():
+            nme = names[int(i)]
+            if nme not in self.store.offsets:
+                raise RuntimeError(f"optimizer state names an unknown parameter {nme!r}")
             a, cnt = self.store.offsets[nme]
+            shape = tuple(self.store.params[nme].shape)
+            for k in ("exp_avg", "exp_avg_sq"):
+                if tuple(st[k].shape) != shape:
+                    raise RuntimeError(f"optimizer state {k} of {nme} has shape {tuple(st[k].shape)}, expected {shape}")
             self.exp_avg[a:a + cnt].copy_(st["exp_avg"].reshape(-1))
             self.exp_avg_sq[a:a + cnt].copy_(st["exp_avg_sq"].reshape(-1))
-            if not sd.get("t"):
-                self.t = int(float(st["step"]))
+            steps.add(int(float(st["step"])))
+        if "t" not in sd and steps:
+            if len(steps) > 1:
+                raise RuntimeError(f"per-parameter step counts differ ({sorted(steps)}); the fused AdamW keeps one counter")
+            self.t = steps.pop()
         self.hyper[1:2].fill_(float(self.t))
+
+
+def timm_weight_decay_plan(named_params, weight_decay: float):
+    """timm 0.4.12 `optim_factory.add_weight_decay(model, wd)` as called at main_pretrain.py:217: walk
+    `named_parameters()`, skip frozen tensors, `ndim == 1 or name.endswith(".bias")` -> the wd-0 group; the result is
+    `[{'params': no_decay, 'weight_decay': 0.}, {'params': decay, 'weight_decay': wd}]` in THAT order, which fixes the
+    parameter indices of `optimizer.state_dict()`."""
+    no_decay, decay = [], []
+    for name, p in named_params:
+        if not p.requires_grad:
+            continue
+        (no_decay if (p.ndim == 1 or name.endswith(".bias")) else decay).append(name)
+    return [({"weight_decay": 0.0}, no_decay), ({"weight_decay": float(weight_decay)}, decay)]
+
+
+def finetune_group_plan(named_params, lr: float):
+    """train_classification.py:5751-5768 over finetune.py:94-126: group "head" = the parameters of `lin_head` (frozen
+    or not), group "backbone" = every other parameter in `model.parameters()` order; a model without a separate head
+    puts everything in "head"."""
+    head = [n for n, _ in named_params if n.startswith("lin_head.")]
+    backbone = [n for n, _ in named_params if not n.startswith("lin_head.")]
+    if not head and backbone:
+        head, backbone = backbone, []
+    plan = [({"lr": lr, "name": "head"}, head)]
+    if backbone:
+        plan.append(({"lr": lr, "name": "backbone"}, backbone))
+    return plan
 
 
 class PretrainEngine(TrainEngine):
@@ -208,6 +276,16 @@ class PretrainEngine(TrainEngine):
                                accumulate=micro_index > 0, do_step=last)
         return loss
 
+    def gradients(self, imgs, noise, reduce: bool):
+        """Forward + backward WITHOUT the optimiser update -> (loss, gradient arena clone).  reduce=True sends the
+        gradients through the same bucketed all-reduce as `step` and returns the mean over ranks (what AdamW would have
+        consumed); reduce=False returns this rank's own gradient.  Used by bench.py's `dp_check`."""
+        m = self.model
+        loss, _, _, _, sv = vit_core.mae_fwd(self.store, m._dims, imgs, noise, m._len_keep(self.mask_ratio), m.norm_pix_loss, True)
+        self.backward_and_step(lambda sink: vit_core.mae_bwd(self.store, sink, m._dims, sv, self._one), do_step=reduce, apply=False)
+        g = self.grads.clone()
+        return loss, (g / self.world if reduce else g)
+
 
 class ClassifierEngine(TrainEngine):
     """Fine-tune step (train_classification.py:4525-4546): logits -> BCE-with-logits on logit1-logit0 (2 classes,
@@ -220,6 +298,9 @@ class ClassifierEngine(TrainEngine):
         super().__init__(model, lr, weight_decay, betas, **kw)
         self.pos_weight = pos_weight
         self.class_weights = class_weights      # CrossEntropyLoss(weight=...) for > 2 classes (:6103)
+
+    def _group_plan(self):
+        return finetune_group_plan([(n, self.store.params[n]) for n in self.store.offsets], self.lr)
 
     def step(self, imgs, target, lr=None, graph: bool = False):
         if graph:
@@ -235,6 +316,80 @@ class ClassifierEngine(TrainEngine):
         (dlogits,) = torch.autograd.grad(loss, lg)
         self.backward_and_step(lambda sink: vit_core.classifier_bwd(self.store, sink, m._dims, sv, dlogits.contiguous()), lr=lr)
         return loss.detach()
+
+
+class HostPipeline:
+    """Feeds an engine from HOST batches without ever letting the GPU wait for the host:
+
+      * batch i+1 is copied host -> device on a side stream (pinned source, double-buffered destination) while step i runs;
+      * the step itself is the captured CUDA graph (`engine.step(..., graph=True)`) whenever the batch has the static shape;
+      * the step's loss goes device -> host asynchronously into a pinned slot and is handed to the caller ONE step late,
+        when its event has completed - the reference's `loss.item()` + `torch.cuda.synchronize()` + scalar all-reduce per
+        iteration (engine_pretrain.py:55,74,81) without the pipeline bubble.  What the caller observes is unchanged: every
+        loss value, in order; a non-finite loss is seen one step later than in the reference.
+
+    `submit(batch..., lr=...)` enqueues one step and returns the losses that completed meanwhile (possibly none);
+    `drain()` returns the rest.  `depth` steps may be in flight."""
+
+    def __init__(self, engine: TrainEngine, graph: bool = True, depth: int = 2):
+        self.e, self.graph, self.depth = engine, graph, max(2, depth)
+        dev = engine.device
+        self.copy_stream = torch.cuda.Stream(device=dev)
+        self.bufs: list = [None] * self.depth
+        self.ready = [torch.cuda.Event() for _ in range(self.depth)]
+        self.consumed = [torch.cuda.Event() for _ in range(self.depth)]
+        self.loss_host = torch.zeros(self.depth, dtype=torch.float32).pin_memory()
+        self.loss_done = [torch.cuda.Event() for _ in range(self.depth)]
+        self.i = 0                       # steps submitted
+        self.j = 0                       # losses handed out
+        self.h2d_bytes = 0
+        self._static_shapes = None
+
+    def _harvest(self, block_until: int) -> list:
+        """Losses of steps [j, ...) whose D2H has completed; blocks for every step < block_until."""
+        out = []
+        while self.j < self.i:
+            ev = self.loss_done[self.j % self.depth]
+            if self.j < block_until:
+                ev.synchronize()
+            elif not ev.query():
+                break
+            out.append(float(self.loss_host[self.j % self.depth]))
+            self.j += 1
+        return out
+
+    def submit(self, *batch, lr=None, **step_kw) -> list:
+        done = self._harvest(self.i - self.depth + 1)          # frees this slot's loss word and device buffers
+        k = self.i % self.depth
+        cur = torch.cuda.current_stream()
+        on_host = not batch[0].is_cuda
+        if on_host:
+            shapes = [(tuple(t.shape), t.dtype) for t in batch]
+            if self.bufs[k] is None or [(tuple(t.shape), t.dtype) for t in self.bufs[k]] != shapes:
+                self.bufs[k] = [torch.empty(s, dtype=d, device=self.e.device) for s, d in shapes]
+            with torch.cuda.stream(self.copy_stream):
+                self.copy_stream.wait_event(self.consumed[k])
+                for dst, src in zip(self.bufs[k], batch):
+                    dst.copy_(src, non_blocking=True)
+                    self.h2d_bytes += src.numel() * src.element_size()
+                self.ready[k].record(self.copy_stream)
+            cur.wait_event(self.ready[k])
+            dev_batch = self.bufs[k]
+        else:
+            dev_batch = list(batch)
+        shapes = [tuple(t.shape) for t in dev_batch]
+        if self._static_shapes is None:
+            self._static_shapes = shapes
+        graph = self.graph and shapes == self._static_shapes and not step_kw.get("accum_iter", 1) > 1
+        loss = self.e.step(*dev_batch, lr=lr, graph=graph, **step_kw)
+        self.consumed[k].record(cur)
+        self.loss_host[k:k + 1].copy_(loss.detach().reshape(1), non_blocking=True)
+        self.loss_done[k].record(cur)
+        self.i += 1
+        return done
+
+    def drain(self) -> list:
+        return self._harvest(self.i)
 
 
 def cosine_lr(it_epoch: float, lr: float, min_lr: float, warmup_epochs: float, epochs: float) -> float:

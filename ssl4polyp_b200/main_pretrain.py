@@ -77,23 +77,28 @@ def get_args_parser():
     # not in the reference: run the Compose's pixel work (crop, bicubic resize, flip, normalise) on the GPU
     parser.add_argument('--device_transform', action='store_true',
                         help='DataLoader workers only decode; RandomResizedCrop/flip/ToTensor/Normalize run on the device (bit-identical)')
+    parser.add_argument('--no_graph', action='store_true',
+                        help='enqueue every kernel of the step from Python instead of replaying the captured CUDA graph (debugging)')
     return parser
 
 
 class _SyntheticBatches:
-    """`--data_path synthetic[:N]`: N batches per epoch of ImageNet-normalised-looking noise (no dataset on the box)."""
+    """`--data_path synthetic[:N]`: N batches per epoch of ImageNet-normalised-looking noise (no dataset on the box).
+    A pool of up to 4 distinct pinned batches is drawn once and cycled (two 154 MB batches already exceed the L2), so the
+    host never becomes the bottleneck the way a per-step `torch.randn` of 38 M values would."""
 
     def __init__(self, n, batch, size, seed):
         self.n, self.batch, self.size, self.seed = n, batch, size, seed
         self.sampler = None
+        g = torch.Generator().manual_seed(seed)
+        self.pool = [torch.randn(batch, 3, size, size, generator=g).pin_memory() for _ in range(min(n, 4))]
 
     def __len__(self):
         return self.n
 
     def __iter__(self):
-        g = torch.Generator().manual_seed(self.seed)
-        for _ in range(self.n):
-            yield torch.randn(self.batch, 3, self.size, self.size, generator=g).pin_memory(), None
+        for i in range(self.n):
+            yield self.pool[i % len(self.pool)], None
 
 
 def _init_distributed(args):
@@ -145,44 +150,82 @@ def _collate_frames(batch):
 
 
 def train_one_epoch(engine, data_loader, device, epoch, args, save_ckpt_fn=None, last_time_save=None, time_save_sec=None):
-    """One epoch of engine_pretrain.train_one_epoch (:22-100) on `PretrainEngine`."""
-    from .engine import cosine_lr
+    """One epoch of engine_pretrain.train_one_epoch (:22-100) on `PretrainEngine`, fed through `engine.HostPipeline`: the
+    step is the captured CUDA graph (when --accum_iter is 1), the next batch is copied to the device while the current
+    step runs, and each loss is read from a pinned slot one step late instead of `loss.item()` + `cuda.synchronize()` +
+    a scalar all-reduce per iteration (:55,74,81).  Kept observable behaviour: per-iteration lr schedule (:47-48),
+    `sys.exit(1)` on a non-finite loss (:59-62, seen one step late), the `Epoch: [e] [it/n]` log every 20 iterations, the
+    cross-rank mean loss in the returned stats (MetricLogger.synchronize_between_processes, :95) and the
+    `EpochSummary.finalize` block (util/misc.py:439-509) with its `throughput: ... samples/s` line: samples SUM-reduced
+    over ranks / epoch wall clock MAX-reduced over ranks."""
+    from .engine import HostPipeline, cosine_lr
     accum_iter = args.accum_iter
     n_iter = len(data_loader)
-    loss_sum, loss_cnt, lr = 0.0, 0, args.lr
+    pipe = getattr(engine, '_host_pipeline', None)
+    if pipe is None:                                   # kept on the engine: the captured graph and buffers live across epochs
+        pipe = engine._host_pipeline = HostPipeline(engine, graph=(accum_iter == 1) and not getattr(args, 'no_graph', False))
+    loss_sum, loss_sq_sum, loss_cnt, samples_seen, lr = 0.0, 0.0, 0, 0, args.lr
+    lrs = []
+    torch.cuda.synchronize()
     t0 = time.time()
+
+    def account(values, it_now):
+        nonlocal loss_sum, loss_sq_sum, loss_cnt
+        for v in values:
+            if not math.isfinite(v):
+                print("Loss is {}, stopping training".format(v))
+                sys.exit(1)
+            loss_sum += v
+            loss_sq_sum += v * v
+            loss_cnt += 1
+            it_done = loss_cnt - 1
+            if it_done % 20 == 0 or it_done == n_iter - 1:
+                print(f"Epoch: [{epoch}]  [{it_done:4d}/{n_iter}]  lr: {lrs[it_done]:.6f}  loss: {v:.4f} ({loss_sum / loss_cnt:.4f})  "
+                      f"time: {(time.time() - t0) / max(it_now, 1):.4f}")
+
     for it, (samples, _) in enumerate(data_loader):
         if it % accum_iter == 0:                       # per-iteration (not per-epoch) lr schedule
             lr = cosine_lr(it / n_iter + epoch, args.lr, args.min_lr, args.warmup_epochs, args.epochs)
+        lrs.append(lr)
         if isinstance(samples, list):                  # --device_transform: uint8 frames of any size
             if getattr(engine, '_device_tf', None) is None:          # kept off `args`: args is pickled into checkpoints
                 from .input_pipeline import TrainTransform
                 engine._device_tf = TrainTransform(args.input_size, device=device)
             samples = engine._device_tf(samples)
-        else:
-            samples = samples.to(device, non_blocking=True)
-        loss = engine.step(samples, lr=lr, accum_iter=accum_iter, micro_index=it % accum_iter)
-        loss_value = loss.item()                       # the reference syncs here too (engine_pretrain.py:55)
-        if not math.isfinite(loss_value):
-            print("Loss is {}, stopping training".format(loss_value))
-            sys.exit(1)
-        if args.distributed:                           # util/misc.py all_reduce_mean
-            t = torch.tensor([loss_value], device=device)
-            dist.all_reduce(t)
-            loss_value = (t / args.world_size).item()
-        loss_sum += loss_value
-        loss_cnt += 1
-        if it % 20 == 0 or it == n_iter - 1:
-            print(f"Epoch: [{epoch}]  [{it:4d}/{n_iter}]  lr: {lr:.6f}  loss: {loss_value:.4f} ({loss_sum / loss_cnt:.4f})  "
-                  f"time: {(time.time() - t0) / (it + 1):.4f}")
+        samples_seen += int(samples.shape[0])
+        kw = {} if accum_iter == 1 else {"accum_iter": accum_iter, "micro_index": it % accum_iter}
+        account(pipe.submit(samples, lr=lr, **kw), it + 1)
         if save_ckpt_fn is not None and last_time_save is not None and time_save_sec:
             if (time.time() - last_time_save[0]) >= time_save_sec:
+                account(pipe.drain(), it + 1)
                 save_ckpt_fn(epoch)
                 last_time_save[0] = time.time()
+    account(pipe.drain(), n_iter)
+    torch.cuda.synchronize()
+    epoch_time = time.time() - t0
     bad = engine.nonfinite_count()
-    if bad:
-        print(f"[warn] {bad} optimiser blocks saw a non-finite gradient so far")
-    return {"loss": loss_sum / max(loss_cnt, 1), "lr": lr}
+    stats = torch.tensor([loss_sum, loss_sq_sum, loss_cnt, samples_seen, n_iter, bad], dtype=torch.float64, device=device)
+    tmax = torch.tensor([epoch_time], dtype=torch.float64, device=device)
+    if args.distributed:                               # util/misc.py:455-470: one SUM and one MAX per EPOCH
+        dist.all_reduce(stats, op=dist.ReduceOp.SUM)
+        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+    g_sum, g_sq, g_cnt, g_samples, g_batches, g_bad = stats.tolist()
+    epoch_time = float(tmax.item())
+    mean = g_sum / g_cnt if g_cnt else float('nan')
+    std = math.sqrt(max(g_sq / g_cnt - mean * mean, 0.0)) if g_cnt > 1 else 0.0
+    throughput = g_samples / epoch_time if epoch_time > 0 else 0.0
+    if args.rank == 0:
+        print(f"Train epoch {epoch} summary:")
+        print(f"  loss: mean={mean:.6f}" + (f", std={std:.6f}" if g_cnt > 1 else "") if g_cnt else "  loss: mean=N/A")
+        if lrs:
+            lo, hi = min(lrs), max(lrs)
+            print("  lr: " + (f"{lo:.6f}" if math.isclose(lo, hi, rel_tol=1e-12, abs_tol=1e-12) else f"min={lo:.6f}, max={hi:.6f}"))
+        print(f"  throughput: {throughput:.2f} samples/s")
+        print(f"  wall clock: {epoch_time:.2f} s")
+        print(f"  data: batches={int(round(g_batches))}, samples={int(round(g_samples))}")
+        if g_bad:
+            print(f"  anomalies:\n    optimiser blocks with a non-finite gradient so far: {int(round(g_bad))}")
+    return {"loss": mean, "lr": lr, "throughput": throughput, "epoch_time": epoch_time}
 
 
 def main(args):
@@ -207,6 +250,8 @@ def main(args):
     print("actual lr: %.2e" % args.lr)
     print("accumulate grad iterations: %d" % args.accum_iter)
     print("effective batch size: %d" % eff_batch_size)
+    # Ranks are seeded `seed + rank` before the model is built, as in the reference (:146-148), so their initial weights
+    # differ; like DistributedDataParallel's constructor (:212-214) the engine broadcasts rank 0's parameter arena.
     engine = PretrainEngine(model, lr=args.lr, weight_decay=args.weight_decay, betas=(0.9, 0.95), mask_ratio=args.mask_ratio)
 
     if args.resume:                                    # util/misc.py load_model

@@ -98,7 +98,7 @@ class ViT_from_MAE(_ClassifierMixin, MaskedAutoencoderViT):
                          decoder_embed_dim=512, decoder_depth=8, decoder_num_heads=16, mlp_ratio=4,
                          norm_layer=partial(nn.LayerNorm, eps=1e-6))
         if weight_path is not None:
-            weights = torch.load(weight_path, map_location="cpu")["model"]
+            weights = torch.load(weight_path, map_location="cpu", weights_only=False)["model"]   # checkpoints carry argparse.Namespace ("args", util/misc.py:312-318)
             self.load_my_state_dict(weights)
         del self.mask_token
         del self.decoder_embed
@@ -194,7 +194,7 @@ class VisionTransformer_from_Any(_ClassifierMixin, nn.Module):
         state dict, non-strict)."""
         if str(checkpoint_path).lower().endswith(".npz"):
             raise NotImplementedError("numpy (.npz) checkpoints need timm's _load_weights, which is not part of the hot path")
-        ckpt = torch.load(checkpoint_path, map_location="cpu")
+        ckpt = torch.load(checkpoint_path, map_location="cpu", weights_only=False)
         sd = None
         if isinstance(ckpt, dict):
             for key in ("state_dict", "model", "model_state", "weights", "params"):

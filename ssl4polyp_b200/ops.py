@@ -34,13 +34,20 @@ def _req(t: torch.Tensor, dtype, name: str, contiguous: bool = True):
 
 
 _ws_cache: dict = {}
+_ws_retired: list = []      # superseded scratch buffers stay allocated: a captured CUDA graph may hold their addresses
 
 
 def workspace(nbytes: int, device, tag: str = "ws") -> torch.Tensor:
-    """Grow-only scratch arena per (device, tag); kernels on one stream are serialised, so reuse is safe."""
+    """Grow-only scratch arena per (device, tag); kernels on one stream are serialised, so reuse is safe.
+    A buffer that has to grow is replaced, never freed: `engine._replay` bakes workspace pointers into its CUDA graph,
+    and a later, larger eager call must not hand that memory back to the caching allocator under the graph.  Growth is
+    geometric (at least 2x), so the retired buffers add up to less than the live one."""
     key = (device.index if device.index is not None else torch.cuda.current_device(), tag)
     t = _ws_cache.get(key)
     if t is None or t.numel() < nbytes:
+        if t is not None:
+            _ws_retired.append(t)
+            nbytes = max(nbytes, 2 * t.numel())
         t = torch.empty(max(nbytes, 1 << 20), dtype=torch.uint8, device=device)
         _ws_cache[key] = t
     return t

@@ -210,8 +210,8 @@ def should_stop(no_improve: int, patience: int, epochs_done: int, min_epochs: in
 class SyntheticFrames:
     """`n` fp32 224x224 frames with seeded labels; a class-dependent mean shift makes the task learnable so the loop's
     metrics move.  Iterating yields `(images, labels)` host tensors in `batch`-sized chunks; `labels_list` mirrors
-    PackDataset's attribute that `build` reads class counts from (:5610-5622).  `shard=(rank, world)` takes every
-    world-th batch (training only; evaluation runs the whole split on every rank)."""
+    PackDataset's attribute that `build` reads class counts from (:5610-5622).  `shard=(rank, world)` splits the samples
+    like `DistributedSampler` (training only; evaluation runs the whole split on every rank)."""
 
     def __init__(self, n: int, batch: int, n_class: int = 2, image_size: int = 224, seed: int = 0, shard=(0, 1), shuffle=False):
         g = torch.Generator().manual_seed(seed)
@@ -232,19 +232,31 @@ class SyntheticFrames:
             out[j] = torch.randn(3, self.size, self.size, generator=g) + 0.35 * (float(self.labels[i]) - 0.5 * (self.n_class - 1))
         return out, self.labels[idx]
 
-    def __len__(self):
-        nb = (self.n + self.batch - 1) // self.batch
-        r, w = self.shard
-        return (nb - r + w - 1) // w
-
-    def __iter__(self):
+    def _rank_order(self) -> torch.Tensor:
+        """This rank's sample indices for the current epoch: `DistributedSampler` semantics (the reference's training
+        sampler) - pad the (shuffled) order to a multiple of the world size by wrapping around and take every world-th
+        sample, so EVERY rank sees the same number of samples and therefore the same number of equally-sized batches
+        (a rank with one step more would pair its bucket all-reduce with the other ranks' epoch-end collective)."""
         order = torch.arange(self.n)
         if self.shuffle:
             order = torch.randperm(self.n, generator=torch.Generator().manual_seed(self.seed + 7919 * self.epoch))
         r, w = self.shard
-        for b, start in enumerate(range(0, self.n, self.batch)):
-            if b % w == r:
-                yield self._frame_batch(order[start:start + self.batch])
+        if w > 1:
+            total = (self.n + w - 1) // w * w
+            if total > self.n:
+                order = torch.cat([order, order[:total - self.n]])
+            order = order[r::w]
+        return order
+
+    def __len__(self):
+        r, w = self.shard
+        per_rank = (self.n + w - 1) // w
+        return (per_rank + self.batch - 1) // self.batch
+
+    def __iter__(self):
+        order = self._rank_order()
+        for start in range(0, len(order), self.batch):
+            yield self._frame_batch(order[start:start + self.batch])
 
 
 def _class_weights(args, labels, n_class):

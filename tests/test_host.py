@@ -77,6 +77,61 @@ def test_oracle_base_forward_matches_reference_golden(golden):
     assert torch.equal(mask, c["mask"])
 
 
+CLS_GOLDEN = os.path.join(ROOT, "tests", "golden", "cls_golden.pt")
+
+
+@pytest.fixture(scope="module")
+def cls_golden():
+    return torch.load(CLS_GOLDEN)
+
+
+def cls_case_state_dict(c):
+    """Weights of a cls_golden case, rebuilt from its seed (pinned bit-for-bit to the reference constructors by
+    oracle/make_cls_golden.py)."""
+    if c["kind"] == "mae":
+        return O.init_state_dict(O.MAE_BASE, seed=c["seed"], head_classes=c["num_classes"])
+    return O.vit_any_state_dict(c["seed"], c["num_classes"])
+
+
+@pytest.mark.parametrize("idx", [0, 3, 4])
+def test_oracle_classifier_matches_reference_golden(cls_golden, idx):
+    """a13/a14/a17: `O.classifier_forward` + the loss glue against vectors produced by the UNMODIFIED reference
+    `models/models.py` (ViT_from_MAE :143-222, VisionTransformer_from_Any :26-140) and
+    `train_classification._compute_supervised_loss` (:3361-3374).  Cases 1 and 2 are covered by the GPU tests."""
+    c = cls_golden["cases"][idx]
+    sd = cls_case_state_dict(c)
+    assert torch.equal(subsample(sd["blocks.0.attn.qkv.weight"], 16), c["w_sample"])
+    assert torch.equal(sd["lin_head.weight"], c["head_w"])
+    frozen = ("pos_embed", "decoder_pos_embed") if c["kind"] == "mae" else ()
+    sd_g = {k: v.clone().requires_grad_(k not in frozen) for k, v in sd.items()}
+    logits = O.classifier_forward(sd_g, synth_imgs(c["B"], c["seed"]), O.MAE_BASE, c["out_token"], True)
+    if c["num_classes"] == 2:
+        loss = O.binary_polyp_loss(logits, c["target"], pos_weight=torch.tensor(c["pos_weight"]))
+    else:
+        loss = O.multiclass_loss(logits, c["target"], c["class_weights"])
+    loss.backward()
+    assert torch.allclose(logits.detach(), c["logits"], rtol=1e-5, atol=1e-6)
+    assert abs(loss.item() - c["loss"].item()) < 1e-6 * abs(c["loss"].item())
+    for k, gn in c["grad_norm"].items():
+        assert abs(sd_g[k].grad.norm().item() - gn.item()) <= 1e-3 * gn.item() + 1e-10, k
+    for k, gs in c["grad_sample"].items():
+        assert torch.allclose(subsample(sd_g[k].grad, 256), gs, rtol=1e-3, atol=1e-7), k
+
+
+def test_pretrain_lr_schedule_matches_reference_golden(cls_golden):
+    """a19: `engine.cosine_lr` (and the oracle's copy) against values computed by the reference's own
+    `util/lr_sched.py:9-21` over warm-up + decay (fixture written by oracle/make_cls_golden.py)."""
+    from ssl4polyp_b200.engine import cosine_lr
+    g = cls_golden["lr"]
+    for args, pts in ((g["args"], g["points"]), (g["short_args"], g["short_points"])):
+        for e, want in pts:
+            assert cosine_lr(e, args["lr"], args["min_lr"], args["warmup_epochs"], args["epochs"]) == want, e
+            assert O.cosine_lr(e, args["lr"], args["min_lr"], args["warmup_epochs"], args["epochs"]) == want, e
+    a = g["args"]
+    assert cosine_lr(0.0, **a) == 0.0 and cosine_lr(a["warmup_epochs"], **a) == a["lr"]
+    assert abs(cosine_lr(a["epochs"], **a) - a["min_lr"]) < 1e-12
+
+
 def test_oracle_patchify_roundtrip_and_len_keep():
     x = torch.randn(2, 3, 64, 64)
     assert torch.equal(O.unpatchify(O.patchify(x)), x)
@@ -211,9 +266,16 @@ def test_bucket_plan_covers_trainable_range_in_backward_order():
 _DP_WORKER = r"""
 import os, sys, torch, torch.distributed as dist
 sys.path.insert(0, sys.argv[3])
-from ssl4polyp_b200.dp import plan_buckets, BucketReducer
+from ssl4polyp_b200.dp import plan_buckets, BucketReducer, broadcast_parameters
 rank, world = int(sys.argv[1]), 2
 dist.init_process_group("gloo", init_method=f"tcp://127.0.0.1:{sys.argv[2]}", rank=rank, world_size=world)
+# ranks are seeded seed+rank before the model is built (main_pretrain.py:146-148): the arenas differ until rank 0's is broadcast
+torch.manual_seed(7 + rank)
+arena = torch.randn(5000)
+want0 = torch.randn(5000, generator=torch.Generator().manual_seed(7))
+assert torch.equal(arena, want0) == (rank == 0)
+broadcast_parameters(arena)
+assert torch.equal(arena, want0), "arena differs from rank 0's after the constructor broadcast"
 offsets, off = {}, 0
 for i in range(12):
     n = 1000 + 37 * i
@@ -254,6 +316,40 @@ def test_bucket_reducer_world_size_2_gloo(tmp_path):
         assert "ok" in out
 
 
+def test_synthetic_frames_shards_like_distributed_sampler():
+    """Every rank must see the same number of equally-sized batches (DistributedSampler pads by wrapping around)."""
+    from ssl4polyp_b200.train_classification import SyntheticFrames
+    for n, b, w in [(40, 8, 2), (41, 8, 2), (7, 4, 3), (40, 8, 1), (9, 2, 4)]:
+        loaders = [SyntheticFrames(n, b, 2, 8, 0, (r, w), shuffle=True) for r in range(w)]
+        shapes = [[x[0].shape[0] for x in l] for l in loaders]
+        assert all(s == shapes[0] for s in shapes), (n, b, w, shapes)
+        assert all(len(l) == len(shapes[0]) for l in loaders)
+        seen = torch.cat([l._rank_order() for l in loaders]).tolist()
+        assert set(seen) == set(range(n)) and len(seen) == (n + w - 1) // w * w
+
+
+def test_optimizer_state_layout_is_the_reference_adamw_state_dict():
+    """engine.optimizer_state_dict() must be what `torch.optim.AdamW(add_weight_decay(model, wd)).state_dict()` looks like
+    (timm 0.4.12 group order: no-decay first; main_pretrain.py:216-218), and for the fine-tune script the head / backbone
+    groups of train_classification.py:5751-5768 - checked against a real torch optimizer built the reference's way."""
+    from ssl4polyp_b200.engine import finetune_group_plan, timm_weight_decay_plan
+    net = torch.nn.ModuleDict({"patch": torch.nn.Conv2d(3, 8, 4, 4), "norm": torch.nn.LayerNorm(8), "fc": torch.nn.Linear(8, 8),
+                               "lin_head": torch.nn.Linear(8, 2)})
+    net.pos = torch.nn.Parameter(torch.zeros(1, 5, 8), requires_grad=False)
+    named = list(net.named_parameters())
+    plan = timm_weight_decay_plan(named, 0.05)
+    no_decay = [p for n, p in named if p.requires_grad and (p.ndim == 1 or n.endswith(".bias"))]
+    decay = [p for n, p in named if p.requires_grad and not (p.ndim == 1 or n.endswith(".bias"))]
+    opt = torch.optim.AdamW([{"params": no_decay, "weight_decay": 0.}, {"params": decay, "weight_decay": 0.05}], lr=1e-3, betas=(0.9, 0.95))
+    by_id = {id(p): n for n, p in named}
+    want = [[by_id[id(p)] for p in g["params"]] for g in opt.param_groups]
+    assert [g for _, g in plan] == want and "pos" not in sum(want, [])
+    assert [e["weight_decay"] for e, _ in plan] == [0.0, 0.05]
+    fplan = finetune_group_plan(named, 1e-4)
+    assert [e["name"] for e, _ in fplan] == ["head", "backbone"]
+    assert fplan[0][1] == ["lin_head.weight", "lin_head.bias"] and "pos" in fplan[1][1] and len(fplan[1][1]) == len(named) - 2
+
+
 def test_main_pretrain_parser_matches_the_reference_flag_for_flag():
     """Same flags and defaults as /root/reference/.../mae/main_pretrain.py:47-135 (parsed out of the reference source when
     the reference tree is present; the frozen expectation below otherwise)."""
@@ -266,7 +362,7 @@ def test_main_pretrain_parser_matches_the_reference_flag_for_flag():
         src = open(ref_path).read()
         ns = {"argparse": argparse, "Path": Path}
         exec(src[src.index("def get_args_parser"):src.index("def main(")], ns)
-        extra = {"device_transform"}                     # this implementation's own switch (input_pipeline.TrainTransform)
+        extra = {"device_transform", "no_graph"}         # this implementation's own switches (input_pipeline.TrainTransform; eager launches)
         assert vars(ns["get_args_parser"]().parse_args([])) == {k: v for k, v in ours.items() if k not in extra}
         assert ours["device_transform"] is False
     assert ours["batch_size"] == 64 and ours["model"] == "mae_vit_large_patch16" and ours["mask_ratio"] == 0.75

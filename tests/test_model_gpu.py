@@ -81,6 +81,16 @@ def test_mae_base_against_reference_golden(golden, idx):
         if r > 5e-2:
             bad.append((k, r))
     assert not bad, bad[:8]
+    # The fixture holds 64-element SAMPLES (bf16 round-off on 64 numbers leaves ~0.99 there); the stated bar - every
+    # parameter's FULL gradient cosine > 0.999, pred cosine > 0.999 - is checked on the same case against the oracle,
+    # which make_golden.py proved equal to the reference on exactly these inputs (loss 1e-5, pred 1e-4, grads 1e-3).
+    cfg = O.MAEConfig(**c["cfg"])
+    sd = O.init_state_dict(cfg, seed=seed)
+    loss_o, pred_o, mask_o, ids_o, grads_o = _oracle_run(cfg, sd, imgs, c["noise"], mr)
+    assert abs(loss_o.item() - c["loss"].item()) < 1e-5 * abs(c["loss"].item())
+    assert cos(pred.cpu(), pred_o) > 0.999
+    report = sorted((cos(grads[k].cpu(), g), k) for k, g in grads_o.items())
+    assert report[0][0] > GRAD_COS, report[:5]
 
 
 def _oracle_run(cfg, sd, imgs, noise, mr):
@@ -117,6 +127,67 @@ def _check_against_oracle(m, cfg, B, seed, mr, size):
 def test_mae_base_all_grads_against_oracle():
     m = build_base(5, True)
     _check_against_oracle(m, O.MAEConfig(norm_pix_loss=True), B=2, seed=5, mr=0.75, size=224)
+
+
+def test_mae_large_against_oracle():
+    """BASELINE configs[4] / SURVEY a10: `mae_vit_large_patch16` (D=1024, 24 blocks, 16 heads of 64, decoder 512/8/16;
+    reference models_mae.py:231-236) at B=2 - masking bit-exact, loss 1e-2, pred and every parameter's gradient
+    cosine > 0.999 against the oracle on the same weights / images / noise."""
+    from ssl4polyp_b200 import models_mae
+    torch.manual_seed(21)
+    m = models_mae.mae_vit_large_patch16(norm_pix_loss=True).to(dev()).train()
+    assert m.pos_embed.shape == (1, 197, 1024) and len(m.blocks) == 24 and len(m.decoder_blocks) == 8
+    cfg = O.MAEConfig(embed_dim=1024, depth=24, num_heads=16, norm_pix_loss=True)
+    worst = _check_against_oracle(m, cfg, B=2, seed=21, mr=0.75, size=224)
+    assert worst > GRAD_COS
+
+
+def _oracle_run_chunked(cfg, sd, imgs, noise, mr, chunk):
+    """The oracle over a large batch in chunks of `chunk` images with gradient accumulation.  Exact, not an
+    approximation: every image has the same number of masked patches, so the batch loss (models_mae.py:213) is the mean
+    of the chunk losses and its gradient the mean of the chunk gradients."""
+    B = imgs.shape[0]
+    assert B % chunk == 0
+    n = B // chunk
+    sd_g = {k: v.clone().requires_grad_(k not in ("pos_embed", "decoder_pos_embed")) for k, v in sd.items()}
+    loss_sum, preds, masks = 0.0, [], []
+    for i in range(n):
+        sl = slice(i * chunk, (i + 1) * chunk)
+        loss, pred, mask = O.mae_forward(sd_g, imgs[sl], noise[sl], mr, cfg)
+        (loss / n).backward()
+        loss_sum += loss.item() / n
+        preds.append(pred.detach()); masks.append(mask)
+    _, _, ids_restore = O.masking_from_noise(noise, mr)
+    return loss_sum, torch.cat(preds), torch.cat(masks), ids_restore, {k: v.grad for k, v in sd_g.items() if v.grad is not None}
+
+
+def test_full_size_batch_256_against_oracle():
+    """BASELINE configs[1] at its real size (ViT-B/16, B=256, mask 0.75, norm_pix_loss: M = 12 800 encoder / 50 432 decoder
+    token rows, i.e. the multi-tile, multi-wave, split-K-16 regime the benchmark runs in) against the CPU oracle on the
+    same weights, images and noise (with crafted ties): masking bit-exact, loss rel 1e-2, pred cosine > 0.999 and EVERY
+    parameter's gradient cosine > 0.999.  The oracle runs in 8 chunks of 32 images (exact, see _oracle_run_chunked)."""
+    torch.set_num_threads(max(torch.get_num_threads(), min(32, os.cpu_count() or 8)))
+    m = build_base(0, True)
+    cfg = O.MAEConfig(norm_pix_loss=True)
+    B = 256
+    imgs = synth_imgs(B, 0)
+    noise = torch.rand(B, 196, generator=torch.Generator().manual_seed(7))
+    noise[3, 10] = noise[3, 150]; noise[5, :] = 0.25; noise[200, ::2] = noise[200, 1::2]
+    sd = {k: v.detach().cpu().clone() for k, v in m.state_dict().items()}
+    loss, pred, mask, ids_restore = m.forward_with_noise(imgs.to(dev()), noise.to(dev()), 0.75)
+    loss.backward()
+    grads = {k: p.grad.cpu() for k, p in m.named_parameters() if p.grad is not None}
+    loss_o, pred_o, mask_o, ids_o, grads_o = _oracle_run_chunked(cfg, sd, imgs, noise, 0.75, 32)
+    assert torch.equal(ids_restore.cpu(), ids_o) and torch.equal(mask.cpu(), mask_o)
+    assert abs(loss.item() - loss_o) / abs(loss_o) < LOSS_RTOL, (loss.item(), loss_o)
+    assert cos(pred.cpu(), pred_o) > 0.999
+    per_image = torch.nn.functional.cosine_similarity(pred.cpu().flatten(1).double(), pred_o.flatten(1).double(), dim=1)
+    assert per_image.min().item() > 0.998, per_image.min().item()
+    assert set(grads) == set(grads_o)
+    report = sorted((cos(grads[k], g), k) for k, g in grads_o.items())
+    assert report[0][0] > GRAD_COS, report[:6]
+    norms = [(k, grads[k].norm().item() / g.norm().item()) for k, g in grads_o.items()]
+    assert all(abs(r - 1.0) < 3e-2 for _, r in norms), [x for x in norms if abs(x[1] - 1.0) >= 3e-2][:6]
 
 
 def test_mae_small_config_against_oracle():
@@ -191,6 +262,66 @@ def test_piecewise_api_matches_fused_forward():
     assert torch.equal(xm.cpu(), torch.gather(x.cpu(), 1, ik.unsqueeze(-1).expand(-1, -1, 768)))
 
 
+CLS_GOLDEN = os.path.join(os.path.dirname(__file__), "golden", "cls_golden.pt")
+
+
+def _worst_cosines(named_grads, want, n=6):
+    """[(cosine, name)] ascending; `want` name -> oracle gradient."""
+    rep = []
+    for k, g in want.items():
+        assert named_grads.get(k) is not None, k
+        rep.append((cos(named_grads[k].cpu(), g), k))
+    return sorted(rep)[:n]
+
+
+@pytest.mark.parametrize("idx", [0, 1, 2, 3, 4])
+def test_classifier_against_reference_golden(idx):
+    """a13 / a14 / a17 against vectors produced by the UNMODIFIED reference (`models/models.py:26-222`,
+    `train_classification.py:3347-3374`; fixture by oracle/make_cls_golden.py): logits, loss, gradient norms and samples
+    from the fixture, and every parameter's full gradient (cosine > 0.999) against the oracle on the same weights,
+    which make_cls_golden.py showed to agree with the reference to fp32 round-off on exactly these inputs."""
+    from ssl4polyp_b200 import models
+    c = torch.load(CLS_GOLDEN)["cases"][idx]
+    if c["kind"] == "mae":
+        sd = O.init_state_dict(O.MAE_BASE, seed=c["seed"], head_classes=c["num_classes"])
+        m = models.ViT_from_MAE(None, True, c["num_classes"], False, None, embed_dim=768, depth=12, num_heads=12, out_token=c["out_token"])
+        frozen = ("pos_embed", "decoder_pos_embed")
+    else:
+        sd = O.vit_any_state_dict(c["seed"], c["num_classes"])
+        m = models.VisionTransformer_from_Any(True, c["num_classes"], False, None, 768, 12, 12, c["out_token"])
+        frozen = ()
+    assert torch.equal(subsample(sd["blocks.0.attn.qkv.weight"], 16), c["w_sample"]) and torch.equal(sd["lin_head.weight"], c["head_w"])
+    missing, unexpected = m.load_state_dict(sd, strict=False)
+    assert not missing and set(unexpected) <= {"decoder_pos_embed"}, (missing, unexpected)
+    m = m.to(dev()).train()
+    imgs, target = synth_imgs(c["B"], c["seed"]), c["target"]
+
+    def loss_of(lg, tg):
+        if c["num_classes"] == 2:
+            return O.binary_polyp_loss(lg, tg, pos_weight=torch.tensor(c["pos_weight"], device=lg.device))
+        return O.multiclass_loss(lg, tg, c["class_weights"].to(lg.device))
+
+    logits = m(imgs.to(dev()))
+    assert logits.shape == c["logits"].shape and logits.dtype == torch.float32
+    assert (logits.cpu() - c["logits"]).abs().max().item() < 2e-2 * max(1.0, c["logits"].abs().max().item())
+    loss = loss_of(logits, target.to(dev()))                  # B x ncls scalars of glue stay in torch (SURVEY K22)
+    assert abs(loss.item() - c["loss"].item()) / abs(c["loss"].item()) < LOSS_RTOL
+    loss.backward()
+    grads = {k: p.grad for k, p in m.named_parameters() if p.grad is not None}
+    assert set(grads) == set(c["grad_norm"]), set(grads) ^ set(c["grad_norm"])
+    bad = [(k, grads[k].norm().item(), gn.item()) for k, gn in c["grad_norm"].items()
+           if abs(grads[k].norm().item() - gn.item()) > 3e-2 * gn.item()]
+    assert not bad, bad[:8]
+    for k, gs in c["grad_sample"].items():
+        assert cos(subsample(grads[k].cpu(), 256), gs) > 0.995, (k, cos(subsample(grads[k].cpu(), 256), gs))
+    sd_g = {k: v.clone().requires_grad_(k not in frozen) for k, v in sd.items()}
+    logits_o = O.classifier_forward(sd_g, imgs, O.MAE_BASE, c["out_token"], True)
+    loss_of(logits_o, target).backward()
+    assert torch.allclose(logits_o.detach(), c["logits"], rtol=1e-5, atol=1e-6)
+    worst = _worst_cosines(grads, {k: v.grad for k, v in sd_g.items() if v.grad is not None})
+    assert worst[0][0] > GRAD_COS, worst
+
+
 def test_classifier_against_oracle():
     from ssl4polyp_b200 import models
     torch.manual_seed(2)
@@ -209,12 +340,8 @@ def test_classifier_against_oracle():
     loss = O.binary_polyp_loss(logits, target.to(dev()))          # 4 scalars of glue, stays in torch
     assert abs(loss.item() - loss_o.item()) / abs(loss_o.item()) < LOSS_RTOL
     loss.backward()
-    for k, v in sd_g.items():
-        if v.grad is None:
-            continue
-        g = dict(m.named_parameters())[k].grad
-        assert g is not None, k
-        assert cos(g.cpu(), v.grad) > 0.995, (k, cos(g.cpu(), v.grad))
+    worst = _worst_cosines({k: p.grad for k, p in m.named_parameters()}, {k: v.grad for k, v in sd_g.items() if v.grad is not None})
+    assert worst[0][0] > GRAD_COS, worst
 
 
 def test_vit_from_any_against_oracle():
@@ -240,10 +367,8 @@ def test_vit_from_any_against_oracle():
     loss.backward()
     params = dict(m.named_parameters())
     assert params["pos_embed"].grad is not None
-    for k, v in sd_g.items():
-        g = params[k].grad
-        assert g is not None, k
-        assert cos(g.cpu(), v.grad) > 0.995, (k, cos(g.cpu(), v.grad))
+    worst = _worst_cosines({k: p.grad for k, p in params.items()}, {k: v.grad for k, v in sd_g.items()})
+    assert worst[0][0] > GRAD_COS, worst
     # the fused fine-tune step (ClassifierEngine) accepts it too
     from ssl4polyp_b200.engine import ClassifierEngine
     eng = ClassifierEngine(m, lr=5e-5, weight_decay=0.05)
@@ -366,6 +491,108 @@ def test_main_pretrain_cli_synthetic_run_and_resume(tmp_path):
                                             ["--resume", str(out / "ckpts" / "checkpoint-1.pth")])
     MP.main(args2)
     assert args2.start_epoch == 2 and (out / "ckpts" / "checkpoint-2.pth").exists()
+    assert all(l["train_throughput"] > 0 for l in [json.loads(x) for x in open(out / "log.txt")][-1:])
+    # (1) the optimizer entry is a torch.optim.AdamW state dict in the reference's layout: an AdamW built the reference's way
+    # (timm add_weight_decay groups, main_pretrain.py:216-218) over a model with the same parameters loads it as is
+    from ssl4polyp_b200 import models_mae, utils
+    ref_like = models_mae.mae_vit_base_patch16(norm_pix_loss=True)
+    opt = torch.optim.AdamW(O.weight_decay_groups(ref_like.named_parameters(), 0.05), lr=1e-3, betas=(0.9, 0.95))
+    opt.load_state_dict(ck["optimizer"])
+    by_param = {id(p): n for n, p in ref_like.named_parameters()}
+    assert len(opt.state) == sum(p.requires_grad for p in ref_like.parameters())
+    for p_, st in opt.state.items():
+        assert st["exp_avg"].shape == p_.shape and float(st["step"]) == 6.0, by_param[id(p_)]     # 2 epochs x 3 iterations
+    assert [g["weight_decay"] for g in opt.param_groups] == [0.0, 0.05]
+    # ... and the other direction: the state dict of that torch optimizer (no `param_names`) goes back into an engine
+    from ssl4polyp_b200.engine import PretrainEngine
+    m2 = models_mae.mae_vit_base_patch16(norm_pix_loss=True).to(dev())
+    eng2 = PretrainEngine(m2, lr=1e-3)
+    eng2.load_optimizer_state_dict(opt.state_dict())
+    a, n = eng2.store.offsets["blocks.3.mlp.fc1.weight"]
+    want = ck["optimizer"]["state"][ck["optimizer"]["param_names"].index("blocks.3.mlp.fc1.weight")]["exp_avg"]
+    assert eng2.t == 6 and torch.equal(eng2.exp_avg[a:a + n].cpu().view_as(want), want)
+    bad = opt.state_dict(); bad["param_groups"][0]["params"] = bad["param_groups"][0]["params"][:-1]
+    with pytest.raises(RuntimeError, match="not a checkpoint of this architecture"):
+        eng2.load_optimizer_state_dict(bad)
+    # (2) the pretrain -> fine-tune hand-off takes the checkpoint this script wrote (it pickles argparse.Namespace)
+    cls = utils.get_MAE_backbone(str(out / "ckpts" / "checkpoint-1.pth"), True, 2, False, None)
+    assert torch.equal(cls.state_dict()["blocks.7.attn.qkv.weight"].cpu(), ck["model"]["blocks.7.attn.qkv.weight"])
+
+
+def test_module_inside_distributed_data_parallel():
+    """The reference wraps the model in DistributedDataParallel(find_unused_parameters=True) (main_pretrain.py:212-214) and
+    drives it with a stock torch optimizer.  The drop-in module has to survive that wrapper: DDP's constructor broadcast
+    writes the parameters in place (the arena views stay intact), its autograd hooks see our hand-written backward's
+    gradients, and an AdamW step through `param.data` is picked up by the next forward (bf16 shadow refresh).
+    gloo cannot hold CUDA-kernel modules on CPU, so this is a 1-rank NCCL group on the one GPU."""
+    import socket
+    import torch.distributed as dist
+    from torch.nn.parallel import DistributedDataParallel as DDP
+    s_ = socket.socket(); s_.bind(("127.0.0.1", 0)); port = s_.getsockname()[1]; s_.close()
+    dist.init_process_group("nccl", init_method=f"tcp://127.0.0.1:{port}", rank=0, world_size=1, device_id=dev())
+    try:
+        plain, wrapped = _small_mae(3), _small_mae(3)
+        ddp = DDP(wrapped, device_ids=[0], find_unused_parameters=True)
+        opt = torch.optim.AdamW(ddp.parameters(), lr=1e-3, betas=(0.9, 0.95))
+        opt_p = torch.optim.AdamW(plain.parameters(), lr=1e-3, betas=(0.9, 0.95))
+        imgs = synth_imgs(4, 2, 64).to(dev())
+        for it in range(3):
+            torch.manual_seed(50 + it)
+            loss_p, _, _ = plain(imgs, 0.75)
+            torch.manual_seed(50 + it)
+            loss_w, pred, mask = ddp(imgs, mask_ratio=0.75)
+            assert loss_w.item() == loss_p.item(), (it, loss_w.item(), loss_p.item())
+            opt.zero_grad(set_to_none=True); opt_p.zero_grad(set_to_none=True)
+            loss_w.backward(); loss_p.backward()
+            for (k, a), (_, b) in zip(wrapped.named_parameters(), plain.named_parameters()):
+                assert (a.grad is None) == (b.grad is None), k
+                if a.grad is not None:
+                    assert torch.equal(a.grad, b.grad), k
+            opt.step(); opt_p.step()
+        assert wrapped._store._intact(), "DDP re-pointed the parameters away from the arena"
+        assert loss_w.item() < 10 and math.isfinite(loss_w.item())
+    finally:
+        dist.destroy_process_group()
+
+
+def test_main_pretrain_cli_runs_the_benchmarked_path():
+    """The drop-in command line must run the path bench.py measures: captured step, host batches prefetched on a copy
+    stream, loss read one step late.  `--data_path synthetic:40 --batch_size 256`: the `throughput: ... samples/s` of the
+    reference's epoch summary (util/misc.py:485,509) on the second epoch has to be within 10 % of the end-to-end figure
+    measured bench.py's way (engine.HostPipeline over the same engine class) in this process."""
+    import contextlib
+    import io
+    import re
+    from ssl4polyp_b200 import main_pretrain as MP
+    argv = ["--model", "mae_vit_base_patch16", "--norm_pix_loss", "--batch_size", "256", "--epochs", "2", "--warmup_epochs", "1",
+            "--blr", "1.5e-4", "--data_path", "synthetic:40", "--output_dir", ""]
+    buf = io.StringIO()
+    with contextlib.redirect_stdout(buf):
+        MP.main(MP.get_args_parser().parse_args(argv))
+    text = buf.getvalue()
+    thr = [float(x) for x in re.findall(r"throughput: ([0-9.]+) samples/s", text)]
+    assert len(thr) == 2 and "Train epoch 1 summary:" in text and "data: batches=40, samples=10240" in text
+    from ssl4polyp_b200 import models_mae
+    from ssl4polyp_b200.engine import HostPipeline, PretrainEngine
+    torch.manual_seed(0)
+    eng = PretrainEngine(models_mae.mae_vit_base_patch16(norm_pix_loss=True).to(dev()), lr=1e-4)
+    host = [torch.randn(256, 3, 224, 224).pin_memory() for _ in range(2)]
+    pipe = HostPipeline(eng)
+    for i in range(4):
+        pipe.submit(host[i % 2])
+    pipe.drain()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    n = 0
+    for i in range(40):
+        n += len(pipe.submit(host[i % 2]))
+    n += len(pipe.drain())
+    e1.record()
+    torch.cuda.synchronize()
+    assert n == 40
+    e2e = 256 * 40 / (e0.elapsed_time(e1) / 1e3)
+    assert abs(thr[1] - e2e) / e2e < 0.10, (thr, e2e)
 
 
 def test_train_classification_cli_synthetic_run(tmp_path):
