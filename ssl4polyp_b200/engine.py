@@ -367,6 +367,10 @@ class HostPipeline:
             shapes = [(tuple(t.shape), t.dtype) for t in batch]
             if self.bufs[k] is None or [(tuple(t.shape), t.dtype) for t in self.bufs[k]] != shapes:
                 self.bufs[k] = [torch.empty(s, dtype=d, device=self.e.device) for s, d in shapes]
+                # The caching allocator hands out blocks in the order of the ALLOCATING (compute) stream: this block may
+                # still be in use by kernels already enqueued there (activations of an earlier step).  The copy stream
+                # must not write it before they have run.
+                self.copy_stream.wait_stream(cur)
             with torch.cuda.stream(self.copy_stream):
                 self.copy_stream.wait_event(self.consumed[k])
                 for dst, src in zip(self.bufs[k], batch):
