@@ -337,10 +337,12 @@ def b200_arm(args):
 
     # ---- roofline leg: every GEMM launch of one step timed with CUDA events on the launching stream ---------
     resident0 = tuple(t.to(dev) for t in host[0])
-    ops.GEMM_PROFILE = []
+    overlap, eng.sink.overlap = eng.sink.overlap, False               # one stream: each GEMM is timed alone, not while sharing the
+    ops.GEMM_PROFILE = []                                             # SMs with the side stream's weight-gradient kernels
     eng.step(*resident0)
     torch.cuda.synchronize()
     prof, ops.GEMM_PROFILE = ops.GEMM_PROFILE, None
+    eng.sink.overlap = overlap
     g_ms = sum(a.elapsed_time(b) for a, b, _, _ in prof)
     g_flops = sum(f for _, _, f, _ in prof)
     achieved = g_flops / (g_ms / 1e3) / 1e12 if g_ms > 0 else 0.0
@@ -394,7 +396,9 @@ def b200_arm(args):
             "config": {"workload": f"{WORKLOADS[head][0]}, batch {B}/GPU, 224x224 fp32 images",
                        "global_batch": B * world, "parallelism": f"dp{world}",
                        "l2_policy": "two alternating 154 MB input batches (> 126 MB L2); per-step activations ~14 GB",
-                       "launch": "whole step replayed from one CUDA graph" if use_graph else "eager (one C-ABI call per kernel)"},
+                       "launch": "whole step replayed from one CUDA graph" if use_graph else "eager (one C-ABI call per kernel)",
+                       "streams": "dgrad chain on the main stream; weight-gradient GEMMs + their reductions on a side stream; "
+                                  "AdamW bucket by bucket on a third; (N>1) bucket all-reduces on a fourth"},
             "clocks": r["clocks"], "e2e": r.get("e2e"), "gpu_launches": int(r["launches_per_step"] * args.steps), "roofline": roofline,
             "cpu_baseline": cpu, "loss": r["loss"], "nonfinite_grad_blocks": r["nonfinite"], "dp_check": check, "extra_configs": extra,
         }

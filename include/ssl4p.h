@@ -179,6 +179,14 @@ int ssl4p_adamw_flat(float* p, const float* g, float* m, float* v, void* p_bf16,
 int ssl4p_adamw_flat_dev(float* p, const float* g, float* m, float* v, void* p_bf16, const uint8_t* wd_flags, long long n,
                          float* hyper, float beta1, float beta2, float eps, float weight_decay,
                          float grad_scale, int* nonfinite, void* stream);
+/* The same update over ONE RANGE of the arena (a gradient bucket: the pointers are the arena bases advanced by the bucket
+ * offset, wd_flags by offset/256) WITHOUT touching the step counter, so the optimiser can run bucket by bucket behind the
+ * backward / the bucket all-reduces (reference: DDP bucketed averaging, main_pretrain.py:212-214, then optimizer.step,
+ * engine_pretrain.py:67-70).  Call ssl4p_adamw_advance_step once after the last range of a step. */
+int ssl4p_adamw_flat_dev_range(float* p, const float* g, float* m, float* v, void* p_bf16, const uint8_t* wd_flags, long long n,
+                               const float* hyper, float beta1, float beta2, float eps, float weight_decay,
+                               float grad_scale, int* nonfinite, void* stream);
+int ssl4p_adamw_advance_step(float* hyper, void* stream);
 
 /* ViT_from_MAE head (models.py:211-222): logits[n,:] = W . pooled[n,:] + b with pooled = x[n,0,:] ("cls") or
  * mean_i x[n,1+i,:] ("spatial"); x is the fp32 output of the final LayerNorm kept as bf16 [N,T,D]. */

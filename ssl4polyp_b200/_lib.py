@@ -52,6 +52,8 @@ SIGNATURES = {
     "ssl4p_cast_f32_bf16": (i32, [vp, vp, i64, vp]),
     "ssl4p_adamw_flat": (i32, [vp, vp, vp, vp, vp, vp, i64, f32, f32, f32, f32, f32, f32, f32, f32, vp, vp]),
     "ssl4p_adamw_flat_dev": (i32, [vp, vp, vp, vp, vp, vp, i64, vp, f32, f32, f32, f32, f32, vp, vp]),
+    "ssl4p_adamw_flat_dev_range": (i32, [vp, vp, vp, vp, vp, vp, i64, vp, f32, f32, f32, f32, f32, vp, vp]),
+    "ssl4p_adamw_advance_step": (i32, [vp, vp]),
     "ssl4p_pool_head_fwd": (i32, [vp, vp, vp, vp, i32, i32, i32, i32, i32, vp]),
     "ssl4p_pool_head_bwd": (i32, [vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, vp]),
 }

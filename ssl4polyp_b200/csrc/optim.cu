@@ -92,3 +92,25 @@ extern "C" int ssl4p_adamw_flat_dev(float* p, const float* g, float* m, float* v
     adamw_step_inc_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(hyper);
     return check_launch("adamw_step_inc_kernel");
 }
+
+extern "C" int ssl4p_adamw_flat_dev_range(float* p, const float* g, float* m, float* v, void* p_bf16, const uint8_t* wd_flags, long long n,
+                                          const float* hyper, float beta1, float beta2, float eps, float weight_decay,
+                                          float grad_scale, int* nonfinite, void* stream) {
+    SSL4P_REQUIRE(p && g && m && v && hyper, "adamw_dev_range: null pointer");
+    SSL4P_REQUIRE(n >= 0 && n % 256 == 0, "adamw_dev_range: a range must be whole 256-element arena chunks");
+    SSL4P_REQUIRE((reinterpret_cast<uintptr_t>(p) & 15) == 0 && (reinterpret_cast<uintptr_t>(g) & 15) == 0, "adamw_dev_range: unaligned range");
+    if (n == 0) return SSL4P_OK;
+    const long long n4 = n / 4;
+    long long blocks = (n4 + 255) / 256;
+    const long long cap = (long long)num_sms() * 8;
+    if (blocks > cap) blocks = cap;
+    adamw_flat_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(p, g, m, v, (__nv_bfloat16*)p_bf16, wd_flags, n4, 0.f, beta1, beta2, eps,
+                                                                          weight_decay, 1.f, 1.f, grad_scale, nonfinite, hyper);
+    return check_launch("adamw_flat_kernel");
+}
+
+extern "C" int ssl4p_adamw_advance_step(float* hyper, void* stream) {
+    SSL4P_REQUIRE(hyper, "adamw_advance_step: null pointer");
+    adamw_step_inc_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(hyper);
+    return check_launch("adamw_step_inc_kernel");
+}

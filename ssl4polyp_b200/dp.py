@@ -47,6 +47,21 @@ def plan_buckets(offsets: dict, trainable: list, limit_elems: int, align: int = 
     return buckets
 
 
+def plan_buckets_tapered(offsets: dict, trainable: list, limit_elems: int, align: int = 256, tail_elems: int | None = None) -> list:
+    """`plan_buckets`, then the LAST bucket (lowest offsets: what backward finishes last, i.e. the only all-reduce and
+    optimiser slice with nothing left to hide behind) is re-cut into pieces of `tail_elems` (default limit/4), so the
+    exposed tail of a step is one small bucket instead of one full-size one."""
+    buckets = plan_buckets(offsets, trainable, limit_elems, align)
+    tail_elems = tail_elems or max(limit_elems // 4, 1)
+    if not buckets or tail_elems >= limit_elems:
+        return buckets
+    last = buckets.pop()
+    names = sorted(last.names, key=lambda n: offsets[n][0], reverse=True)
+    sub = plan_buckets({n: offsets[n] for n in names}, names, tail_elems, align)
+    sub[0].end = last.end
+    return buckets + sub
+
+
 def broadcast_parameters(flat: torch.Tensor, group=None, src: int = 0) -> None:
     """Every rank starts from rank `src`'s parameter arena - what `DistributedDataParallel.__init__` does in the reference
     (main_pretrain.py:212-214): ranks are seeded `seed + rank` BEFORE the model is built (:146-148), so without this
@@ -71,6 +86,18 @@ _SKIP_COLLECTIVE = bool(int(__import__("os").environ.get("SSL4P_DP_SKIP_COLLECTI
 
 
 class BucketReducer:
+    """Drives the per-bucket work of a step as the backward completes buckets:
+
+      ready(name)  the kernels producing gradient `name` have been enqueued (on one of `producer_streams`);
+      bucket i complete -> (world > 1) SUM all-reduce of its arena slice on the communication stream, ordered after the
+                           producers by events;
+      on_bucket(j, deps)   optional hook (the engine's per-bucket AdamW), called for bucket j ONE bucket late - when the
+                           next bucket completes, or in finish() - with the events it has to wait for: bucket j's
+                           all-reduce, plus the producers' position at the time of the call.  The lag is what makes an
+                           in-place parameter update safe: every backward kernel that still READS the weights of bucket j
+                           (the dgrad GEMMs of its layers) was enqueued before the next bucket could complete.
+    With world == 1 there is no collective; readiness tracking and the hook work the same way."""
+
     def __init__(self, flat: torch.Tensor, buckets: list, group=None):
         self.flat = flat
         self.buckets = buckets
@@ -80,6 +107,8 @@ class BucketReducer:
         self.comm_stream = torch.cuda.Stream(device=flat.device) if (self.cuda and self.world > 1) else None
         self.bucket_of = {n: i for i, b in enumerate(buckets) for n in b.names}
         self.launch_order: list[int] = []
+        self.producer_streams = None            # streams the gradients are produced on (None: the current stream)
+        self.on_bucket = None
         self.reset()
 
     def reset(self):
@@ -87,11 +116,21 @@ class BucketReducer:
         self._seen = set()
         self._launched = set()
         self._handles = []
+        self._done = {}                         # bucket -> [events] after which its (reduced) gradients are final
+        self._pending_hook = None               # bucket whose on_bucket call is lagging
         self.launch_order = []
 
+    def _producer_events(self):
+        evs = []
+        for st in (self.producer_streams or [torch.cuda.current_stream()]):
+            ev = torch.cuda.Event()
+            ev.record(st)
+            evs.append(ev)
+        return evs
+
     def ready(self, name: str) -> None:
-        """The kernels producing gradient `name` have been enqueued on the current stream."""
-        if self.world == 1 or name in self._seen:
+        """The kernels producing gradient `name` have been enqueued."""
+        if (self.world == 1 and self.on_bucket is None) or name in self._seen:
             return
         i = self.bucket_of.get(name)
         if i is None:
@@ -107,25 +146,41 @@ class BucketReducer:
         self._launched.add(i)
         self.launch_order.append(i)
         if self.cuda:
-            ev = torch.cuda.Event()
-            ev.record(torch.cuda.current_stream())
-            self.comm_stream.wait_event(ev)
-            with torch.cuda.stream(self.comm_stream):
-                if not _SKIP_COLLECTIVE:
-                    dist.all_reduce(view, op=dist.ReduceOp.SUM, group=self.group)
-        else:
+            evs = self._producer_events()
+            if self.world > 1:
+                for ev in evs:
+                    self.comm_stream.wait_event(ev)
+                with torch.cuda.stream(self.comm_stream):
+                    if not _SKIP_COLLECTIVE:
+                        dist.all_reduce(view, op=dist.ReduceOp.SUM, group=self.group)
+                    done = torch.cuda.Event()
+                    done.record(self.comm_stream)
+                self._done[i] = [done]
+            else:
+                self._done[i] = evs
+            if self.on_bucket is not None:
+                if self._pending_hook is not None:
+                    j = self._pending_hook
+                    self.on_bucket(j, self._done[j] + evs)
+                self._pending_hook = i
+        elif self.world > 1:
             self._handles.append(dist.all_reduce(view, op=dist.ReduceOp.SUM, group=self.group, async_op=True))
 
     def finish(self) -> None:
-        """Reduce whatever has not been launched (parameters that received no gradient this step), then make the
-        current stream wait for all bucket reductions."""
-        if self.world == 1:
+        """Reduce whatever has not been launched (parameters that received no gradient this step), run the lagging hook,
+        then make the current stream wait for all bucket reductions."""
+        if self.world == 1 and self.on_bucket is None:
             return
         for i in range(len(self.buckets)):
             if i not in self._launched:
                 self._launch(i)
         if self.cuda:
-            torch.cuda.current_stream().wait_stream(self.comm_stream)
+            if self.on_bucket is not None and self._pending_hook is not None:
+                j = self._pending_hook
+                self.on_bucket(j, self._done[j] + self._producer_events())
+                self._pending_hook = None
+            if self.comm_stream is not None:
+                torch.cuda.current_stream().wait_stream(self.comm_stream)
         else:
             for h in self._handles:
                 h.wait()

@@ -17,6 +17,7 @@ What `engine_pretrain.train_one_epoch` does per iteration in the reference
 """
 from __future__ import annotations
 
+import contextlib
 import math
 import os
 
@@ -24,20 +25,61 @@ import torch
 import torch.distributed as dist
 
 from . import ops, vit_core
-from .dp import BucketReducer, broadcast_parameters, plan_buckets
+from .dp import BucketReducer, broadcast_parameters, plan_buckets_tapered
 from .param_store import ALIGN
 
 
 class ArenaSink(vit_core.GradSink):
+    """Gradients go straight into the engine's flat arena.  With `overlap` the weight-gradient work of the backward
+    (wgrad GEMM + split-K reduce + bias column sums: ~45 % of the backward's kernel time, none of it on the dgrad chain)
+    is enqueued on the engine's side stream: its CTAs fill the SMs that the critical chain's kernels leave idle at their
+    tails and between launches, and the ~300 short reduction kernels disappear from the critical path."""
+
+    LAG = 2                                     # side work of a block is joined this many blocks later
+
     def __init__(self, engine: "TrainEngine"):
         self.e = engine
         self.accumulate = False
+        self.overlap = False
+        self._kept = []                         # operands the side stream may still be reading (this block)
+        self._lagging = []                      # [(event on the side stream, operands)] of earlier blocks
 
     def buf(self, name, like):
         return self.e.grad_views[name], self.accumulate
 
     def ready(self, name):
         self.e._on_ready(name)
+
+    def side(self, *operands):
+        if not self.overlap:
+            return contextlib.nullcontext()
+        aux = self.e.aux_stream
+        ev = torch.cuda.Event()
+        ev.record(torch.cuda.current_stream())
+        aux.wait_event(ev)                      # the operands were produced on the main stream
+        # They were also ALLOCATED there: once the schedule drops its references the caching allocator may hand their
+        # memory to a later main-stream kernel while the side stream still reads it -> keep them until the join.
+        self._kept.extend(operands)
+        return torch.cuda.stream(aux)
+
+    def block_boundary(self):
+        if not self.overlap:
+            return
+        if self._kept:
+            ev = torch.cuda.Event()
+            ev.record(self.e.aux_stream)
+            self._lagging.append((ev, self._kept))
+            self._kept = []
+        while len(self._lagging) > self.LAG:
+            ev, _ = self._lagging.pop(0)
+            torch.cuda.current_stream().wait_event(ev)
+
+    def join(self):
+        """All side work done before whatever the main stream enqueues next (the optimiser, or the caller)."""
+        if not self.overlap:
+            return
+        torch.cuda.current_stream().wait_stream(self.e.aux_stream)
+        self._kept, self._lagging = [], []
 
 
 class TrainEngine:
@@ -79,7 +121,7 @@ class TrainEngine:
         # ---- data parallel (dp.py): bucket plan over the gradient arena + overlapped all-reduce
         trainable = [n for n in store.offsets if store.params[n].requires_grad]
         bucket_mb = float(os.environ.get("SSL4P_DP_BUCKET_MB", bucket_mb))
-        self.buckets = plan_buckets(store.offsets, trainable, int(bucket_mb * (1 << 20) / 4), ALIGN)
+        self.buckets = plan_buckets_tapered(store.offsets, trainable, int(bucket_mb * (1 << 20) / 4), ALIGN)
         self.reducer = BucketReducer(self.grads, self.buckets, process_group)
         self.world = self.reducer.world
         if self.world > 1 and dev.type == "cuda":
@@ -90,6 +132,12 @@ class TrainEngine:
             _lib.load().ssl4p_reserve_sms(int(os.environ.get("SSL4P_DP_SMS", "0")))
         self.sink = ArenaSink(self)
         self._reduce_now = True
+        # second stream for the weight-gradient half of the backward (ArenaSink.side); SSL4P_WGRAD_OVERLAP=0 disables it
+        self.aux_stream = torch.cuda.Stream(device=dev) if dev.type == "cuda" else None
+        self.sink.overlap = self.aux_stream is not None and os.environ.get("SSL4P_WGRAD_OVERLAP", "1") != "0"
+        # third stream: AdamW bucket by bucket behind the backward / the bucket all-reduces; SSL4P_BUCKET_ADAMW=0 -> one pass
+        self.opt_stream = torch.cuda.Stream(device=dev) if dev.type == "cuda" else None
+        self.bucket_adamw = self.opt_stream is not None and os.environ.get("SSL4P_BUCKET_ADAMW", "1") != "0"
 
     def _on_ready(self, name):
         if self._reduce_now:
@@ -104,19 +152,40 @@ class TrainEngine:
         self.sink.accumulate = accumulate
         self._reduce_now = do_step
         self.reducer.reset()
+        main = torch.cuda.current_stream()
+        self.reducer.producer_streams = [main, self.aux_stream] if self.sink.overlap else None
+        stepping = do_step and apply
+        if stepping and not torch.cuda.is_current_stream_capturing():
+            self._set_lr(self.lr if lr is None else lr)          # before the first bucket's AdamW can run
+            self.t += 1
+        self.reducer.on_bucket = self._adamw_bucket if (stepping and self.bucket_adamw) else None
         run_backward(self.sink)
+        self.sink.join()
         if not do_step:
             return
         self.reducer.finish()
         if not apply:
             return
         b1, b2 = self.betas
-        if not torch.cuda.is_current_stream_capturing():
-            self._set_lr(self.lr if lr is None else lr)
-            self.t += 1
-        ops.adamw_flat_dev(self.store.flat, self.grads, self.exp_avg, self.exp_avg_sq, self.store.shadow, self.wd_flags,
-                           self.hyper, b1, b2, self.eps, self.wd, grad_scale=1.0 / self.world, nonfinite=self.nonfinite)
+        if self.bucket_adamw:
+            main.wait_stream(self.opt_stream)
+            ops.adamw_advance_step(self.hyper)
+        else:
+            ops.adamw_flat_dev(self.store.flat, self.grads, self.exp_avg, self.exp_avg_sq, self.store.shadow, self.wd_flags,
+                               self.hyper, b1, b2, self.eps, self.wd, grad_scale=1.0 / self.world, nonfinite=self.nonfinite)
         self.store.mark_shadow_fresh()
+
+    def _adamw_bucket(self, i: int, deps) -> None:
+        """AdamW over bucket i's arena range on the optimiser stream, after `deps` (its all-reduce and the backward's
+        position one bucket later: dp.BucketReducer).  Parameters outside every bucket are frozen: nothing to update."""
+        b = self.buckets[i]
+        for ev in deps:
+            self.opt_stream.wait_event(ev)
+        b1, b2 = self.betas
+        with torch.cuda.stream(self.opt_stream):
+            ops.adamw_flat_dev_range(self.store.flat, self.grads, self.exp_avg, self.exp_avg_sq, self.store.shadow, self.wd_flags,
+                                     b.start, b.end, self.hyper, b1, b2, self.eps, self.wd, grad_scale=1.0 / self.world,
+                                     nonfinite=self.nonfinite)
 
     def _set_lr(self, lr: float) -> None:
         if lr != self._lr_on_device:

@@ -448,6 +448,23 @@ def adamw_flat_dev(p, g, m, v, p_bf16, wd_flags, hyper, beta1, beta2, eps, weigh
                                         float(grad_scale), _ptr(nonfinite), _stream()), "adamw_flat_dev")
 
 
+def adamw_flat_dev_range(p, g, m, v, p_bf16, wd_flags, start, end, hyper, beta1, beta2, eps, weight_decay, grad_scale=1.0, nonfinite=None):
+    """AdamW over arena elements [start, end) (multiples of 256) with lr / step read from `hyper`; the step counter is NOT
+    advanced (adamw_advance_step does that once per optimiser step)."""
+    lib = _lib.load()
+    assert start % 256 == 0 and end % 256 == 0 and start <= end
+    n = end - start
+    _lib.check(lib.ssl4p_adamw_flat_dev_range(p.data_ptr() + 4 * start, g.data_ptr() + 4 * start, m.data_ptr() + 4 * start,
+                                              v.data_ptr() + 4 * start, None if p_bf16 is None else p_bf16.data_ptr() + 2 * start,
+                                              None if wd_flags is None else wd_flags.data_ptr() + start // 256, n, hyper.data_ptr(),
+                                              float(beta1), float(beta2), float(eps), float(weight_decay), float(grad_scale),
+                                              _ptr(nonfinite), _stream()), "adamw_flat_dev_range")
+
+
+def adamw_advance_step(hyper):
+    _lib.check(_lib.load().ssl4p_adamw_advance_step(hyper.data_ptr(), _stream()), "adamw_advance_step")
+
+
 def pool_head_fwd(xn, W, b, N, T, D, spatial):
     lib = _lib.load()
     ncls = W.shape[0]

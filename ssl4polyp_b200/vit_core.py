@@ -17,6 +17,7 @@ fp32 accumulation; weight gradients fp32.
 """
 from __future__ import annotations
 
+import contextlib
 from dataclasses import dataclass, field
 
 import torch
@@ -66,10 +67,17 @@ class Weights:
 
 class GradSink:
     """Where weight gradients go.  `buf(name, shape)` -> (fp32 tensor to write, accumulate?);
-    `ready(name)` is called once the kernels producing that gradient have been enqueued."""
+    `ready(name)` is called once the kernels producing that gradient have been enqueued.
+
+    Weight gradients are OFF the critical path of the backward (the dgrad chain never reads them), so a sink may run them
+    on a second stream: `side(*operands)` is the context in which `_wgrad` enqueues its kernels (default: the current
+    stream), `block_boundary()` is called between transformer blocks (a sink with a side stream joins lagging side work
+    there and releases the operands it kept alive for it)."""
 
     def buf(self, name: str, like: torch.Tensor): raise NotImplementedError
     def ready(self, name: str) -> None: pass
+    def side(self, *operands): return contextlib.nullcontext()
+    def block_boundary(self) -> None: pass
 
 
 class FreshGrads(GradSink):
@@ -98,21 +106,24 @@ def _block_needs(W: Weights, pre: str) -> bool:
 def _wgrad(W: Weights, sink: GradSink, wname: str, bname: str | None, dy: torch.Tensor, x: torch.Tensor):
     """dW[out,in] = dy^T x (TN GEMM, deterministic split-K), db = column sums of dy (bname None: the bias gradient
     was already produced by the LayerNorm backward that wrote dy, see _ln_bwd)."""
-    if W.need(wname):
-        w = W.f(wname)
-        buf, acc = sink.buf(wname, w)
-        buf2 = buf.view(w.shape[0], -1)
-        M, N, K = dy.shape[1], x.shape[1], dy.shape[0]
-        s = ops.pick_splits(M, N, K)
-        if acc:
-            ops.gemm(dy, x, GEMM_TN, EPI_PARTIAL_F32, accumulate_into=buf2, splits=s)
-        else:
-            ops.gemm(dy, x, GEMM_TN, EPI_PARTIAL_F32, out=buf2, splits=s)
-        sink.ready(wname)
-    if bname is not None and W.need(bname):
-        buf, acc = sink.buf(bname, W.f(bname))
-        ops.colsum(dy, out=buf, accumulate=acc)
-        sink.ready(bname)
+    if not (W.need(wname) or (bname is not None and W.need(bname))):
+        return
+    with sink.side(dy, x):
+        if W.need(wname):
+            w = W.f(wname)
+            buf, acc = sink.buf(wname, w)
+            buf2 = buf.view(w.shape[0], -1)
+            M, N, K = dy.shape[1], x.shape[1], dy.shape[0]
+            s = ops.pick_splits(M, N, K)
+            if acc:
+                ops.gemm(dy, x, GEMM_TN, EPI_PARTIAL_F32, accumulate_into=buf2, splits=s)
+            else:
+                ops.gemm(dy, x, GEMM_TN, EPI_PARTIAL_F32, out=buf2, splits=s)
+            sink.ready(wname)
+        if bname is not None and W.need(bname):
+            buf, acc = sink.buf(bname, W.f(bname))
+            ops.colsum(dy, out=buf, accumulate=acc)
+            sink.ready(bname)
 
 
 def _ln_bwd(W: Weights, sink: GradSink, pre: str, dy, x, mean, rstd, residual_grad, want_bf16=True, upstream_bias=None):
@@ -168,6 +179,7 @@ def block_bwd(W: Weights, sink: GradSink, pre: str, saved, dx: torch.Tensor, dxb
     x, mean1, rstd1, h, qkv, o, lse, x1, mean2, rstd2, h2, dact, act = saved
     D = x.shape[1]
     hd = D // H
+    sink.block_boundary()
     # ---- MLP branch
     _wgrad(W, sink, pre + "mlp.fc2.weight", None if fc2_bias_done else pre + "mlp.fc2.bias", dxb, act)
     b1 = pre + "mlp.fc1.bias"
