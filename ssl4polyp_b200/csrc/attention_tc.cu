@@ -23,14 +23,17 @@
 #include "attn_common.cuh"
 #include <mutex>
 #include <stdlib.h>
+#include <type_traits>
 #include <unordered_map>
 
 namespace ssl4p {
 
 struct AttnFwdParams {
+    int B, pair;                               // pair: two images share one 128-row tile (T <= 64), item = (image pair, slice)
     int T, H, items, slices_per_img;           // slices_per_img = H*hd/64
     int Npad, NB, NKB;                         // keys padded to 16; query tiles of 128; key boxes of 128 rows
     int sep;                                   // 1: O has its own TMEM columns (deferred read-out), 0: O overwrites S
+    int backoff_ns;                            // MMA issuer: sleep this long after a polling sweep without progress (0: spin)
     int s_stride;                              // sep: TMEM columns between the two S buffers
     float scale;
     __nv_bfloat16* out;                        // [B*T, H*hd]
@@ -48,7 +51,7 @@ struct AttnFwdParams {
 // Otherwise (`sep` = 0) O is accumulated over the dead S columns and read out before the next S may be issued.
 template <int HD>
 __global__ void __launch_bounds__(kAttnThreads, 1)
-attention_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnFwdParams p) {
+attention_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CUtensorMap tmQKV64, const AttnFwdParams p) {
     constexpr int HP = 64 / HD;                                  // heads per work item
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -76,7 +79,7 @@ attention_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnFwd
     const int my_items = p.items > (int)blockIdx.x ? (p.items - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
     const bool sep = p.sep != 0;
 
-    if (warp == 8 && lane == 0) tma_prefetch_desc(&tmQKV);
+    if (warp == 8 && lane == 0) { tma_prefetch_desc(&tmQKV); tma_prefetch_desc(&tmQKV64); }
     if (warp == 9) {
         if (lane == 0) {
             mbar_init(qk_full, 1); mbar_init(qk_empty, NT);
@@ -112,6 +115,19 @@ attention_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnFwd
                 const int so = stage * kTileBytes;
                 mbar_wait(qe, (use & 1) ^ 1);
                 mbar_expect_tx(qf, (uint32_t)(p.NB + p.NKB) * kTileBytes);
+                if (p.pair) {
+                    // images 2b and 2b+1 in rows [0,64) and [64,128) of every operand tile (64-row boxes; rows t >= T and a
+                    // second image beyond the batch are zero-filled by TMA)
+                    for (int im = 0; im < 2; ++im) {
+                        tma_load_3d(sQ + so + im * (kTileBytes / 2), &tmQKV64, qf, sl * 64, 0, 2 * b + im);
+                        tma_load_3d(sK + so + im * (kTileBytes / 2), &tmQKV64, qf, HHD + sl * 64, 0, 2 * b + im);
+                    }
+                    mbar_wait(ve, (use & 1) ^ 1);
+                    mbar_expect_tx(vf, (uint32_t)kTileBytes);
+                    for (int im = 0; im < 2; ++im)
+                        tma_load_3d(sV + so + im * (kTileBytes / 2), &tmQKV64, vf, 2 * HHD + sl * 64, 0, 2 * b + im);
+                    continue;
+                }
                 for (int i = 0; i < p.NB; ++i) tma_load_3d(sQ + so + i * kTileBytes, &tmQKV, qf, sl * 64, i * 128, b);
                 for (int i = 0; i < p.NKB; ++i) tma_load_3d(sK + so + i * kTileBytes, &tmQKV, qf, HHD + sl * 64, i * 128, b);
                 mbar_wait(ve, (use & 1) ^ 1);
@@ -166,12 +182,13 @@ attention_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnFwd
                 return true;
             };
             while (nxt[0] < total || nxt[1] < total) {
+                bool progress = false;
 #pragma unroll
                 for (int w = 0; w < 2; ++w) {
                     const int g = nxt[w];
                     if (g >= total) continue;
                     const int u = g >> 1, il = g / NT, t = g - il * NT;
-                    if (s_done[w] <= u) { try_issue_s(w); continue; }                 // S(g) itself not issued yet
+                    if (s_done[w] <= u) { progress |= try_issue_s(w); continue; }     // S(g) itself not issued yet
                     if (!mbar_test_wait(&p_full[w], u & 1)) continue;
                     tc_fence_after();
                     // sep plan: P(g) complete means S(g) has been consumed -> the chain's next S goes first, then P V
@@ -192,7 +209,11 @@ attention_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnFwd
                     umma_commit(&o_full[w]);
                     umma_commit((ring && (il & 1)) ? v_empty1 : v_empty);
                     nxt[w] = g + 2;
+                    progress = true;
                 }
+                // This thread shares its scheduler with two softmax warps: polling flat out takes a third of that
+                // scheduler's issue slots away from the warps everybody is waiting for.
+                if (!progress && p.backoff_ns) __nanosleep(p.backoff_ns);
             }
         }
         __syncwarp();
@@ -201,19 +222,31 @@ attention_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnFwd
         const int wg = warp >> 2, q4 = warp & 3;
         const int row = q4 * 32 + lane;
         const uint32_t tlanes = tmem_base + ((uint32_t)(q4 * 32) << 16);
-        const uint32_t taddr = tlanes + (sep ? (uint32_t)(wg * p.s_stride) : (uint32_t)wg * 256u);            // S of this chain
-        const uint32_t oaddr = tlanes + (sep ? (uint32_t)(2 * p.s_stride + wg * HD) : (uint32_t)wg * 256u);   // O of this chain
+        // pair mode: rows [0,64) are image 0 and see key columns [0,64), rows [64,128) image 1 / columns [64,128)
+        const int img = p.pair ? (q4 >> 1) : 0;
+        const int kbase = img * 64;                              // first key column of this row's image
+        const int klen = p.pair ? 64 : p.Npad;                   // key columns this row reads
+        const int lrow = p.pair ? (row & 63) : row;              // query index inside the image (before the tile offset)
+        const uint32_t taddr = tlanes + (sep ? (uint32_t)(wg * p.s_stride) : (uint32_t)wg * 256u) + (uint32_t)kbase;   // S of this chain
+        const uint32_t oaddr = tlanes + (sep ? (uint32_t)(2 * p.s_stride + wg * HD) : (uint32_t)wg * 256u);            // O of this chain
         const uint32_t pw = smem_u32(sP) + wg * 4 * kTileBytes;
         const float sl2 = p.scale * kLog2eF;
+        if (p.pair) {
+            // P is block diagonal: the key chunk of the OTHER image is never written by this row and must read as zero
+            const uint32_t other = pw + (uint32_t)(1 - img) * kTileBytes;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) sts_v4(other + sw128_off(row, i), 0u, 0u, 0u, 0u);
+        }
         // O / rowsum -> bf16 row of `out`, log-sum-exp of the row
         auto read_out = [&](int b, int head, int qrow, float mx, float sum) {
             const float inv = 1.0f / sum;
+            const bool ok = qrow < p.T && b < p.B;
 #pragma unroll
             for (int hf = 0; hf < HD / 32; ++hf) {
                 uint32_t r[32];
                 tmem_ld_32x32(oaddr + hf * 32, r);
                 tmem_ld_wait();
-                if (qrow < p.T) {
+                if (ok) {
                     __nv_bfloat16* dst = p.out + ((size_t)(b * p.T + qrow) * p.H + head) * HD + hf * 32;
 #pragma unroll
                     for (int i = 0; i < 4; ++i)
@@ -224,20 +257,36 @@ attention_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnFwd
                                pack_bf16(__uint_as_float(r[8 * i + 6]) * inv, __uint_as_float(r[8 * i + 7]) * inv));
                 }
             }
-            if (qrow < p.T) p.lse[((size_t)b * p.H + head) * p.T + qrow] = mx * p.scale + __logf(sum);
+            if (ok) p.lse[((size_t)b * p.H + head) * p.T + qrow] = mx * p.scale + __logf(sum);
+        };
+        // running maximum over one 32-column chunk held in registers (columns c .. c+31 of this row's key range)
+        auto chunk_max = [&](const uint32_t (&r)[32], int c, float mx) -> float {
+            if (c + 32 <= p.T) {
+                float m0 = mx, m1 = mx, m2 = mx, m3 = mx;
+#pragma unroll
+                for (int jj = 0; jj < 32; jj += 4) {
+                    m0 = fmaxf(m0, __uint_as_float(r[jj])); m1 = fmaxf(m1, __uint_as_float(r[jj + 1]));
+                    m2 = fmaxf(m2, __uint_as_float(r[jj + 2])); m3 = fmaxf(m3, __uint_as_float(r[jj + 3]));
+                }
+                return fmaxf(fmaxf(m0, m1), fmaxf(m2, m3));
+            }
+#pragma unroll
+            for (int jj = 0; jj < 32; ++jj) if (c + jj < p.T) mx = fmaxf(mx, __uint_as_float(r[jj]));
+            return mx;
         };
         int pb = 0, phead = 0, pqrow = 0, pu = -1;               // tile whose O is still in TMEM (sep plan)
         float pmx = 0.f, psum = 1.f;
         for (int il = 0; il < my_items; ++il) {
             const int item = blockIdx.x + il * gridDim.x;
-            const int b = item / p.slices_per_img, sl = item % p.slices_per_img;
+            const int b0 = item / p.slices_per_img, sl = item % p.slices_per_img;
+            const int b = p.pair ? 2 * b0 + img : b0;
             for (int t = 0; t < NT; ++t) {
                 const int g = il * NT + t;
                 if ((g & 1) != wg) continue;
                 const int u = g >> 1;
                 const int hh = t / p.NB, mb = t - hh * p.NB;
                 const int head = sl * HP + hh;
-                const int qrow = mb * 128 + row;
+                const int qrow = mb * 128 + lrow;
                 mbar_wait(&s_full[wg], u & 1);
                 tc_fence_after();
                 // ---- pass 1: row maximum over the valid keys (the TMEM load of chunk c+1 is in flight during the max of chunk c)
@@ -245,67 +294,70 @@ attention_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnFwd
                 {
                     uint32_t ra[32], rb[32];
                     tmem_ld_32x32(taddr, ra);
-                    for (int c = 0; c < p.Npad; c += 64) {
+                    for (int c = 0; c < klen; c += 64) {
                         tmem_ld_wait();
-                        if (c + 32 < p.Npad) tmem_ld_32x32(taddr + c + 32, rb);
-                        if (c + 32 <= p.T) {
-                            float m0 = mx, m1 = mx, m2 = mx, m3 = mx;
-#pragma unroll
-                            for (int jj = 0; jj < 32; jj += 4) {
-                                m0 = fmaxf(m0, __uint_as_float(ra[jj])); m1 = fmaxf(m1, __uint_as_float(ra[jj + 1]));
-                                m2 = fmaxf(m2, __uint_as_float(ra[jj + 2])); m3 = fmaxf(m3, __uint_as_float(ra[jj + 3]));
-                            }
-                            mx = fmaxf(fmaxf(m0, m1), fmaxf(m2, m3));
-                        } else {
-#pragma unroll
-                            for (int jj = 0; jj < 32; ++jj) if (c + jj < p.T) mx = fmaxf(mx, __uint_as_float(ra[jj]));
-                        }
-                        if (c + 32 >= p.Npad) break;
+                        if (c + 32 < klen) tmem_ld_32x32(taddr + c + 32, rb);
+                        mx = chunk_max(ra, c, mx);
+                        if (c + 32 >= klen) break;
                         tmem_ld_wait();
-                        if (c + 64 < p.Npad) tmem_ld_32x32(taddr + c + 64, ra);
-                        if (c + 64 <= p.T) {
-                            float m0 = mx, m1 = mx, m2 = mx, m3 = mx;
-#pragma unroll
-                            for (int jj = 0; jj < 32; jj += 4) {
-                                m0 = fmaxf(m0, __uint_as_float(rb[jj])); m1 = fmaxf(m1, __uint_as_float(rb[jj + 1]));
-                                m2 = fmaxf(m2, __uint_as_float(rb[jj + 2])); m3 = fmaxf(m3, __uint_as_float(rb[jj + 3]));
-                            }
-                            mx = fmaxf(fmaxf(m0, m1), fmaxf(m2, m3));
-                        } else {
-#pragma unroll
-                            for (int jj = 0; jj < 32; ++jj) if (c + 32 + jj < p.T) mx = fmaxf(mx, __uint_as_float(rb[jj]));
-                        }
+                        if (c + 64 < klen) tmem_ld_32x32(taddr + c + 64, ra);
+                        mx = chunk_max(rb, c + 32, mx);
                     }
                 }
                 // sep plan: the P buffer of this chain is still being read by P V of the previous tile until o_full
                 if (sep && pu >= 0) { mbar_wait(&o_full[wg], pu & 1); tc_fence_after(); }
-                // ---- pass 2: p = exp2((s - max) * scale * log2e), row sum, bf16 P into the SW128 K-major tile
+                // ---- pass 2: p = exp2((s - max) * scale * log2e), row sum, bf16 P into the SW128 K-major tile; the scale /
+                // subtract and the row sum run two elements per instruction (FFMA2 / FADD2), the TMEM load of the next
+                // chunk is in flight during the exponentials of this one
                 const float msl = mx * sl2;
-                float sum = 0.f;
-                for (int c = 0; c < p.Npad; c += 32) {
-                    uint32_t r[32];
-                    tmem_ld_32x32(taddr + c, r);
-                    tmem_ld_wait();
-                    float e[32];
-                    if (c + 32 <= p.T) {
+                const f32x2 sl2v = f2_splat(sl2), mslv = f2_splat(-msl);
+                f32x2 acc0 = f2_splat(0.f), acc1 = f2_splat(0.f);
+                auto chunk_p = [&](const uint32_t (&r)[32], int c) {
+                    const uint32_t tile = pw + (uint32_t)((kbase + c) >> 6) * kTileBytes;
+                    const int sub = ((kbase + c) & 63) >> 3;
+                    const bool tail = c + 32 > p.T;
 #pragma unroll
-                        for (int jj = 0; jj < 32; ++jj) e[jj] = fast_exp2(fmaf(__uint_as_float(r[jj]), sl2, -msl));
-                    } else {
+                    for (int h16 = 0; h16 < 2; ++h16) {           // 16 columns at a time keeps the live exponentials at 16
+                        float e[16];
 #pragma unroll
-                        for (int jj = 0; jj < 32; ++jj) e[jj] = (c + jj < p.T) ? fast_exp2(fmaf(__uint_as_float(r[jj]), sl2, -msl)) : 0.f;
+                        for (int jj = 0; jj < 16; jj += 2) {
+                            float x0, x1;
+                            f2_unpack(f2_fma(f2_pack(__uint_as_float(r[h16 * 16 + jj]), __uint_as_float(r[h16 * 16 + jj + 1])), sl2v, mslv), x0, x1);
+                            e[jj] = fast_exp2(x0); e[jj + 1] = fast_exp2(x1);
+                        }
+                        if (tail) {
+#pragma unroll
+                            for (int jj = 0; jj < 16; ++jj) if (c + h16 * 16 + jj >= p.T) e[jj] = 0.f;
+                        }
+#pragma unroll
+                        for (int jj = 0; jj < 16; jj += 4) {
+                            acc0 = f2_add(acc0, f2_pack(e[jj], e[jj + 1]));
+                            acc1 = f2_add(acc1, f2_pack(e[jj + 2], e[jj + 3]));
+                        }
+#pragma unroll
+                        for (int i = 0; i < 2; ++i)
+                            sts_v4(tile + sw128_off(row, sub + h16 * 2 + i), pack_bf16(e[8 * i + 0], e[8 * i + 1]), pack_bf16(e[8 * i + 2], e[8 * i + 3]),
+                                   pack_bf16(e[8 * i + 4], e[8 * i + 5]), pack_bf16(e[8 * i + 6], e[8 * i + 7]));
                     }
-                    {                                             // four independent chains (a single one costs 32 x 4 dependent cycles)
-                        float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
-#pragma unroll
-                        for (int jj = 0; jj < 32; jj += 4) { s0 += e[jj]; s1 += e[jj + 1]; s2 += e[jj + 2]; s3 += e[jj + 3]; }
-                        sum += (s0 + s1) + (s2 + s3);
+                };
+                {
+                    uint32_t ra[32], rb[32];
+                    tmem_ld_32x32(taddr, ra);
+                    for (int c = 0; c < klen; c += 64) {
+                        tmem_ld_wait();
+                        if (c + 32 < klen) tmem_ld_32x32(taddr + c + 32, rb);
+                        chunk_p(ra, c);
+                        if (c + 32 >= klen) break;
+                        tmem_ld_wait();
+                        if (c + 64 < klen) tmem_ld_32x32(taddr + c + 64, ra);
+                        chunk_p(rb, c + 32);
                     }
-                    const uint32_t tile = pw + (c >> 6) * kTileBytes;
-                    const int sub = (c & 63) >> 3;
-#pragma unroll
-                    for (int i = 0; i < 4; ++i)
-                        sts_v4(tile + sw128_off(row, sub + i), pack_bf16(e[8 * i + 0], e[8 * i + 1]), pack_bf16(e[8 * i + 2], e[8 * i + 3]),
-                               pack_bf16(e[8 * i + 4], e[8 * i + 5]), pack_bf16(e[8 * i + 6], e[8 * i + 7]));
+                }
+                float sum;
+                {
+                    float a, b2, c2, d2;
+                    f2_unpack(acc0, a, b2); f2_unpack(acc1, c2, d2);
+                    sum = (a + b2) + (c2 + d2);
                 }
                 if (sep) {
                     // O of the chain's previous tile (complete: o_full was observed above) leaves TMEM before P V of this
@@ -346,6 +398,7 @@ attention_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnFwd
 // backward
 // =========================================================================================================
 struct AttnBwdParams {
+    int B, pair;                               // pair: two images per 128-row tile (T <= 64); half block h = queries of image h
     int T, H, items, slices_per_img;
     int Npad, NB;
     float scale;
@@ -392,7 +445,8 @@ struct HalfBlk {
 
 template <int HD>
 __global__ void __launch_bounds__(kAttnThreads, 1)
-attention_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CUtensorMap tmDO, const AttnBwdParams p) {
+attention_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CUtensorMap tmDO,
+                        const __grid_constant__ CUtensorMap tmQKV64, const __grid_constant__ CUtensorMap tmDO64, const AttnBwdParams p) {
     constexpr int HP = 64 / HD;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -422,7 +476,7 @@ attention_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_
     const int my_items = p.items > (int)blockIdx.x ? (p.items - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
     const int HHD = p.H * HD;
 
-    if (warp == 8 && lane == 0) { tma_prefetch_desc(&tmQKV); tma_prefetch_desc(&tmDO); }
+    if (warp == 8 && lane == 0) { tma_prefetch_desc(&tmQKV); tma_prefetch_desc(&tmDO); tma_prefetch_desc(&tmQKV64); tma_prefetch_desc(&tmDO64); }
     if (warp == 9) {
         if (lane == 0) {
             for (int i = 0; i < 2; ++i) { mbar_init(&in_full[i], 1); mbar_init(&in_empty[i], 1); }
@@ -450,6 +504,16 @@ attention_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_
                 const int stage = ring ? (il & 1) : 0, use = ring ? (il >> 1) : il;
                 mbar_wait(&in_empty[stage], (use & 1) ^ 1);
                 mbar_expect_tx(&in_full[stage], (uint32_t)(4 * p.NB) * kTileBytes);
+                if (p.pair) {                                     // images 2b, 2b+1 -> rows [0,64), [64,128) of every operand tile
+                    for (int im = 0; im < 2; ++im) {
+                        const int slot = stage * kTileBytes + im * (kTileBytes / 2);
+                        tma_load_3d(sQ + slot, &tmQKV64, &in_full[stage], sl * 64, 0, 2 * b + im);
+                        tma_load_3d(sK + slot, &tmQKV64, &in_full[stage], HHD + sl * 64, 0, 2 * b + im);
+                        tma_load_3d(sV + slot, &tmQKV64, &in_full[stage], 2 * HHD + sl * 64, 0, 2 * b + im);
+                        tma_load_3d(sDO + slot, &tmDO64, &in_full[stage], sl * 64, 0, 2 * b + im);
+                    }
+                    continue;
+                }
                 for (int i = 0; i < p.NB; ++i) {
                     const int slot = (stage + i) * kTileBytes;
                     tma_load_3d(sQ + slot, &tmQKV, &in_full[stage], sl * 64, i * 128, b);
@@ -535,7 +599,9 @@ attention_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_
                             if (c.kt == p.NB - 1) { umma_commit(dq_full); ++nhead; }
                         }
                     }
-                    if (ahead.hh < HP) { issue_scores(ahead, ja++); ahead.next(p.Npad, p.NB); }   // refill the buffer just drained
+                    // refill the buffer just drained (issuing these BEFORE the gradient MMAs was measured slower: 346 -> 367 us
+                    // at B=256, T=197, hd 32 - the gradient MMAs gate blk_done, which the element-wise warps wait for first)
+                    if (ahead.hh < HP) { issue_scores(ahead, ja++); ahead.next(p.Npad, p.NB); }
                 }
                 umma_commit(&in_empty[stage]);
             }
@@ -554,26 +620,37 @@ attention_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_
         // Deferred read-out of the TMEM gradient accumulators: it is done inside the NEXT half block, between its
         // arithmetic and its shared-memory stores, so the wait for the last dV/dK (dQ) MMAs hides behind useful work.
         int pend_kt = -1, pend_kt_hh = 0, pend_dq_hh = -1, pend_b = 0, pend_sl = 0;
+        const int img = p.pair ? (q4 >> 1) : 0;                  // pair mode: image of this thread's tile row
+        const int lrow = p.pair ? (row & 63) : row;              // token index of the row inside its image (before the tile offset)
+        if (p.pair) {
+            // P^T / dS^T are block diagonal: chunk h (queries of image h) is only ever written by the key rows of image h; the
+            // rows of the other image must read as zero.  Warps 0-3 clear P^T, warps 4-7 dS^T.
+            const uint32_t base = (half == 0 ? sPTa : sDSa) + (uint32_t)(1 - img) * kTileBytes;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) sts_v4(base + sw128_off(row, i), 0u, 0u, 0u, 0u);
+        }
         auto write_dvk = [&]() {                                 // dV / dK of key tile pend_kt: warps 0-3 write dV, warps 4-7 dK
-            const int key = pend_kt * 128 + row;
+            const int key = pend_kt * 128 + lrow;
+            const int pb_ = p.pair ? 2 * pend_b + img : pend_b;
+            const bool ok = key < p.T && pb_ < p.B;
             const int head = pend_sl * HP + pend_kt_hh;
             mbar_wait(dvk_full, wkt & 1);
             tc_fence_after();
             const uint32_t col = half == 0 ? kColDV : kColDK;
-            __nv_bfloat16* dst = p.dqkv + (size_t)(pend_b * p.T + key) * (3 * HHD) + (half == 0 ? 2 * HHD : HHD) + head * HD;
+            __nv_bfloat16* dst = p.dqkv + (size_t)(pb_ * p.T + key) * (3 * HHD) + (half == 0 ? 2 * HHD : HHD) + head * HD;
             if constexpr (HD == 64) {
 #pragma unroll
                 for (int h2 = 0; h2 < 2; ++h2) {
                     uint32_t r[32];
                     tmem_ld_32x32(tlane + col + h2 * 32, r);
                     tmem_ld_wait();
-                    if (key < p.T) store_row32_bf16(dst + h2 * 32, r);
+                    if (ok) store_row32_bf16(dst + h2 * 32, r);
                 }
             } else {
                 uint32_t r[32];
                 tmem_ld_32x32(tlane + col + pend_kt_hh * 32, r);
                 tmem_ld_wait();
-                if (key < p.T) store_row32_bf16(dst, r);
+                if (ok) store_row32_bf16(dst, r);
             }
             tc_fence_before();
             mbar_arrive(dvk_empty);
@@ -584,21 +661,23 @@ attention_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_
             mbar_wait(dq_full, whd & 1);
             tc_fence_after();
             if (half < p.NB) {
-                const int q = half * 128 + row;
-                __nv_bfloat16* dst = p.dqkv + (size_t)(pend_b * p.T + q) * (3 * HHD) + head * HD;
+                const int q = half * 128 + lrow;
+                const int pb_ = p.pair ? 2 * pend_b + img : pend_b;
+                const bool ok = q < p.T && pb_ < p.B;
+                __nv_bfloat16* dst = p.dqkv + (size_t)(pb_ * p.T + q) * (3 * HHD) + head * HD;
                 if constexpr (HD == 64) {
 #pragma unroll
                     for (int h2 = 0; h2 < 2; ++h2) {
                         uint32_t r[32];
                         tmem_ld_32x32(tlane + kColDQ + half * 64 + h2 * 32, r);
                         tmem_ld_wait();
-                        if (q < p.T) store_row32_bf16(dst + h2 * 32, r);
+                        if (ok) store_row32_bf16(dst + h2 * 32, r);
                     }
                 } else {
                     uint32_t r[32];
                     tmem_ld_32x32(tlane + kColDQ + half * 64 + pend_dq_hh * 32, r);
                     tmem_ld_wait();
-                    if (q < p.T) store_row32_bf16(dst, r);
+                    if (ok) store_row32_bf16(dst, r);
                 }
             }
             tc_fence_before();
@@ -611,16 +690,18 @@ attention_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_
             // ---- per-query statistics of both heads: lse*log2e and D*scale, D = sum_d dO*O.  All global loads of the
             // thread are issued before the first use (one memory round trip per item).
             {
-                const int q = tid;
+                const int q = tid;                               // slot in the statistics arrays = query row of the tile(s)
+                const int qb = p.pair ? 2 * b + (q >> 6) : b;     // image and token of that slot
+                const int qt_ = p.pair ? (q & 63) : q;
                 uint4 ra[HP][HD / 8], rd[HP][HD / 8];
                 float lv[HP], dv[HP];
-                if (q < p.T) {
+                if (qt_ < p.T && qb < p.B && (!p.pair || q < 128)) {
 #pragma unroll
                     for (int hh = 0; hh < HP; ++hh) {
-                        const size_t off = ((size_t)(b * p.T + q) * p.H + sl * HP + hh) * HD;
+                        const size_t off = ((size_t)(qb * p.T + qt_) * p.H + sl * HP + hh) * HD;
 #pragma unroll
                         for (int c = 0; c < HD / 8; ++c) { ra[hh][c] = ldg_v4(p.out + off + c * 8); rd[hh][c] = ldg_v4(p.dout + off + c * 8); }
-                        lv[hh] = __ldg(p.lse + ((size_t)b * p.H + sl * HP + hh) * p.T + q) * kLog2eF;
+                        lv[hh] = __ldg(p.lse + ((size_t)qb * p.H + sl * HP + hh) * p.T + qt_) * kLog2eF;
                     }
 #pragma unroll
                     for (int hh = 0; hh < HP; ++hh) {
@@ -646,15 +727,17 @@ attention_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_
 
             for (int hh = 0; hh < HP; ++hh) {
                 for (int kt = 0; kt < p.NB; ++kt) {
-                    const int key = kt * 128 + row;
-                    const bool key_ok = key < p.T;
+                    const int key = kt * 128 + lrow;
+                    const bool key_ok = key < p.T && (!p.pair || 2 * b + img < p.B);
+                    const bool keys_all_ok = __all_sync(0xffffffffu, key_ok);
                     for (int qt = 0; qt < p.NB; ++qt, ++nblk) {
                         const int nq = min(128, p.Npad - qt * 128);
                         const int nh = nq > 64 ? 2 : 1;
                         for (int h = 0; h < nh; ++h, ++j) {
                             const int nqh = h == 0 ? min(64, nq) : nq - 64;
                             const int c = half * 32;                            // this warp's 32 query columns of the half block
-                            const bool active = c < nqh;
+                            // pair mode: half block h holds the queries of image h; key rows of the other image stay zero
+                            const bool active = c < nqh && (!p.pair || img == h);
                             uint32_t pw[16], dw[16];
                             mbar_wait(&st_full[j & 1], (j >> 1) & 1);
                             tc_fence_after();
@@ -663,24 +746,30 @@ attention_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_
                                 const uint32_t tb = tlane + (uint32_t)(j & 1) * kColBuf;
                                 tmem_ld_32x32(tb + kColST + c, rs);
                                 tmem_ld_32x32(tb + kColDP + c, rd);
-                                const int q0 = qt * 128 + h * 64 + c;
+                                const int q0 = qt * 128 + h * 64 + c;                // slot of the first query in the statistics arrays
                                 const uint32_t la = sLa + (hh * 256 + q0) * 4, da = sDa + (hh * 256 + q0) * 4;
                                 tmem_ld_wait();
+                                // Padding QUERIES need no masking: their statistics slot holds lse = +inf, so p = exp2(-inf) = 0
+                                // and dS = 0 * finite = 0.  Padding KEYS (zero K rows: s = 0, p = exp2(-lse) != 0) do; the select
+                                // is only compiled into the path taken by warps that own such rows.
+                                auto body = [&](auto mask_keys) {
 #pragma unroll
-                                for (int jj = 0; jj < 32; jj += 4) {
-                                    const float4 l4 = lds_v4f(la + jj * 4);      // warp-uniform address: one broadcast wavefront
-                                    const float4 d4 = lds_v4f(da + jj * 4);
-                                    const float lq[4] = {l4.x, l4.y, l4.z, l4.w}, dq_[4] = {d4.x, d4.y, d4.z, d4.w};
-                                    float pv[4], ev[4];
+                                    for (int jj = 0; jj < 32; jj += 4) {
+                                        const float4 l4 = lds_v4f(la + jj * 4);      // warp-uniform address: one broadcast wavefront
+                                        const float4 d4 = lds_v4f(da + jj * 4);
+                                        const float lq[4] = {l4.x, l4.y, l4.z, l4.w}, dq_[4] = {d4.x, d4.y, d4.z, d4.w};
+                                        float pv[4], ev[4];
 #pragma unroll
-                                    for (int u = 0; u < 4; ++u) {
-                                        pv[u] = fast_exp2(fmaf(__uint_as_float(rs[jj + u]), sl2, -lq[u]));
-                                        ev[u] = pv[u] * fmaf(__uint_as_float(rd[jj + u]), p.scale, -dq_[u]);
-                                        if (!key_ok || q0 + jj + u >= p.T) { pv[u] = 0.f; ev[u] = 0.f; }
+                                        for (int u = 0; u < 4; ++u) {
+                                            pv[u] = fast_exp2(fmaf(__uint_as_float(rs[jj + u]), sl2, -lq[u]));
+                                            ev[u] = pv[u] * fmaf(__uint_as_float(rd[jj + u]), p.scale, -dq_[u]);
+                                            if (decltype(mask_keys)::value && !key_ok) { pv[u] = 0.f; ev[u] = 0.f; }
+                                        }
+                                        pw[(jj >> 1)] = pack_bf16(pv[0], pv[1]); pw[(jj >> 1) + 1] = pack_bf16(pv[2], pv[3]);
+                                        dw[(jj >> 1)] = pack_bf16(ev[0], ev[1]); dw[(jj >> 1) + 1] = pack_bf16(ev[2], ev[3]);
                                     }
-                                    pw[(jj >> 1)] = pack_bf16(pv[0], pv[1]); pw[(jj >> 1) + 1] = pack_bf16(pv[2], pv[3]);
-                                    dw[(jj >> 1)] = pack_bf16(ev[0], ev[1]); dw[(jj >> 1) + 1] = pack_bf16(ev[2], ev[3]);
-                                }
+                                };
+                                if (keys_all_ok) body(std::false_type{}); else body(std::true_type{});
                             }
                             if (pend_kt >= 0) write_dvk();
                             if (pend_dq_hh >= 0) write_dq();
@@ -767,13 +856,22 @@ constexpr int kBwdSmem = 12 * kTileBytes + 4096 + 256 + 1024;
 
 template <int HD>
 static int launch_fwd_tc(const void* qkv, void* out, float* lse, int B, int T, int H, float scale, cudaStream_t s) {
-    CUtensorMap tm;
+    CUtensorMap tm, tm64;
     int rc = make_tmap_tokens(&tm, qkv, 3LL * H * HD, T, B, 128);
     if (rc) return rc;
+    rc = make_tmap_tokens(&tm64, qkv, 3LL * H * HD, T, B, 64);
+    if (rc) return rc;
     AttnFwdParams p;
-    p.T = T; p.H = H; p.slices_per_img = H * HD / 64; p.items = B * p.slices_per_img;
-    p.Npad = (T + 15) / 16 * 16; p.NB = (T + 127) / 128; p.NKB = (p.Npad + 127) / 128;
+    p.B = B; p.T = T; p.H = H; p.slices_per_img = H * HD / 64;
+    // Short sequences (T <= 64, the masked MAE encoder: 50 tokens): two images share every 128-row tile, the score matrix is
+    // 128 x 128 with the two diagonal 64 x 64 blocks used - half the tiles, MMAs and softmax rows of one image per tile.
+    p.pair = (T <= 64) ? 1 : 0;
+    if (const char* e = getenv("SSL4P_ATTN_PAIR")) p.pair = (T <= 64 && e[0] != '0') ? 1 : 0;   // tests: either mapping
+    p.items = (p.pair ? (B + 1) / 2 : B) * p.slices_per_img;
+    p.Npad = p.pair ? 128 : (T + 15) / 16 * 16; p.NB = (T + 127) / 128; p.NKB = (p.Npad + 127) / 128;
     p.scale = scale; p.out = (__nv_bfloat16*)out; p.lse = lse;
+    p.backoff_ns = 48;
+    if (const char* e = getenv("SSL4P_ATTN_BACKOFF")) p.backoff_ns = atoi(e);
     p.s_stride = (p.Npad + 31) / 32 * 32;
     // Separate O columns pay off when a chain has several tiles per item (T > 128: 175 -> 135 us at the decoder shape); for
     // one-tile items (T = 50: 49 vs 55 us) the read-out that is deferred by a whole item costs more than it hides.
@@ -784,27 +882,34 @@ static int launch_fwd_tc(const void* qkv, void* out, float* lse, int B, int T, i
     static bool attr = false;
     if (!attr) { SSL4P_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kFwdSmem)); attr = true; }
     const int grid = p.items < num_sms() ? p.items : num_sms();
-    kern<<<grid, kAttnThreads, kFwdSmem, s>>>(tm, p);
+    kern<<<grid, kAttnThreads, kFwdSmem, s>>>(tm, tm64, p);
     return check_launch("attention_fwd_tc_kernel");
 }
 
 template <int HD>
 static int launch_bwd_tc(const void* qkv, const void* out, const void* dout, const float* lse, void* dqkv, int B, int T, int H,
                          float scale, cudaStream_t s) {
-    CUtensorMap tmQ, tmD;
+    CUtensorMap tmQ, tmD, tmQ64, tmD64;
     int rc = make_tmap_tokens(&tmQ, qkv, 3LL * H * HD, T, B, 128);
     if (rc) return rc;
     rc = make_tmap_tokens(&tmD, dout, (long long)H * HD, T, B, 128);
     if (rc) return rc;
+    rc = make_tmap_tokens(&tmQ64, qkv, 3LL * H * HD, T, B, 64);
+    if (rc) return rc;
+    rc = make_tmap_tokens(&tmD64, dout, (long long)H * HD, T, B, 64);
+    if (rc) return rc;
     AttnBwdParams p;
-    p.T = T; p.H = H; p.slices_per_img = H * HD / 64; p.items = B * p.slices_per_img;
-    p.Npad = (T + 15) / 16 * 16; p.NB = (T + 127) / 128;
+    p.B = B; p.T = T; p.H = H; p.slices_per_img = H * HD / 64;
+    p.pair = (T <= 64) ? 1 : 0;                                  // see launch_fwd_tc
+    if (const char* e = getenv("SSL4P_ATTN_PAIR")) p.pair = (T <= 64 && e[0] != '0') ? 1 : 0;
+    p.items = (p.pair ? (B + 1) / 2 : B) * p.slices_per_img;
+    p.Npad = p.pair ? 128 : (T + 15) / 16 * 16; p.NB = (T + 127) / 128;
     p.scale = scale; p.out = (const __nv_bfloat16*)out; p.dout = (const __nv_bfloat16*)dout; p.lse = lse; p.dqkv = (__nv_bfloat16*)dqkv;
     auto kern = attention_bwd_tc_kernel<HD>;
     static bool attr = false;
     if (!attr) { SSL4P_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kBwdSmem)); attr = true; }
     const int grid = p.items < num_sms() ? p.items : num_sms();
-    kern<<<grid, kAttnThreads, kBwdSmem, s>>>(tmQ, tmD, p);
+    kern<<<grid, kAttnThreads, kBwdSmem, s>>>(tmQ, tmD, tmQ64, tmD64, p);
     return check_launch("attention_bwd_tc_kernel");
 }
 

@@ -215,16 +215,22 @@ def test_layernorm_fwd_bwd(M, D):
 
 
 # ---------------------------------------------------------------------------------------------- attention
-@pytest.mark.parametrize("impl", ["tcgen05", "tcgen05-alias", "tcgen05-sep", "mma"])
+@pytest.mark.parametrize("impl", ["tcgen05", "tcgen05-alias", "tcgen05-sep", "tcgen05-nopair", "mma"])
 @pytest.mark.parametrize("B,T,H,hd", [(2, 50, 12, 64), (2, 197, 16, 32), (1, 197, 12, 64), (3, 5, 2, 32), (2, 17, 2, 32), (2, 64, 4, 64),
-                                      (40, 50, 12, 64), (21, 197, 16, 32), (3, 128, 2, 64), (2, 129, 4, 32), (1, 256, 2, 32), (300, 208, 2, 32), (5, 209, 2, 64), (160, 16, 2, 32)])
+                                      (40, 50, 12, 64), (21, 197, 16, 32), (3, 128, 2, 64), (2, 129, 4, 32), (1, 256, 2, 32), (300, 208, 2, 32), (5, 209, 2, 64), (160, 16, 2, 32),
+                                      (1, 50, 12, 64), (301, 50, 2, 64), (7, 63, 4, 32), (2, 65, 2, 64)])
 def test_attention_fwd_bwd(B, T, H, hd, impl, monkeypatch):
     """Both attention kernels against fp32 torch on the same bf16 inputs (the larger batches put several work items
     on every persistent CTA; T = 128/129/256 sit on the tile boundaries)."""
     from ssl4polyp_b200 import ops
     if impl == "mma" and T > 208:
         pytest.skip("the mma.sync cross-check kernel stops at T = 208")
-    if impl.startswith("tcgen05-"):                          # force one of the two TMEM plans of the forward for every T
+    if impl == "tcgen05-nopair":                             # T <= 64 normally packs two images per tile: also run one image per tile
+        if T > 64:
+            pytest.skip("pairing only exists for T <= 64")
+        monkeypatch.setenv("SSL4P_ATTN_PAIR", "0")
+        impl = "tcgen05"
+    elif impl.startswith("tcgen05-"):                        # force one of the two TMEM plans of the forward for every T
         monkeypatch.setenv("SSL4P_ATTN_SEP", "0" if impl.endswith("alias") else "1")
         impl = "tcgen05"
     torch.manual_seed(B * 1000 + T)
