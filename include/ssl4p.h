@@ -54,6 +54,11 @@ enum {
 int ssl4p_gemm_bf16(const void* A, const void* B, void* C, void* C2, const float* bias, const void* aux,
                     int M, int N, int K, int lda, int ldb, int ldc, int ldc2, int ldaux,
                     int layout, int epilogue, int splits, int force_bn, void* stream);
+/* force_bn: low 16 bits = N tile (0 = choose; 64, 128, 192, 256), bits 16..23 = CTA group (0 = choose, 1, 2).
+ * CTA group 2 = `tcgen05.mma.cta_group::2`: the two SMs of a TPC (a cluster of two CTAs) share one 256 x BN tile, each
+ * staging its 128 rows of A and half of B.  ssl4p_gemm_set_cta_group sets the process-wide policy (0 = per shape,
+ * 1 = never, 2 = wherever M > 128) and returns the previous one; the environment variable SSL4P_GEMM_CG seeds it. */
+int ssl4p_gemm_set_cta_group(int mode);
 int ssl4p_gemm_pick_splits(int M, int N, int K);
 size_t ssl4p_gemm_workspace_bytes(int M, int N, int K, int layout, int epilogue);
 /* out[j] (+)= sum_g part[g*N + j], g < G  (two fixed-order stages: deterministic); workspace >= 32*N floats */

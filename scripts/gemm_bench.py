@@ -26,6 +26,7 @@ for tag, M, D in (("enc", Me, 768), ("dec", Md, 512)):
               (f"{tag} wproj TN", GEMM_TN, EPI_PARTIAL_F32, D, D, M)]
 cases.append(("dec pred  NT f32", GEMM_NT, EPI_BIAS_F32, Md, 768, 512))
 tot = 0.0
+totals = {}
 only = os.environ.get("GEMM_ONLY")          # e.g. GEMM_ONLY="dec fc1,dec dfc2" (ncu captures)
 for name, layout, epi, M, N, K in cases:
     if only and not any(name.startswith(o) for o in only.split(",")):
@@ -44,7 +45,10 @@ for name, layout, epi, M, N, K in cases:
     out = torch.empty(M, N, device=dev, dtype=torch.float32 if out32 else torch.bfloat16)
     out2 = torch.empty(M, N, device=dev, dtype=torch.bfloat16) if epi == EPI_BIAS_GELU_BF16 else None
     splits = ops.pick_splits(M, N, K) if layout == GEMM_TN else 1
-    for force_bn in [int(x) for x in os.environ.get("GEMM_BN", "0").split(",")]:      # GEMM_BN=0,256,192,128,64 sweeps the N tile
+    # GEMM_BN=0,256,192,128,64 sweeps the N tile; GEMM_CG=1,2 sweeps the CTA group (0 = the library's choice)
+    for force_bn in [int(x) | (int(c) << 16) for c in os.environ.get("GEMM_CG", "0").split(",") for x in os.environ.get("GEMM_BN", "0").split(",")]:
+        if (force_bn >> 16) == 2 and (force_bn & 0xffff) == 64:
+            continue
         ts = []
         for _ in range(reps):
             flush.zero_()
@@ -63,5 +67,7 @@ for name, layout, epi, M, N, K in cases:
         n_per_step = 12 if name.startswith("enc") else 8
         if "pred" in name: n_per_step = 1
         tot += t * n_per_step
-        print(f"{name:18s} bn={force_bn:3d} M={M:6d} N={N:5d} K={K:6d} s={splits:2d}  {t:8.1f} us  {2.0 * M * N * K / t / 1e6:7.1f} TF/s  {byt / t / 1e3:6.0f} GB/s   x{n_per_step}")
-print(f"sum over the step's block GEMMs: {tot / 1e3:.2f} ms")
+        totals[force_bn] = totals.get(force_bn, 0.0) + t * n_per_step
+        print(f"{name:18s} cg={force_bn >> 16} bn={force_bn & 0xffff:3d} M={M:6d} N={N:5d} K={K:6d} s={splits:2d}  {t:8.1f} us  {2.0 * M * N * K / t / 1e6:7.1f} TF/s  {byt / t / 1e3:6.0f} GB/s   x{n_per_step}")
+for k, v in totals.items():
+    print(f"sum over the step's block GEMMs (cg={k >> 16} bn={k & 0xffff}): {v / 1e3:.2f} ms")

@@ -16,6 +16,7 @@
 #include "common.cuh"
 #include "ssl4p.h"
 #include <mutex>
+#include <stdlib.h>
 #include <unordered_map>
 
 namespace ssl4p {
@@ -46,10 +47,12 @@ struct GemmParams {
     long long split_stride;      // elements between split-K partial planes of C
 };
 
-template <int BN, bool A_MN, bool B_MN, int EPI>
+template <int BN, bool A_MN, bool B_MN, int EPI, int CG>
 struct SmemLayout {
-    static constexpr int kABytes = BM * BK * 2;
-    static constexpr int kBBytes = BN * BK * 2;
+    static constexpr int kABytes = BM * BK * 2;                              // this CTA's 128 rows of the (128 * CG)-row tile
+    static constexpr int kBRows = BN / CG;                                   // N elements of the tile this CTA stages (CG = 2: its half)
+    static constexpr int kBRowsLoad = B_MN ? ((kBRows + 63) / 64) * 64 : kBRows;   // MN-major boxes are 64 elements wide
+    static constexpr int kBBytes = kBRowsLoad * BK * 2;
     static constexpr int kStageBytes = kABytes + kBBytes;
     static constexpr int kEpiBytes = epi_warps(EPI) * 32 * 32 * 4;     // per-warp transpose patches of the epilogue
     static constexpr int kBudget = 224 * 1024 - kEpiBytes;
@@ -251,11 +254,16 @@ __device__ __forceinline__ void epilogue_chunk_tma(const CUtensorMap* tmC, const
 }
 
 // ---- the kernel ---------------------------------------------------------------------------------
-template <int BN, bool A_MN, bool B_MN, int EPI>
+// CG = 1: one CTA per 128 x BN tile (cta_group::1).  CG = 2: a CTA pair (cluster of 2 = one TPC) per 256 x BN tile
+// (cta_group::2): CTA r owns rows [128 r, 128 r + 128) of the tile (its A rows, its TMEM accumulator, its epilogue) and
+// stages columns [r BN/2, (r+1) BN/2) of B; rank 0 issues the MMAs, the full barriers live in rank 0, every commit is
+// multicast to both CTAs.
+template <int BN, bool A_MN, bool B_MN, int EPI, int CG>
 __global__ void __launch_bounds__(gemm_threads(EPI), 1)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                     const __grid_constant__ CUtensorMap tmC, const GemmParams p) {
-    using L = SmemLayout<BN, A_MN, B_MN, EPI>;
+    using L = SmemLayout<BN, A_MN, B_MN, EPI, CG>;
+    constexpr int TM = BM * CG;                               // tile rows
     constexpr int kStages = L::kStages;
     constexpr int kEpiWarps = epi_warps(EPI);
     constexpr int kChunkStep = (kEpiWarps / 4) * 32;          // columns between two chunks of the same warp
@@ -275,10 +283,14 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     uint8_t* epi_stage = smem + kStages * L::kStageBytes + L::kBarBytes;   // kEpiWarps x 4 KB
 
     const int warp = threadIdx.x >> 5;
-    const int mt = (p.M + BM - 1) / BM;
+    const int mt = (p.M + TM - 1) / TM;
     const int nt = (p.N + BN - 1) / BN;
     const int tiles_mn = mt * nt;
     const int total_tiles = tiles_mn * p.splits;
+    uint32_t rank = 0;                                        // rank inside the CTA pair
+    if constexpr (CG == 2) rank = cluster_ctarank();
+    const int unit = CG == 2 ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;       // tile-processing unit (CTA or CTA pair)
+    const int nunits = CG == 2 ? (int)(gridDim.x >> 1) : (int)gridDim.x;
 
     if (warp == 0 && lane_id() == 0) {
         tma_prefetch_desc(&tmA);
@@ -287,15 +299,15 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     if (warp == 1) {
         if (lane_id() == 0) {
             for (int i = 0; i < kStages; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], 1); }
-            for (int i = 0; i < 2; ++i) { mbar_init(&tmem_full[i], 1); mbar_init(&tmem_empty[i], kEpiWarps); }
+            for (int i = 0; i < 2; ++i) { mbar_init(&tmem_full[i], 1); mbar_init(&tmem_empty[i], kEpiWarps * CG); }
             mbar_fence_init();
             fence_proxy_async();
         }
         __syncwarp();
-        tmem_alloc<kTmemCols>(tmem_slot);
+        if constexpr (CG == 2) tmem_alloc_cg2<kTmemCols>(tmem_slot); else tmem_alloc<kTmemCols>(tmem_slot);
     }
     tc_fence_before();
-    __syncthreads();
+    if constexpr (CG == 2) cluster_sync_all(); else __syncthreads();      // barriers of BOTH CTAs initialised before any TMA / commit
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
 
@@ -303,30 +315,36 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         // ===================== TMA producer =====================
         if (lane_id() == 0) {
             int stage = 0; uint32_t phase = 0;
-            for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+            // the barrier that counts this CTA's bytes: its own (CG = 1) or the leader's (CG = 2)
+            auto load = [&](void* dst, const CUtensorMap* m, int st, int c0, int c1) {
+                if constexpr (CG == 2) tma_load_2d_cg2(dst, m, mapa_u32(smem_u32(&full_bar[st]), 0), c0, c1);
+                else tma_load_2d(dst, m, &full_bar[st], c0, c1);
+            };
+            for (int tile = unit; tile < total_tiles; tile += nunits) {
                 const int split = tile / tiles_mn;
                 const int t = tile - split * tiles_mn;
-                const int m0 = (t / nt) * BM, n0 = (t % nt) * BN;
+                const int m0 = (t / nt) * TM + (int)rank * BM;                         // this CTA's A rows
+                const int n0 = (t % nt) * BN + (int)rank * L::kBRows;                  // this CTA's share of B
                 const int k_begin = split * p.k_per_split;
                 const int k_end = min(p.K, k_begin + p.k_per_split);
                 for (int k = k_begin; k < k_end; k += BK) {
                     mbar_wait(&empty_bar[stage], phase ^ 1);
-                    mbar_expect_tx(&full_bar[stage], L::kStageBytes);
+                    if (CG == 1 || rank == 0) mbar_expect_tx(&full_bar[stage], L::kStageBytes * CG);   // both CTAs' bytes
                     uint8_t* sa = smem_a + stage * L::kABytes;
                     uint8_t* sb = smem_b + stage * L::kBBytes;
                     if constexpr (!A_MN) {
-                        tma_load_2d(sa, &tmA, &full_bar[stage], k, m0);             // box [64 k] x [128 rows]
+                        load(sa, &tmA, stage, k, m0);                                // box [64 k] x [128 rows]
                     } else {
 #pragma unroll
                         for (int c = 0; c < BM / 64; ++c)                            // box [64 m] x [64 k rows]
-                            tma_load_2d(sa + c * (BK * 128), &tmA, &full_bar[stage], m0 + c * 64, k);
+                            load(sa + c * (BK * 128), &tmA, stage, m0 + c * 64, k);
                     }
                     if constexpr (!B_MN) {
-                        tma_load_2d(sb, &tmB, &full_bar[stage], k, n0);             // box [64 k] x [BN rows]
+                        load(sb, &tmB, stage, k, n0);                                // box [64 k] x [kBRows rows]
                     } else {
 #pragma unroll
-                        for (int c = 0; c < BN / 64; ++c)
-                            tma_load_2d(sb + c * (BK * 128), &tmB, &full_bar[stage], n0 + c * 64, k);
+                        for (int c = 0; c < L::kBRowsLoad / 64; ++c)
+                            load(sb + c * (BK * 128), &tmB, stage, n0 + c * 64, k);
                     }
                     if (++stage == kStages) { stage = 0; phase ^= 1; }
                 }
@@ -334,8 +352,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         }
         __syncwarp();
     } else if (warp == 1) {
-        // ===================== MMA issuer =====================
-        constexpr uint32_t idesc = umma_idesc_bf16(BM, BN, A_MN, B_MN);
+        // ===================== MMA issuer (CG = 2: the leader CTA only) =====================
+        if (CG == 1 || rank == 0) {
+        constexpr uint32_t idesc = umma_idesc_bf16(TM, BN, A_MN, B_MN);
         // K-major SW128: 8-row groups 1024 B apart (SBO), LBO unused.  MN-major SW128: 64-element MN chunks
         // BK*128 B apart (LBO), 8-k-row groups 1024 B apart (SBO).
         constexpr uint32_t a_lbo = A_MN ? BK * 128 : 16, a_sbo = 1024;
@@ -345,7 +364,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         const bool leader = lane_id() == 0;     // tcgen05.commit tracks the issuing thread: one fixed lane issues all
         int stage = 0; uint32_t phase = 0;
         int acc = 0; uint32_t acc_phase = 0;
-        for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        for (int tile = unit; tile < total_tiles; tile += nunits) {
             const int split = tile / tiles_mn;
             const int k_begin = split * p.k_per_split;
             const int k_end = min(p.K, k_begin + p.k_per_split);
@@ -363,27 +382,32 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                     for (int kk = 0; kk < BK / UMMA_K; ++kk) {
                         const uint64_t adesc = umma_smem_desc(sa + kk * a_kstep, a_lbo, a_sbo);
                         const uint64_t bdesc = umma_smem_desc(sb + kk * b_kstep, b_lbo, b_sbo);
-                        umma_bf16(tmem_d, adesc, bdesc, idesc, accumulate);
+                        if constexpr (CG == 2) umma_bf16_cg2(tmem_d, adesc, bdesc, idesc, accumulate);
+                        else umma_bf16(tmem_d, adesc, bdesc, idesc, accumulate);
                         accumulate = 1;
                     }
-                    umma_commit(&empty_bar[stage]);                  // frees the smem slot when the MMAs retire
+                    // frees the smem slot (in both CTAs) when the MMAs retire
+                    if constexpr (CG == 2) umma_commit_cg2(&empty_bar[stage], 3); else umma_commit(&empty_bar[stage]);
                 }
                 __syncwarp();
                 if (++stage == kStages) { stage = 0; phase ^= 1; }
             }
-            if (leader) umma_commit(&tmem_full[acc]);            // accumulator complete -> epilogue
+            if (leader) {                                        // accumulator complete -> epilogue (of both CTAs)
+                if constexpr (CG == 2) umma_commit_cg2(&tmem_full[acc], 3); else umma_commit(&tmem_full[acc]);
+            }
             __syncwarp();
             if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+        }
         }
     } else {
         // ===================== epilogue warps =====================
         const int q = warp & 3;                                       // TMEM lane quarter this warp may access
         const int chunk0 = ((warp - 2) >> 2) * 32;                    // the quarter's two warps interleave 32-column chunks
         int acc = 0; uint32_t acc_phase = 0;
-        for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        for (int tile = unit; tile < total_tiles; tile += nunits) {
             const int split = tile / tiles_mn;
             const int t = tile - split * tiles_mn;
-            const int m0 = (t / nt) * BM, n0 = (t % nt) * BN;
+            const int m0 = (t / nt) * TM + (int)rank * BM, n0 = (t % nt) * BN;
             const int row_base = m0 + q * 32;
             constexpr bool kAux = EPI == SSL4P_EPI_BIAS_RESIDUAL_F32 || EPI == SSL4P_EPI_DGELU_BF16;
             AuxRegs aux_cur, aux_nxt;
@@ -445,7 +469,10 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             }
             tc_fence_before();
             __syncwarp();
-            if (lane_id() == 0) mbar_arrive(&tmem_empty[acc]);
+            if (lane_id() == 0) {                                     // the MMA issuer (leader CTA) may overwrite this accumulator
+                if constexpr (CG == 2) mbar_arrive_cluster(mapa_u32(smem_u32(&tmem_empty[acc]), 0));
+                else mbar_arrive(&tmem_empty[acc]);
+            }
             if (++acc == 2) { acc = 0; acc_phase ^= 1; }
         }
     }
@@ -454,10 +481,11 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         if (warp >= 2 && lane_id() == 0) tma_store_wait_all();     // shared memory must outlive the bulk stores
     }
     tc_fence_before();
-    __syncthreads();
+    // CG = 2: the leader's MMAs read the peer's shared memory and write its TMEM: nobody leaves before both are done
+    if constexpr (CG == 2) cluster_sync_all(); else __syncthreads();
     if (warp == 1) {
         tc_fence_after();
-        tmem_dealloc<kTmemCols>(tmem_base);
+        if constexpr (CG == 2) tmem_dealloc_cg2<kTmemCols>(tmem_base); else tmem_dealloc<kTmemCols>(tmem_base);
     }
 }
 
@@ -520,62 +548,105 @@ static int make_tmap_out(CUtensorMap* out, void* ptr, long long cols, long long 
     return SSL4P_OK;
 }
 
-template <int BN, bool A_MN, bool B_MN, int EPI>
+template <int BN, bool A_MN, bool B_MN, int EPI, int CG>
 static int launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC, const GemmParams& p, cudaStream_t stream) {
-    using L = SmemLayout<BN, A_MN, B_MN, EPI>;
-    auto kern = gemm_tcgen05_kernel<BN, A_MN, B_MN, EPI>;
+    using L = SmemLayout<BN, A_MN, B_MN, EPI, CG>;
+    auto kern = gemm_tcgen05_kernel<BN, A_MN, B_MN, EPI, CG>;
     static bool attr_set = false;
     if (!attr_set) {
         SSL4P_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal));
         attr_set = true;
     }
-    const int mt = (p.M + BM - 1) / BM, nt = (p.N + BN - 1) / BN;
+    const int mt = (p.M + BM * CG - 1) / (BM * CG), nt = (p.N + BN - 1) / BN;
     const int total = mt * nt * p.splits;
-    const int grid = total < num_sms() ? total : num_sms();
-    kern<<<grid, gemm_threads(EPI), L::kTotal, stream>>>(tmA, tmB, tmC, p);
+    const int units = num_sms() / CG;                          // CTAs or CTA pairs (one pair = the two SMs of a TPC)
+    const int grid = (total < units ? total : units) * CG;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)grid);
+    cfg.blockDim = dim3((unsigned)gemm_threads(EPI));
+    cfg.dynamicSmemBytes = L::kTotal;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = CG; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = CG == 2 ? 1 : 0;
+    cudaError_t e = cudaLaunchKernelEx(&cfg, kern, tmA, tmB, tmC, p);
+    if (e != cudaSuccess) { set_error("gemm_tcgen05_kernel launch failed: %s", cudaGetErrorString(e)); return SSL4P_ERR_CUDA; }
     return check_launch("gemm_tcgen05_kernel");
 }
 
 // Only the (layout, epilogue) pairs the model uses are instantiated.
-template <int BN>
+template <int BN, int CG>
 static int dispatch(int layout, int epi, const CUtensorMap& a, const CUtensorMap& b, const CUtensorMap& c, const GemmParams& p, cudaStream_t s) {
     if (layout == SSL4P_GEMM_NT) {
         switch (epi) {
-            case SSL4P_EPI_BIAS_BF16: return launch<BN, false, false, SSL4P_EPI_BIAS_BF16>(a, b, c, p, s);
-            case SSL4P_EPI_BIAS_GELU_BF16: return launch<BN, false, false, SSL4P_EPI_BIAS_GELU_BF16>(a, b, c, p, s);
-            case SSL4P_EPI_BIAS_RESIDUAL_F32: return launch<BN, false, false, SSL4P_EPI_BIAS_RESIDUAL_F32>(a, b, c, p, s);
-            case SSL4P_EPI_BIAS_F32: return launch<BN, false, false, SSL4P_EPI_BIAS_F32>(a, b, c, p, s);
+            case SSL4P_EPI_BIAS_BF16: return launch<BN, false, false, SSL4P_EPI_BIAS_BF16, CG>(a, b, c, p, s);
+            case SSL4P_EPI_BIAS_GELU_BF16: return launch<BN, false, false, SSL4P_EPI_BIAS_GELU_BF16, CG>(a, b, c, p, s);
+            case SSL4P_EPI_BIAS_RESIDUAL_F32: return launch<BN, false, false, SSL4P_EPI_BIAS_RESIDUAL_F32, CG>(a, b, c, p, s);
+            case SSL4P_EPI_BIAS_F32: return launch<BN, false, false, SSL4P_EPI_BIAS_F32, CG>(a, b, c, p, s);
         }
     } else if (layout == SSL4P_GEMM_NN) {
         switch (epi) {
-            case SSL4P_EPI_BIAS_BF16: return launch<BN, false, true, SSL4P_EPI_BIAS_BF16>(a, b, c, p, s);
-            case SSL4P_EPI_DGELU_BF16: return launch<BN, false, true, SSL4P_EPI_DGELU_BF16>(a, b, c, p, s);
+            case SSL4P_EPI_BIAS_BF16: return launch<BN, false, true, SSL4P_EPI_BIAS_BF16, CG>(a, b, c, p, s);
+            case SSL4P_EPI_DGELU_BF16: return launch<BN, false, true, SSL4P_EPI_DGELU_BF16, CG>(a, b, c, p, s);
         }
     } else {
         switch (epi) {
-            case SSL4P_EPI_PARTIAL_F32: return launch<BN, true, true, SSL4P_EPI_PARTIAL_F32>(a, b, c, p, s);
+            case SSL4P_EPI_PARTIAL_F32: return launch<BN, true, true, SSL4P_EPI_PARTIAL_F32, CG>(a, b, c, p, s);
         }
     }
     set_error("gemm: epilogue %d is not available for layout %d", epi, layout);
     return SSL4P_ERR_UNSUPPORTED;
 }
 
-// wave-quantisation aware choice of the N tile: minimise ceil(tiles/SMs) * per-tile cost (~BN, plus a fixed term)
-static int pick_bn(int M, int N, int splits, bool need64) {
-    const int cands[4] = {256, 192, 128, 64};
-    const int sms = num_sms();
-    int best = 128; double best_cost = 1e30;
-    for (int i = 0; i < 4; ++i) {
-        const int bn = cands[i];
-        (void)need64;
-        const long long tiles = (long long)((M + BM - 1) / BM) * ((N + bn - 1) / bn) * splits;
-        const long long waves = (tiles + sms - 1) / sms;
-        // smaller N tiles run the tensor pipe below peak (A re-read from smem per MMA): mild penalty
-        const double eff = bn >= 256 ? 1.0 : bn >= 192 ? 0.95 : bn >= 128 ? 0.85 : 0.6;
-        const double cost = (double)waves * (bn / eff + 24.0);
-        if (cost < best_cost) { best_cost = cost; best = bn; }
+// 0 = choose per shape, 1 = cta_group::1 only, 2 = the CTA pair wherever the shape allows it
+// (ssl4p_gemm_set_cta_group; initial value from the environment variable SSL4P_GEMM_CG)
+static int& cta_group_mode() {
+    static int mode = [] { const char* e = getenv("SSL4P_GEMM_CG"); const int v = e ? atoi(e) : 0; return v >= 0 && v <= 2 ? v : 0; }();
+    return mode;
+}
+
+// Wave-quantisation aware choice of the tile: minimise ceil(tiles / units) * per-tile cost.  Every CTA computes
+// 128 x bn x K per tile in both modes, so the per-tile cost is ~ bn / rate + a fixed term; `rate` = relative tensor
+// throughput of the configuration (smaller N tiles re-read A from shared memory per MMA; a CTA pair fills
+// (128 + bn/2) x 64 operands per k-block and SM instead of (128 + bn) x 64).
+// bn_fixed / cg_fixed != 0 restrict the search (force_bn of the C-ABI call).
+// Policy 0 (per shape): the pair pays where the main loop is the bound.  Measured on B200 (profiles/r02b_gemm_bench.txt):
+// long-K shapes gain 8-14 % (dec dfc1 1160 -> 1308 TF/s, wgrads 1087 -> 1244), while at K = 512..768 the tile time is the
+// epilogue's and coupling two epilogues to one accumulator hand-off loses 3-8 % (dec fc1 + GELU 132 -> 140 us).
+static bool pair_pays(int K, int epi) {
+    switch (epi) {
+        case SSL4P_EPI_PARTIAL_F32: return true;
+        case SSL4P_EPI_BIAS_BF16: case SSL4P_EPI_DGELU_BF16: return K >= 768;
+        default: return K >= 1024;                  // GELU, residual and fp32 outputs: heavier epilogues
     }
-    return best;
+}
+
+static void pick_config(int M, int N, int K, int epi, int splits, int bn_fixed, int cg_fixed, int& bn_out, int& cg_out) {
+    const int sms = num_sms();
+    static const int cands[4] = {256, 192, 128, 64};
+    static const double rate1[4] = {1.00, 0.95, 0.85, 0.60};
+    static const double rate2[4] = {1.00, 0.95, 0.85, 0.0};
+    int mode = cg_fixed ? cg_fixed : cta_group_mode();
+    if (mode == 0) mode = pair_pays(K, epi) ? 2 : 1;
+    const bool pair_ok = M > BM && sms >= 2 && bn_fixed != 64;
+    double best_cost = 1e30;
+    bn_out = bn_fixed ? bn_fixed : 128; cg_out = 1;
+    for (int cg = 1; cg <= 2; ++cg) {
+        if (cg == 2 && (mode == 1 || !pair_ok)) continue;
+        if (cg == 1 && mode == 2 && pair_ok) continue;
+        for (int i = 0; i < 4; ++i) {
+            const double rate = cg == 2 ? rate2[i] : rate1[i];
+            const int bn = cands[i];
+            if (rate <= 0.0 || (bn_fixed && bn != bn_fixed)) continue;
+            const long long tiles = (long long)((M + BM * cg - 1) / (BM * cg)) * ((N + bn - 1) / bn) * splits;
+            const long long units = sms / cg;
+            const long long waves = (tiles + units - 1) / units;
+            const double cost = (double)waves * (bn / rate + 24.0);
+            if (cost < best_cost) { best_cost = cost; bn_out = bn; cg_out = cg; }
+        }
+    }
 }
 
 }  // namespace ssl4p
@@ -588,12 +659,20 @@ extern "C" size_t ssl4p_gemm_workspace_bytes(int M, int N, int K, int layout, in
     return (size_t)SSL4P_MAX_SPLITS * (size_t)M * (size_t)N * sizeof(float);
 }
 
+extern "C" int ssl4p_gemm_set_cta_group(int mode) {
+    const int prev = cta_group_mode();
+    if (mode >= 0 && mode <= 2) cta_group_mode() = mode;
+    return prev;
+}
+
 extern "C" int ssl4p_gemm_pick_splits(int M, int N, int K) {
     // ONE wave of 128x256 tiles: the largest split count whose tile total still fits the SM count (measured on B200,
     // scripts/wgrad_sweep.py: a second, partly filled wave costs more than the longer K loop of a single full one);
     // each split keeps >= 4 K-blocks.
-    const int sms = num_sms();
-    const int tiles = ((M + BM - 1) / BM) * ((N + 255) / 256);
+    // With the CTA pair the unit is a 256x256 tile on one of sms/2 pairs.
+    const bool pair = cta_group_mode() != 1 && M > BM;
+    const int sms = pair ? num_sms() / 2 : num_sms();
+    const int tiles = ((M + (pair ? 2 * BM : BM) - 1) / (pair ? 2 * BM : BM)) * ((N + 255) / 256);
     int s = sms / tiles;
     const int kb = (K + BK - 1) / BK;
     if (s > kb / 4) s = kb / 4;
@@ -623,8 +702,11 @@ extern "C" int ssl4p_gemm_bf16(const void* A, const void* B, void* C, void* C2, 
     if (aux) SSL4P_REQUIRE(ldaux % 8 == 0 && (reinterpret_cast<uintptr_t>(aux) & 15) == 0, "gemm: aux alignment");
     if (bias) SSL4P_REQUIRE((reinterpret_cast<uintptr_t>(bias) & 15) == 0, "gemm: bias alignment");
 
-    int bn = force_bn > 0 ? force_bn : pick_bn(M, N, splits, b_mn);
+    // force_bn: low 16 bits = N tile (0 = choose), bits 16.. = CTA group (0 = choose, 1, 2)
+    int bn, cg;
+    pick_config(M, N, K, epilogue, splits, force_bn & 0xffff, (force_bn >> 16) & 0xff, bn, cg);
     SSL4P_REQUIRE(bn == 64 || bn == 128 || bn == 192 || bn == 256, "gemm: unsupported N tile %d", bn);
+    SSL4P_REQUIRE(cg == 1 || (cg == 2 && bn >= 128), "gemm: unsupported CTA group %d for N tile %d", cg, bn);
 
     GemmParams p;
     p.M = M; p.N = N; p.K = K; p.ldc = ldc; p.ldc2 = ldc2; p.ldaux = ldaux;
@@ -639,16 +721,21 @@ extern "C" int ssl4p_gemm_bf16(const void* A, const void* B, void* C, void* C2, 
     if (!a_mn) rc = make_tmap(&tmA, A, K, M, lda, BM);            // A[M,K], K contiguous
     else       rc = make_tmap(&tmA, A, M, K, lda, BK);            // A stored [K,M], M contiguous
     if (rc) return rc;
-    if (!b_mn) rc = make_tmap(&tmB, B, K, N, ldb, bn);            // B[N,K], K contiguous
+    if (!b_mn) rc = make_tmap(&tmB, B, K, N, ldb, bn / cg);       // B[N,K], K contiguous (a CTA pair: half the tile per CTA)
     else       rc = make_tmap(&tmB, B, N, K, ldb, BK);            // B stored [K,N], N contiguous
     if (rc) return rc;
 
     CUtensorMap tmC = tmA;                                         // placeholder unless the epilogue stores through TMA
     if (epilogue == SSL4P_EPI_BIAS_BF16) { rc = make_tmap_out(&tmC, C, N, M, ldc); if (rc) return rc; }
-    if (bn == 256) return dispatch<256>(layout, epilogue, tmA, tmB, tmC, p, stream);
-    if (bn == 192) return dispatch<192>(layout, epilogue, tmA, tmB, tmC, p, stream);
-    if (bn == 128) return dispatch<128>(layout, epilogue, tmA, tmB, tmC, p, stream);
-    if (bn == 64) return dispatch<64>(layout, epilogue, tmA, tmB, tmC, p, stream);
+    if (cg == 2) {
+        if (bn == 256) return dispatch<256, 2>(layout, epilogue, tmA, tmB, tmC, p, stream);
+        if (bn == 192) return dispatch<192, 2>(layout, epilogue, tmA, tmB, tmC, p, stream);
+        if (bn == 128) return dispatch<128, 2>(layout, epilogue, tmA, tmB, tmC, p, stream);
+    }
+    if (bn == 256) return dispatch<256, 1>(layout, epilogue, tmA, tmB, tmC, p, stream);
+    if (bn == 192) return dispatch<192, 1>(layout, epilogue, tmA, tmB, tmC, p, stream);
+    if (bn == 128) return dispatch<128, 1>(layout, epilogue, tmA, tmB, tmC, p, stream);
+    if (bn == 64) return dispatch<64, 1>(layout, epilogue, tmA, tmB, tmC, p, stream);
     set_error("gemm: dispatch fell through");
     return SSL4P_ERR_ARG;
 }

@@ -92,6 +92,78 @@ def test_gemm_tn_wgrad(M, N, K, splits, bn):
     assert rel_err(acc, ref + 1) < 2e-3
 
 
+CG2 = 2 << 16          # force_bn bits 16..: CTA group 2 (tcgen05.mma.cta_group::2, a CTA pair per 256-row tile)
+
+
+@pytest.mark.parametrize("M,N,K", [(256, 256, 64), (300, 512, 512), (394, 2304, 768), (1000, 192, 1024), (12800, 768, 3072), (25216, 768, 768)])
+@pytest.mark.parametrize("bn", [CG2, CG2 | 128, CG2 | 192, CG2 | 256])
+def test_gemm_cta_pair_forward_epilogues(M, N, K, bn):
+    """Every NT epilogue through the CTA-pair kernel (ragged last row tile, N not a multiple of the tile, multi-wave)."""
+    from ssl4polyp_b200 import ops
+    g = torch.Generator(device="cpu").manual_seed(M + N + K + bn)
+    a = torch.randn(M, K, generator=g).to(dev()).bfloat16()
+    w = (torch.randn(N, K, generator=g) / math.sqrt(K)).to(dev()).bfloat16()
+    bias = torch.randn(N, generator=g).to(dev())
+    ref = a.float() @ w.float().t() + bias
+    out = ops.gemm(a, w, ops.GEMM_NT, ops.EPI_BIAS_BF16, bias=bias, force_bn=bn)
+    assert rel_err(out, ref) < 1e-2, rel_err(out, ref)
+    out32 = ops.gemm(a, w, ops.GEMM_NT, ops.EPI_BIAS_F32, bias=bias, force_bn=bn)
+    assert rel_err(out32, ref) < 2e-3, rel_err(out32, ref)
+    res = torch.randn(M, N, generator=g).to(dev())
+    outr = ops.gemm(a, w, ops.GEMM_NT, ops.EPI_BIAS_RESIDUAL_F32, bias=bias, aux=res, force_bn=bn)
+    assert rel_err(outr, ref + res) < 2e-3
+    dg, ge = ops.gemm(a, w, ops.GEMM_NT, ops.EPI_BIAS_GELU_BF16, bias=bias, force_bn=bn)
+    dgelu = 0.5 * (1 + torch.erf(ref / math.sqrt(2))) + ref * torch.exp(-0.5 * ref * ref) / math.sqrt(2 * math.pi)
+    assert rel_err(ge, F.gelu(ref)) < 4e-3 and rel_err(dg, dgelu) < 4e-3
+    # the pair and the single-CTA kernel run the same k order per output element: identical bits
+    assert torch.equal(out, ops.gemm(a, w, ops.GEMM_NT, ops.EPI_BIAS_BF16, bias=bias, force_bn=(1 << 16) | (bn & 0xffff)))
+
+
+@pytest.mark.parametrize("M,N,K", [(256, 128, 64), (394, 512, 2048), (300, 768, 2304), (12800, 768, 3072)])
+@pytest.mark.parametrize("bn", [CG2, CG2 | 128, CG2 | 192, CG2 | 256])
+def test_gemm_cta_pair_dgrad(M, N, K, bn):
+    from ssl4polyp_b200 import ops
+    dy = torch.randn(M, K, device=dev()).bfloat16()
+    w = (torch.randn(K, N, device=dev()) / math.sqrt(K)).bfloat16()
+    ref = dy.float() @ w.float()
+    out = ops.gemm(dy, w, ops.GEMM_NN, ops.EPI_BIAS_BF16, force_bn=bn)
+    assert rel_err(out, ref) < 1e-2, rel_err(out, ref)
+    dact = torch.randn(M, N, device=dev()).bfloat16()
+    cs = torch.full((N,), 7.0, device=dev())
+    out2 = ops.gemm(dy, w, ops.GEMM_NN, ops.EPI_DGELU_BF16, aux=dact, force_bn=bn, colsum_out=cs)
+    assert rel_err(out2, ref * dact.float()) < 1e-2
+    assert rel_err(cs, (ref * dact.float()).sum(0)) < 2e-3
+
+
+@pytest.mark.parametrize("M,N,K", [(256, 64, 64), (768, 768, 100), (2304, 768, 394), (512, 2048, 12800), (768, 3072, 1000), (512, 512, 50432)])
+@pytest.mark.parametrize("splits", [1, 3, 0])
+@pytest.mark.parametrize("bn", [CG2, CG2 | 128, CG2 | 256])
+def test_gemm_cta_pair_wgrad(M, N, K, splits, bn):
+    from ssl4polyp_b200 import ops
+    dy = torch.randn(K, M, device=dev()).bfloat16()
+    x = torch.randn(K, N, device=dev()).bfloat16()
+    ref = dy.float().t() @ x.float()
+    s = splits if splits > 0 else ops.pick_splits(M, N, K)
+    out = ops.gemm(dy, x, ops.GEMM_TN, ops.EPI_PARTIAL_F32, splits=s, force_bn=bn)
+    assert rel_err(out, ref) < 2e-3, (rel_err(out, ref), s)
+
+
+def test_gemm_cta_group_policy_switch():
+    """ssl4p_gemm_set_cta_group: both policies give the same bits on a model-shaped GEMM; the previous value comes back."""
+    from ssl4polyp_b200 import ops, _lib
+    lib = _lib.load()
+    a = torch.randn(1024, 768, device=dev()).bfloat16()
+    w = (torch.randn(2304, 768, device=dev()) / 28).bfloat16()
+    prev = lib.ssl4p_gemm_set_cta_group(1)
+    try:
+        o1 = ops.gemm(a, w, ops.GEMM_NT, ops.EPI_BIAS_BF16)
+        assert lib.ssl4p_gemm_set_cta_group(2) == 1
+        o2 = ops.gemm(a, w, ops.GEMM_NT, ops.EPI_BIAS_BF16)
+    finally:
+        lib.ssl4p_gemm_set_cta_group(prev)
+    assert torch.equal(o1, o2)
+
+
 def test_gemm_strided_views():
     """A operand as a row-strided view (qkv slices), C as a strided view."""
     from ssl4polyp_b200 import ops
