@@ -172,3 +172,197 @@ def transform_eval(frame: np.ndarray, size: int = 224) -> np.ndarray:
     """classification/data/transforms.py:233-258 without augmentations (val / test stages): T.Resize((size, size)) - PIL
     BILINEAR over the whole frame - then ToTensor and Normalize."""
     return to_tensor_normalize(crop_resize_u8(frame, 0, 0, frame.shape[0], frame.shape[1], size, "bilinear"), False)
+
+
+# =====================================================================================================================
+# Fine-tune TRAIN augmentations (classification/data/transforms.py:233-246), applied to the PIL image AFTER
+# T.Resize((S, S)):  ColorJitter(0.4, 0.5, 0.25, 0.01) -> GaussianBlur((25, 25), sigma=(0.001, 2.0)) -> RandomHorizontalFlip
+# -> RandomVerticalFlip -> RandomRotation(180) -> ToTensor -> Normalize.
+# The arithmetic is Pillow's (ImageEnhance = Image.blend with a degenerate image, libImaging/Blend.c, Convert.c rgb2l /
+# rgb2hsv_row / hsv2rgb, Image.rotate -> Geometry.c affine_fixed for NEAREST) and torchvision's (ColorJitter.get_params
+# order, adjust_hue's uint8 wrap-around shift, gaussian_blur = float32 conv2d of the uint8 image with a reflect pad, then
+# round-half-even).  Pinned against the INSTALLED libraries by oracle/make_augment_golden.py: every stage bit for bit
+# (the two HSV conversions over ALL 2^24 inputs) EXCEPT the blur, whose float32 summation order inside torch's CPU conv2d is
+# not specified: the restatement sums in float64 and may differ from torch by one grey level where the exact value lies
+# within ~1e-5 of a rounding boundary (a few values per image; the fixture records how many).
+# =====================================================================================================================
+def rgb_to_l(img: np.ndarray) -> np.ndarray:
+    """Convert.c rgb2l (ITU-R 601-2, 16-bit fixed point): L = (19595 R + 38470 G + 7471 B + 0x8000) >> 16."""
+    r, g, b = (img[..., i].astype(np.int64) for i in range(3))
+    return ((r * 19595 + g * 38470 + b * 7471 + 0x8000) >> 16).astype(np.uint8)
+
+
+def blend_u8(a: np.ndarray, b: np.ndarray, alpha: float) -> np.ndarray:
+    """Blend.c ImagingBlend(a, b, (float)alpha): a + alpha (b - a) in float32 (a multiply, then an add), truncated;
+    clipped to [0, 255] when alpha extrapolates."""
+    al = np.float32(alpha)
+    a32, b32 = a.astype(np.float32), b.astype(np.float32)
+    t = (a32 + (al * (b32 - a32)).astype(np.float32)).astype(np.float32)
+    if 0.0 <= alpha <= 1.0:
+        return t.astype(np.uint8)
+    return np.where(t <= 0, 0, np.where(t >= 255, 255, np.floor(t))).astype(np.uint8)
+
+
+def adjust_brightness(img, f):      # ImageEnhance.Brightness: degenerate = black
+    return blend_u8(np.zeros_like(img), img, f)
+
+
+def adjust_contrast(img, f):        # ImageEnhance.Contrast: degenerate = int(mean(L) + 0.5) everywhere
+    L = rgb_to_l(img)
+    mean = int(int(L.astype(np.int64).sum()) / L.size + 0.5)
+    return blend_u8(np.full_like(img, mean), img, f)
+
+
+def adjust_saturation(img, f):      # ImageEnhance.Color: degenerate = L replicated to three bands
+    return blend_u8(rgb_to_l(img)[..., None].repeat(3, axis=2), img, f)
+
+
+def rgb2hsv_u8(rgb: np.ndarray) -> np.ndarray:
+    """Convert.c rgb2hsv_row: float32 quotients, the hue assembled in double, stored to float32, scaled in double, truncated."""
+    f32, f64 = np.float32, np.float64
+    r, g, b = (rgb[..., i].astype(np.int32) for i in range(3))
+    maxc, minc = np.maximum(r, np.maximum(g, b)), np.minimum(r, np.minimum(g, b))
+    cr = (maxc - minc).astype(f32)
+    with np.errstate(divide="ignore", invalid="ignore"):
+        s = cr / maxc.astype(f32)
+        rc, gc, bc = ((maxc - c).astype(f32) / cr for c in (r, g, b))
+        h = np.where(r == maxc, (bc - gc).astype(f64),
+                     np.where(g == maxc, (2.0 + rc.astype(f64)) - bc.astype(f64), (4.0 + gc.astype(f64)) - rc.astype(f64))).astype(f32)
+        h = np.fmod(h.astype(f64) / 6.0 + 1.0, 1.0).astype(f32)
+        uh = np.clip((h.astype(f64) * 255.0).astype(np.int64), 0, 255)
+        us = np.clip((s.astype(f64) * 255.0).astype(np.int64), 0, 255)
+    gray = maxc == minc
+    return np.stack([np.where(gray, 0, uh), np.where(gray, 0, us), maxc], -1).astype(np.uint8)
+
+
+def hsv2rgb_u8(hsv: np.ndarray) -> np.ndarray:
+    """Convert.c hsv2rgb: sextant i = floor(h 6 / 255) and remainder f in double -> float32, p/q/t = round(v (1 - ...)) in double."""
+    f32, f64 = np.float32, np.float64
+    h6 = hsv[..., 0].astype(f64) * 6.0 / 255.0
+    i = np.floor(h6).astype(np.int64)
+    f = (h6 - i.astype(f64)).astype(f32).astype(f64)
+    fs = (hsv[..., 1].astype(f64) / 255.0).astype(f32).astype(f64)
+    v = hsv[..., 2].astype(f64)
+    rnd = lambda x: np.floor(x + 0.5).astype(np.int64)                # C round() of a non-negative value
+    p, q, t = (np.clip(rnd(v * (1.0 - e)), 0, 255) for e in (fs, fs * f, fs * (1.0 - f)))
+    vi = hsv[..., 2].astype(np.int64)
+    k = [i % 6 == n for n in range(6)]
+    R = np.select(k, [vi, q, p, p, t, vi]); G = np.select(k, [t, vi, vi, q, p, p]); B = np.select(k, [p, p, t, vi, vi, q])
+    gray = hsv[..., 1] == 0
+    return np.stack([np.where(gray, vi, R), np.where(gray, vi, G), np.where(gray, vi, B)], -1).astype(np.uint8)
+
+
+def hue_shift_u8(hue_factor: float) -> int:
+    """torchvision _functional_pil.adjust_hue: np.int32(hue_factor * 255).astype(np.uint8) (truncation toward zero, wrap)."""
+    return int(np.int32(hue_factor * 255).astype(np.uint8))
+
+
+def adjust_hue(img, hue_factor):    # RGB -> HSV, h += shift (uint8 wrap-around), HSV -> RGB; lossy even for a zero shift
+    hsv = rgb2hsv_u8(img)
+    hsv[..., 0] = hsv[..., 0] + np.uint8(hue_shift_u8(hue_factor))
+    return hsv2rgb_u8(hsv)
+
+
+def color_jitter(img, order, b, c, s, h):
+    """torchvision ColorJitter.forward with get_params' (fn_idx, brightness, contrast, saturation, hue)."""
+    for fn in order:
+        img = (adjust_brightness(img, b) if fn == 0 else adjust_contrast(img, c) if fn == 1 else
+               adjust_saturation(img, s) if fn == 2 else adjust_hue(img, h))
+    return img
+
+
+def gaussian_kernel1d(ksize: int, sigma: float) -> np.ndarray:
+    """torchvision _get_gaussian_kernel1d, the same float32 torch CPU ops call for call (the taps are host-side scalars)."""
+    import torch
+    half = (ksize - 1) * 0.5
+    x = torch.linspace(-half, half, steps=ksize, dtype=torch.float32)
+    pdf = torch.exp(-0.5 * (x / sigma).pow(2))
+    return (pdf / pdf.sum()).numpy()
+
+
+def gaussian_blur_u8(img: np.ndarray, k1d: np.ndarray) -> np.ndarray:
+    """F.gaussian_blur on a uint8 image: reflect pad, the separable kernel (ky kx^T, the same sigma on both axes), float
+    accumulate, round half to even, uint8.  Summed in float64 here (see the header of this section)."""
+    r = len(k1d) // 2
+    x = np.pad(img.astype(np.float64), ((r, r), (r, r), (0, 0)), mode="reflect")
+    k = k1d.astype(np.float64)
+    H, W = img.shape[:2]
+    tmp = sum(k[j] * x[:, j:j + W, :] for j in range(len(k)))
+    out = sum(k[i] * tmp[i:i + H, :, :] for i in range(len(k)))
+    return np.clip(np.rint(out), 0, 255).astype(np.uint8)
+
+
+def rotate_coeffs(angle: float, w: int, h: int):
+    """Image.rotate(angle, NEAREST, expand=False, center=None) -> (mode, a0..a5): mode 0 = Geometry.c affine_fixed with the
+    16.16 fixed-point coefficients (x_in = (a2 + a0 x + a1 y) >> 16, y_in = (a5 + a3 x + a4 y) >> 16), 1 = identity,
+    2 = rotate 180, 3 = rotate 90 (counter-clockwise), 4 = rotate 270; modes 3/4 only for square images."""
+    angle = angle % 360.0
+    if angle == 0:
+        return 1, (0,) * 6
+    if angle == 180:
+        return 2, (0,) * 6
+    if angle in (90, 270) and w == h:
+        return (3 if angle == 90 else 4), (0,) * 6
+    cx, cy = w / 2.0, h / 2.0
+    a = -math.radians(angle)
+    m = [round(math.cos(a), 15), round(math.sin(a), 15), 0.0, round(-math.sin(a), 15), round(math.cos(a), 15), 0.0]
+    m[2] = m[0] * (-cx) + m[1] * (-cy) + m[2]
+    m[5] = m[3] * (-cx) + m[4] * (-cy) + m[5]
+    m[2] += cx
+    m[5] += cy
+    fix = lambda v: int(math.floor(v * 65536.0 + 0.5))
+    return 0, (fix(m[0]), fix(m[1]), fix(m[2] + m[0] * 0.5 + m[1] * 0.5), fix(m[3]), fix(m[4]), fix(m[5] + m[3] * 0.5 + m[4] * 0.5))
+
+
+def rotate_nearest(img: np.ndarray, angle: float) -> np.ndarray:
+    h, w = img.shape[:2]
+    mode, (a0, a1, a2, a3, a4, a5) = rotate_coeffs(angle, w, h)
+    if mode == 1:
+        return img.copy()
+    if mode == 2:
+        return img[::-1, ::-1].copy()
+    if mode in (3, 4):
+        return np.rot90(img, 1 if mode == 3 else 3).copy()
+    ys, xs = np.mgrid[0:h, 0:w].astype(np.int64)
+    xin, yin = (a2 + a0 * xs + a1 * ys) >> 16, (a5 + a3 * xs + a4 * ys) >> 16
+    ok = (xin >= 0) & (xin < w) & (yin >= 0) & (yin < h)
+    out = np.zeros_like(img)
+    out[ok] = img[yin[ok], xin[ok]]
+    return out
+
+
+def draw_augment_params(brightness=0.4, contrast=0.5, saturation=0.25, hue=0.01, sigma=(0.001, 2.0), degrees=180.0):
+    """The random draws of the augmentation Compose for ONE image, global torch RNG, call for call:
+    ColorJitter.get_params (randperm(4), four uniforms), GaussianBlur.get_params, two flips (torch.rand(1) < 0.5),
+    RandomRotation.get_params."""
+    import torch
+    order = [int(v) for v in torch.randperm(4)]
+    b = float(torch.empty(1).uniform_(max(0.0, 1 - brightness), 1 + brightness))
+    c = float(torch.empty(1).uniform_(max(0.0, 1 - contrast), 1 + contrast))
+    s = float(torch.empty(1).uniform_(max(0.0, 1 - saturation), 1 + saturation))
+    h = float(torch.empty(1).uniform_(-hue, hue))
+    sg = torch.empty(1).uniform_(sigma[0], sigma[1]).item()
+    hflip = bool(torch.rand(1) < 0.5)
+    vflip = bool(torch.rand(1) < 0.5)
+    angle = float(torch.empty(1).uniform_(-degrees, degrees).item())
+    return dict(order=order, brightness=b, contrast=c, saturation=s, hue=h, sigma=sg, hflip=hflip, vflip=vflip, angle=angle)
+
+
+def augment_u8(img: np.ndarray, p: dict, ksize: int = 25) -> np.ndarray:
+    """ColorJitter -> GaussianBlur -> flips -> rotation on the resized uint8 image."""
+    img = color_jitter(img, p["order"], p["brightness"], p["contrast"], p["saturation"], p["hue"])
+    img = gaussian_blur_u8(img, gaussian_kernel1d(ksize, p["sigma"]))
+    if p["hflip"]:
+        img = img[:, ::-1]
+    if p["vflip"]:
+        img = img[::-1]
+    return rotate_nearest(np.ascontiguousarray(img), p["angle"])
+
+
+def transform_finetune_train(frame: np.ndarray, size: int = 224):
+    """classification/data/transforms.py:233-258, stage 'train': Resize (PIL bilinear) -> augmentations -> ToTensor -> Normalize,
+    global torch RNG.  Returns (tensor [3,size,size] float32, uint8 image before ToTensor, params)."""
+    img = crop_resize_u8(frame, 0, 0, frame.shape[0], frame.shape[1], size, "bilinear")
+    p = draw_augment_params()
+    u8 = augment_u8(img, p)
+    return to_tensor_normalize(u8, False), u8, p
