@@ -89,6 +89,38 @@ int ssl4p_crop_resize_normalize_u8(const void* frames, const long long* desc, in
                                    const float* mean3, const float* std3, float* out,
                                    void* workspace, size_t workspace_bytes, void* stream);
 
+/* The same resample with the uint8 HWC image as the result (no flip, no normalisation): out_u8 [N,S,S,3].  Feeds the
+ * fine-tune TRAIN augmentations below, which the reference applies to the PIL image between Resize and ToTensor. */
+int ssl4p_crop_resize_u8(const void* frames, const long long* desc, int N, int S, int max_crop, int filter,
+                         void* out_u8, void* workspace, size_t workspace_bytes, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * Fine-tune TRAIN augmentations (classification/data/transforms.py:233-258, stage 'train': ColorJitter(0.4, 0.5, 0.25,
+ * 0.01) -> GaussianBlur((25,25), sigma=(0.001,2)) -> RandomHorizontalFlip -> RandomVerticalFlip -> RandomRotation(180) ->
+ * ToTensor -> Normalize, a torchvision Compose on PIL images run per image on DataLoader workers).  Replaces Pillow's
+ * ImageEnhance / Image.blend (Blend.c), convert('L'/'HSV'/'RGB') (Convert.c), Image.rotate NEAREST (Geometry.c affine_fixed)
+ * and torchvision's adjust_hue / gaussian_blur / to_tensor / normalize; bit-identical to the CPU restatement in
+ * oracle/input_oracle.py (pinned against the installed libraries; the blur sums in float64, see there).
+ * All random draws are made by the caller with the reference's own torch RNG calls and passed per image:
+ *   params  device int32 [N, SSL4P_AUG_PARAM_INTS]: [0..3] the order of the four colour operations as drawn by
+ *           ColorJitter.get_params (0 brightness, 1 contrast, 2 saturation, 3 hue), [4] hue shift =
+ *           uint8(int32(hue_factor * 255)), [5] hflip, [6] vflip, [7] rotation mode (0 = affine with the 16.16 fixed-point
+ *           coefficients [8..13] = a0..a5 of Geometry.c affine_fixed, 1 = identity, 2 = 180, 3 = 90 ccw, 4 = 270),
+ *           [16..18] the float32 bit patterns of the brightness / contrast / saturation factors
+ *   taps    device float32 [N, SSL4P_AUG_MAX_TAPS]: the 1-D Gaussian of torchvision's _get_gaussian_kernel1d (host-computed)
+ * img / out: uint8 [N,S,S,3] (HWC); color_jitter and gaussian_blur may run in place (img == out) only for color_jitter.
+ * ------------------------------------------------------------------------------------------------ */
+#define SSL4P_AUG_PARAM_INTS 32
+#define SSL4P_AUG_MAX_TAPS 32
+int ssl4p_color_jitter_u8(const void* img, void* out, const int* params, int N, int S, void* stream);
+size_t ssl4p_gaussian_blur_workspace_bytes(int N, int S);
+int ssl4p_gaussian_blur_u8(const void* img, void* out, const float* taps, int ntaps, int N, int S,
+                           void* workspace, size_t workspace_bytes, void* stream);
+/* flips + rotation as one gather, then ToTensor + Normalize: out fp32 [N,3,S,S] and/or out_u8 [N,S,S,3] (either may be
+ * NULL); mean3 / std3 HOST pointers to 3 floats */
+int ssl4p_flip_rotate_normalize_u8(const void* img, const int* params, int N, int S, const float* mean3, const float* std3,
+                                   float* out, void* out_u8, void* stream);
+
 /* ------------------------------------------------------------------------------------------------
  * random_masking (models_mae.py:123-148) as a function of the noise the caller drew with torch.rand.
  *   ids_restore[n,i] = rank of noise[n,i] in its row (stable ascending: ties -> lower index first)  int64

@@ -198,7 +198,7 @@ def blend_u8(a: np.ndarray, b: np.ndarray, alpha: float) -> np.ndarray:
     al = np.float32(alpha)
     a32, b32 = a.astype(np.float32), b.astype(np.float32)
     t = (a32 + (al * (b32 - a32)).astype(np.float32)).astype(np.float32)
-    if 0.0 <= alpha <= 1.0:
+    if np.float32(0.0) <= al <= np.float32(1.0):                          # the C function takes alpha as a float
         return t.astype(np.uint8)
     return np.where(t <= 0, 0, np.where(t >= 255, 255, np.floor(t))).astype(np.uint8)
 

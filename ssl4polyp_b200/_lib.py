@@ -28,6 +28,11 @@ SIGNATURES = {
     "ssl4p_reduce_rows_f32": (i32, [vp, i32, i32, vp, i32, vp, sz, vp]),
     "ssl4p_crop_resize_workspace_bytes": (sz, [i32, i32]),
     "ssl4p_crop_resize_normalize_u8": (i32, [vp, vp, i32, i32, i32, i32, vp, vp, vp, vp, sz, vp]),
+    "ssl4p_crop_resize_u8": (i32, [vp, vp, i32, i32, i32, i32, vp, vp, sz, vp]),
+    "ssl4p_color_jitter_u8": (i32, [vp, vp, vp, i32, i32, vp]),
+    "ssl4p_gaussian_blur_workspace_bytes": (sz, [i32, i32]),
+    "ssl4p_gaussian_blur_u8": (i32, [vp, vp, vp, i32, i32, i32, vp, sz, vp]),
+    "ssl4p_flip_rotate_normalize_u8": (i32, [vp, vp, i32, i32, vp, vp, vp, vp, vp]),
     "ssl4p_mask_from_noise": (i32, [vp, i32, i32, i32, vp, vp, vp, vp]),
     "ssl4p_gather_tokens_f32": (i32, [vp, vp, vp, i32, i32, i32, i32, vp]),
     "ssl4p_patchify": (i32, [vp, vp, i32, i32, i32, i32, i32, vp]),

@@ -17,7 +17,7 @@ PKG = os.path.dirname(HERE)
 ROOT = os.path.dirname(PKG)
 OBJ_DIR = os.path.join(HERE, "build")
 LIB_PATH = os.path.join(PKG, "libssl4p.so")
-SOURCES = ["api.cu", "gemm_tcgen05.cu", "tokens.cu", "layernorm.cu", "attention.cu", "attention_tc.cu", "loss.cu", "optim.cu", "input_pipeline.cu"]
+SOURCES = ["api.cu", "gemm_tcgen05.cu", "tokens.cu", "layernorm.cu", "attention.cu", "attention_tc.cu", "loss.cu", "optim.cu", "input_pipeline.cu", "augment.cu"]
 HEADERS = [os.path.join(HERE, "common.cuh"), os.path.join(HERE, "attn_common.cuh"), os.path.join(ROOT, "include", "ssl4p.h")]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",

@@ -103,7 +103,7 @@ template <int kS>
 __global__ void __launch_bounds__(256)
 crop_resize_normalize_kernel(const uint8_t* __restrict__ frames, const long long* __restrict__ desc, const int* __restrict__ ws,
                              int S_rt, int band, int tile_rows, float m0, float m1, float m2, float s0, float s1, float s2,
-                             float* __restrict__ out) {
+                             float* __restrict__ out, uint8_t* __restrict__ out_u8) {
     extern __shared__ uint8_t tile[];                                // [tile_rows][3 S] uint8: rows of the horizontally resized crop
     const int S = kS > 0 ? kS : S_rt;
     const int n = blockIdx.y;
@@ -177,6 +177,11 @@ crop_resize_normalize_kernel(const uint8_t* __restrict__ frames, const long long
             const uint8_t* p = tile + r * row_bytes + xx * 3;
             v0 = p[0]; v1 = p[1]; v2 = p[2];
         }
+        if (out_u8 != nullptr) {                                     // the resized image itself (uint8 HWC), for the augmentation kernels
+            uint8_t* o8 = out_u8 + (((size_t)n * S + rr) * S + xx) * 3;
+            o8[0] = (uint8_t)v0; o8[1] = (uint8_t)v1; o8[2] = (uint8_t)v2;
+            continue;
+        }
         const int xo = flip ? S - 1 - xx : xx;
         float* o = out + (((size_t)n * 3) * S + rr) * S + xo;
         const size_t plane = (size_t)S * S;
@@ -201,10 +206,10 @@ extern "C" size_t ssl4p_crop_resize_workspace_bytes(int N, int S) {
     return (size_t)N * 2 * (size_t)S * (kMaxTaps + 2) * sizeof(int);
 }
 
-extern "C" int ssl4p_crop_resize_normalize_u8(const void* frames, const long long* desc, int N, int S, int max_crop, int filter,
-                                              const float* mean3, const float* std3, float* out,
-                                              void* workspace, size_t workspace_bytes, void* stream) {
-    SSL4P_REQUIRE(frames && desc && out && mean3 && std3, "crop_resize: null argument");
+static int crop_resize_impl(const void* frames, const long long* desc, int N, int S, int max_crop, int filter,
+                            const float* mean3, const float* std3, float* out, uint8_t* out_u8,
+                            void* workspace, size_t workspace_bytes, void* stream) {
+    SSL4P_REQUIRE(frames && desc && (out || out_u8) && mean3 && std3, "crop_resize: null argument");
     SSL4P_REQUIRE(N >= 0 && S > 0 && S <= 1024 && max_crop > 0, "crop_resize: bad shape N=%d S=%d max_crop=%d", N, S, max_crop);
     SSL4P_REQUIRE(filter == SSL4P_RESAMPLE_BICUBIC || filter == SSL4P_RESAMPLE_BILINEAR, "crop_resize: unknown filter %d", filter);
     const double scale = max_crop > S ? (double)max_crop / S : 1.0;
@@ -230,6 +235,20 @@ extern "C" int ssl4p_crop_resize_normalize_u8(const void* frames, const long lon
     if (rc) return rc;
     kernel<<<dim3((S + band - 1) / band, N), 256, smem, STREAM>>>(
         (const uint8_t*)frames, desc, (const int*)workspace, S, band, tile_rows,
-        mean3[0], mean3[1], mean3[2], std3[0], std3[1], std3[2], out);
+        mean3[0], mean3[1], mean3[2], std3[0], std3[1], std3[2], out, out_u8);
     return check_launch("crop_resize_normalize_kernel");
+}
+
+extern "C" int ssl4p_crop_resize_normalize_u8(const void* frames, const long long* desc, int N, int S, int max_crop, int filter,
+                                              const float* mean3, const float* std3, float* out,
+                                              void* workspace, size_t workspace_bytes, void* stream) {
+    SSL4P_REQUIRE(out, "crop_resize: null output");
+    return crop_resize_impl(frames, desc, N, S, max_crop, filter, mean3, std3, out, nullptr, workspace, workspace_bytes, stream);
+}
+
+extern "C" int ssl4p_crop_resize_u8(const void* frames, const long long* desc, int N, int S, int max_crop, int filter,
+                                    void* out_u8, void* workspace, size_t workspace_bytes, void* stream) {
+    static const float unit[3] = {0.f, 0.f, 0.f}, one[3] = {1.f, 1.f, 1.f};
+    SSL4P_REQUIRE(out_u8, "crop_resize_u8: null output");
+    return crop_resize_impl(frames, desc, N, S, max_crop, filter, unit, one, nullptr, (uint8_t*)out_u8, workspace, workspace_bytes, stream);
 }

@@ -86,6 +86,14 @@ class TrainTransform:
         return k, buf
 
     def __call__(self, frames, params=None, out=None):
+        dev, desc_dev, max_crop, n = self._upload(frames, params)
+        if n == 0:
+            return torch.empty(0, 3, self.size, self.size, dtype=torch.float32, device=self.device)
+        return ops.crop_resize_normalize(dev, desc_dev, self.size, max_crop, self.mean, self.std, out=out, filter=self.filter)
+
+    def _upload(self, frames, params=None):
+        """Draw (or take) the crop parameters, pack the crop rectangles into a pinned buffer, one H2D copy.
+        -> (device bytes, device descriptors int64 [N,8], largest crop extent, N)"""
         frames = [f.numpy() if isinstance(f, torch.Tensor) else np.asarray(f) for f in frames]
         for f in frames:
             if f.dtype != np.uint8 or f.ndim != 3 or f.shape[2] != 3:
@@ -121,10 +129,8 @@ class TrainTransform:
         ev.record()
         self._events[k] = ev
         self.h2d_bytes = total + desc.numel() * 8
-        if n == 0:
-            return torch.empty(0, 3, self.size, self.size, dtype=torch.float32, device=self.device)
-        max_crop = max(max(p[2], p[3]) for p in params)
-        return ops.crop_resize_normalize(dev, desc_dev, self.size, max_crop, self.mean, self.std, out=out, filter=self.filter)
+        max_crop = max((max(p[2], p[3]) for p in params), default=1)
+        return dev, desc_dev, max_crop, n
 
 
 class EvalTransform(TrainTransform):
@@ -137,3 +143,103 @@ class EvalTransform(TrainTransform):
 
     def draw(self, height: int, width: int):
         return 0, 0, height, width, False
+
+
+def _gaussian_kernel1d(ksize: int, sigma: float) -> torch.Tensor:
+    """torchvision _get_gaussian_kernel1d, the same float32 CPU ops call for call (25 host-side scalars per image)."""
+    half = (ksize - 1) * 0.5
+    x = torch.linspace(-half, half, steps=ksize, dtype=torch.float32)
+    pdf = torch.exp(-0.5 * (x / sigma).pow(2))
+    return pdf / pdf.sum()
+
+
+def _rotate_coeffs(angle: float, w: int, h: int):
+    """PIL Image.rotate(angle, NEAREST, expand=False, center=None): the special angles PIL turns into transposes, else the
+    affine matrix it builds in Python doubles (cos / sin rounded to 15 decimals, rotation about (w/2, h/2)) converted to the
+    16.16 fixed point of Geometry.c affine_fixed.  -> (mode, a0..a5), see include/ssl4p.h."""
+    angle = angle % 360.0
+    if angle == 0:
+        return 1, (0,) * 6
+    if angle == 180:
+        return 2, (0,) * 6
+    if angle in (90, 270) and w == h:
+        return (3 if angle == 90 else 4), (0,) * 6
+    cx, cy = w / 2.0, h / 2.0
+    a = -math.radians(angle)
+    m = [round(math.cos(a), 15), round(math.sin(a), 15), 0.0, round(-math.sin(a), 15), round(math.cos(a), 15), 0.0]
+    m[2] = m[0] * (-cx) + m[1] * (-cy) + m[2]
+    m[5] = m[3] * (-cx) + m[4] * (-cy) + m[5]
+    m[2] += cx
+    m[5] += cy
+    fix = lambda v: int(math.floor(v * 65536.0 + 0.5))
+    return 0, (fix(m[0]), fix(m[1]), fix(m[2] + m[0] * 0.5 + m[1] * 0.5), fix(m[3]), fix(m[4]), fix(m[5] + m[3] * 0.5 + m[4] * 0.5))
+
+
+class TrainAugment(EvalTransform):
+    """The fine-tune script's TRAIN transform (classification/data/transforms.py:233-258, stage 'train') with the pixel
+    work on the device:
+
+        T.Resize((S, S)) -> ColorJitter(0.4, 0.5, 0.25, 0.01) -> GaussianBlur((25, 25), sigma=(0.001, 2.0)) ->
+        RandomHorizontalFlip -> RandomVerticalFlip -> RandomRotation(180) -> ToTensor -> Normalize
+
+    `draw_augment()` makes the random draws of ONE image with the same torch RNG calls in the same order as that Compose
+    (randperm(4) + four uniforms, the blur sigma, two flips, the angle), so a seeded run augments identically; the frames
+    travel as uint8 (one H2D per batch) and five kernels do the rest (bilinear resample, colour chain, separable blur,
+    flip + rotation gather with ToTensor / Normalize).  `last_augment` holds the drawn parameters per image."""
+
+    def __init__(self, size: int = 224, brightness=0.4, contrast=0.5, saturation=0.25, hue=0.01, kernel_size=25,
+                 sigma=(0.001, 2.0), degrees=180.0, flip_p: float = 0.5, mean=IMAGENET_MEAN, std=IMAGENET_STD, device=None):
+        super().__init__(size, mean=mean, std=std, device=device)
+        if kernel_size % 2 == 0 or kernel_size > ops.AUG_MAX_TAPS:
+            raise RuntimeError(f"TrainAugment: kernel_size must be odd and <= {ops.AUG_MAX_TAPS}")
+        self.brightness = (max(0.0, 1 - brightness), 1 + brightness)      # ColorJitter._check_input
+        self.contrast = (max(0.0, 1 - contrast), 1 + contrast)
+        self.saturation = (max(0.0, 1 - saturation), 1 + saturation)
+        self.hue = (-hue, hue)
+        self.kernel_size, self.sigma, self.degrees, self.flip_p = kernel_size, sigma, float(degrees), flip_p
+        self.last_augment = []
+
+    def draw_augment(self) -> dict:
+        order = [int(v) for v in torch.randperm(4)]                        # ColorJitter.get_params
+        b = float(torch.empty(1).uniform_(self.brightness[0], self.brightness[1]))
+        c = float(torch.empty(1).uniform_(self.contrast[0], self.contrast[1]))
+        s = float(torch.empty(1).uniform_(self.saturation[0], self.saturation[1]))
+        h = float(torch.empty(1).uniform_(self.hue[0], self.hue[1]))
+        sg = torch.empty(1).uniform_(self.sigma[0], self.sigma[1]).item()    # GaussianBlur.get_params
+        hflip = bool(torch.rand(1) < self.flip_p)
+        vflip = bool(torch.rand(1) < self.flip_p)
+        angle = float(torch.empty(1).uniform_(-self.degrees, self.degrees).item())   # RandomRotation.get_params
+        return dict(order=order, brightness=b, contrast=c, saturation=s, hue=h, sigma=sg, hflip=hflip, vflip=vflip, angle=angle)
+
+    def pack_augment(self, aug: list):
+        """-> (int32 [N,32], float32 [N,32]) host tensors in the layout of include/ssl4p.h"""
+        n = len(aug)
+        ints = np.zeros((n, ops.AUG_PARAM_INTS), np.int32)
+        taps = torch.zeros(n, ops.AUG_MAX_TAPS, dtype=torch.float32)
+        S = self.size
+        for i, a in enumerate(aug):
+            ints[i, 0:4] = a["order"]
+            ints[i, 4] = int(np.int32(a["hue"] * 255).astype(np.uint8))    # adjust_hue: truncation toward zero, uint8 wrap
+            ints[i, 5], ints[i, 6] = int(a["hflip"]), int(a["vflip"])
+            mode, coef = _rotate_coeffs(a["angle"], S, S)
+            ints[i, 7] = mode
+            ints[i, 8:14] = coef
+            ints[i, 16:19] = np.array([a["brightness"], a["contrast"], a["saturation"]], np.float32).view(np.int32)
+            taps[i, :self.kernel_size] = _gaussian_kernel1d(self.kernel_size, a["sigma"])
+        return torch.from_numpy(ints), taps
+
+    def __call__(self, frames, augment=None, out=None, want_u8=False):
+        dev, desc_dev, max_crop, n = self._upload(frames)
+        if n == 0:
+            return torch.empty(0, 3, self.size, self.size, dtype=torch.float32, device=self.device)
+        if augment is None:
+            augment = [self.draw_augment() for _ in range(n)]
+        self.last_augment = list(augment)
+        ints, taps = self.pack_augment(augment)
+        ints_d = ints.pin_memory().to(self.device, non_blocking=True)
+        taps_d = taps.pin_memory().to(self.device, non_blocking=True)
+        self.h2d_bytes += ints.numel() * 4 + taps.numel() * 4
+        img = ops.crop_resize_u8(dev, desc_dev, self.size, max_crop, filter=self.filter)
+        ops.color_jitter_u8(img, ints_d, out=img)
+        blurred = ops.gaussian_blur_u8(img, taps_d, self.kernel_size)
+        return ops.flip_rotate_normalize_u8(blurred, ints_d, self.mean, self.std, out=out, want_u8=want_u8)

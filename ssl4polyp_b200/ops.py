@@ -201,6 +201,81 @@ def crop_resize_normalize(frames, desc, size, max_crop, mean, std, out=None, fil
     return out
 
 
+def crop_resize_u8(frames, desc, size, max_crop, filter="bilinear", out=None):
+    """The resample of `crop_resize_normalize` with the uint8 HWC image as the result: [N,size,size,3] (T.Resize of
+    classification/data/transforms.py:233-235 when the box is the whole frame)."""
+    lib = _lib.load()
+    _req(frames, torch.uint8, "crop_resize frames")
+    _req(desc, torch.int64, "crop_resize desc")
+    if desc.dim() != 2 or desc.shape[1] != 8:
+        raise RuntimeError("crop_resize: desc must be int64 [N, 8]")
+    N = desc.shape[0]
+    if out is None:
+        out = torch.empty(N, size, size, 3, dtype=torch.uint8, device=frames.device)
+    _req(out, torch.uint8, "crop_resize_u8 out")
+    assert out.shape == (N, size, size, 3)
+    if N == 0:
+        return out
+    ws = workspace(lib.ssl4p_crop_resize_workspace_bytes(N, size), frames.device, "crop_resize")
+    _lib.check(lib.ssl4p_crop_resize_u8(frames.data_ptr(), desc.data_ptr(), N, size, int(max_crop), {"bicubic": 0, "bilinear": 1}[filter],
+                                        out.data_ptr(), ws.data_ptr(), ws.numel(), _stream()), "crop_resize_u8")
+    return out
+
+
+AUG_PARAM_INTS, AUG_MAX_TAPS = 32, 32
+
+
+def color_jitter_u8(img, params, out=None):
+    """ColorJitter on uint8 [N,S,S,3] with host-drawn parameters (include/ssl4p.h: int32 [N,32]); one CTA per image."""
+    lib = _lib.load()
+    _req(img, torch.uint8, "color_jitter img")
+    _req(params, torch.int32, "color_jitter params")
+    N, S = img.shape[0], img.shape[1]
+    assert img.shape == (N, S, S, 3) and params.shape == (N, AUG_PARAM_INTS)
+    if out is None:
+        out = torch.empty_like(img)
+    _req(out, torch.uint8, "color_jitter out")
+    _lib.check(lib.ssl4p_color_jitter_u8(img.data_ptr(), out.data_ptr(), params.data_ptr(), N, S, _stream()), "color_jitter")
+    return out
+
+
+def gaussian_blur_u8(img, taps, ntaps, out=None):
+    """GaussianBlur on uint8 [N,S,S,3]; taps float32 [N,32] (the first `ntaps` are the 1-D kernel of each image)."""
+    lib = _lib.load()
+    _req(img, torch.uint8, "gaussian_blur img")
+    _req(taps, f32, "gaussian_blur taps")
+    N, S = img.shape[0], img.shape[1]
+    assert img.shape == (N, S, S, 3) and taps.shape == (N, AUG_MAX_TAPS)
+    if out is None:
+        out = torch.empty_like(img)
+    _req(out, torch.uint8, "gaussian_blur out")
+    if out.data_ptr() == img.data_ptr():
+        raise RuntimeError("gaussian_blur: cannot run in place")
+    ws = workspace(lib.ssl4p_gaussian_blur_workspace_bytes(N, S), img.device, "gaussian_blur")
+    _lib.check(lib.ssl4p_gaussian_blur_u8(img.data_ptr(), out.data_ptr(), taps.data_ptr(), int(ntaps), N, S,
+                                          ws.data_ptr(), ws.numel(), _stream()), "gaussian_blur")
+    return out
+
+
+def flip_rotate_normalize_u8(img, params, mean, std, out=None, want_u8=False):
+    """flips + Image.rotate(NEAREST) as one gather, then ToTensor + Normalize: fp32 [N,3,S,S] (and the uint8 image if asked)."""
+    import ctypes
+    lib = _lib.load()
+    _req(img, torch.uint8, "flip_rotate img")
+    _req(params, torch.int32, "flip_rotate params")
+    N, S = img.shape[0], img.shape[1]
+    assert img.shape == (N, S, S, 3) and params.shape == (N, AUG_PARAM_INTS)
+    if out is None:
+        out = torch.empty(N, 3, S, S, dtype=f32, device=img.device)
+    _req(out, f32, "flip_rotate out")
+    u8 = torch.empty_like(img) if want_u8 else None
+    m3 = (ctypes.c_float * 3)(*[float(v) for v in mean])
+    s3 = (ctypes.c_float * 3)(*[float(v) for v in std])
+    _lib.check(lib.ssl4p_flip_rotate_normalize_u8(img.data_ptr(), params.data_ptr(), N, S, ctypes.addressof(m3), ctypes.addressof(s3),
+                                                  out.data_ptr(), _ptr(u8), _stream()), "flip_rotate_normalize")
+    return (out, u8) if want_u8 else out
+
+
 def cast_bf16(src, dst=None):
     lib = _lib.load()
     _req(src, f32, "cast src")

@@ -350,10 +350,13 @@ def evaluate(model, loader, device, n_class, *, pos_weight=None, class_weights=N
     return res
 
 
-def train_epoch(engine, loader, device, epoch, args, *, lr, global_step=0, log=print, rank=0, world=1):
+def train_epoch(engine, loader, device, epoch, args, *, lr, global_step=0, log=print, rank=0, world=1, frame_transform=None):
     """Reference `train_epoch` (:4446-4649): one pass over the loader, a step per batch.  Full-size batches replay the
     captured step; a ragged tail runs eagerly.  The per-step loss stays on the device (the reference all-reduces it and
-    hits a barrier every step, :4547-4551); the epoch mean is reduced once at the end."""
+    hits a barrier every step, :4547-4551); the epoch mean is reduced once at the end.  A batch whose first element is a
+    list of decoded uint8 HWC frames goes through `input_pipeline.TrainAugment`: the stage-'train' transform of
+    classification/data/transforms.py:233-258 (Resize, ColorJitter, GaussianBlur, flips, rotation, ToTensor, Normalize)
+    with the reference's own RNG draws on the host and the pixel work on the device."""
     engine.model.train()
     limit = _limit(args.limit_train_batches)
     max_steps = _limit(args.max_train_steps)
@@ -364,7 +367,15 @@ def train_epoch(engine, loader, device, epoch, args, *, lr, global_step=0, log=p
             break
         if max_steps is not None and global_step + steps >= max_steps:
             break
-        data = batch[0].to(device, non_blocking=True)
+        if isinstance(batch[0], (list, tuple)):        # decoded frames: augment + normalise on the device
+            if frame_transform is None:
+                frame_transform = getattr(engine, "_train_augment", None)
+                if frame_transform is None:
+                    from .input_pipeline import TrainAugment
+                    frame_transform = engine._train_augment = TrainAugment(224, device=device)
+            data = frame_transform(batch[0])
+        else:
+            data = batch[0].to(device, non_blocking=True)
         target = batch[1].to(device, non_blocking=True)
         loss = engine.step(data, target, lr=lr, graph=data.shape[0] == per_rank)
         total = loss.clone() if total is None else total + loss

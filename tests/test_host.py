@@ -564,3 +564,34 @@ def test_input_oracle_matches_pillow_torchvision_golden():
         assert hashlib.sha256(np.ascontiguousarray(t).tobytes()).digest() == g[f"eval_sha256_{sd}"].tobytes(), sd
     ks, b, k = IO.precompute_coeffs(1155, 0.0, 1155.0, 224)
     assert ks == 23 and int(b[:, 1].max()) <= ks and abs(int(k[100].sum()) - (1 << 22)) <= ks
+
+
+def test_augment_oracle_matches_torchvision_golden():
+    """Fine-tune TRAIN augmentations (classification/data/transforms.py:233-258): oracle/input_oracle.py against
+    tests/golden/augment_golden.npz = what the INSTALLED Pillow + torchvision Compose produced under torch.manual_seed(321)
+    (oracle/make_augment_golden.py, which also pins every stage separately and both HSV conversions exhaustively).  Same
+    random draws; uint8 result identical except where the float32 conv2d of torchvision's blur rounds the other way
+    (<= 1 grey level, on the number of values the fixture recorded)."""
+    import numpy as np
+    from oracle import input_oracle as IO
+    g = np.load(os.path.join(ROOT, "tests", "golden", "augment_golden.npz"))
+    torch.manual_seed(int(g["seed"][0]))
+    bad = 0
+    for sd in (0, 1, 4, 6, 8, 9):
+        H, W = (int(v) for v in g[f"frame_{sd}"])
+        t, u8, p = IO.transform_finetune_train(IO.synthetic_frame(sd, H, W))
+        ip, fp = g[f"params_{sd}"], g[f"fparams_{sd}"]
+        assert p["order"] == [int(v) for v in ip[:4]] and IO.hue_shift_u8(p["hue"]) == int(ip[4])
+        assert (int(p["hflip"]), int(p["vflip"])) == (int(ip[5]), int(ip[6]))
+        assert [p["brightness"], p["contrast"], p["saturation"], p["hue"], p["sigma"], p["angle"]] == [float(v) for v in fp]
+        d = np.abs(u8.astype(int) - g[f"u8_{sd}"].astype(int))
+        assert d.max() <= 1, (sd, d.max())
+        bad += int((d > 0).sum())
+        assert t.dtype == np.float32 and np.array_equal(t.view(np.uint32), IO.to_tensor_normalize(u8, False).view(np.uint32))
+    assert bad == int(g["blur_mismatch_values"][0])
+    # stage properties: a zero hue shift still goes through the lossy HSV round trip; identity / 180 rotations are exact
+    img = IO.synthetic_frame(5, 32, 32)
+    assert np.array_equal(IO.rotate_nearest(img, 0.0), img) and np.array_equal(IO.rotate_nearest(img, 180.0), img[::-1, ::-1])
+    assert np.array_equal(IO.rotate_nearest(img, 90.0), np.rot90(img, 1))
+    assert np.array_equal(IO.gaussian_blur_u8(img, IO.gaussian_kernel1d(25, 0.001)), img)          # delta kernel
+    assert np.array_equal(IO.adjust_brightness(img, 1.0), img) and np.array_equal(IO.adjust_saturation(img, 1.0), img)

@@ -759,3 +759,32 @@ def test_evaluate_accepts_uint8_frames_through_the_device_eval_transform():
     b = TC.evaluate(m, as_tensors, dev(), 2)
     assert a["count"] == 6 and a["loss"] == b["loss"] and a["auroc"] == b["auroc"]
     assert torch.equal(a["_probabilities"], b["_probabilities"])
+
+
+def test_train_epoch_accepts_uint8_frames_through_the_device_train_augmentations():
+    """`train_epoch` on batches of decoded uint8 frames == `train_epoch` on the tensors the oracle's stage-'train'
+    transform (classification/data/transforms.py:233-258: Resize, ColorJitter, GaussianBlur, flips, rotation, ToTensor,
+    Normalize) makes from the same frames under the same torch seed: same draws, same pixels, same losses."""
+    import numpy as np
+    from oracle import input_oracle as IO
+    from ssl4polyp_b200 import models
+    from ssl4polyp_b200 import train_classification as TC
+    from ssl4polyp_b200.engine import ClassifierEngine
+    frames = [IO.synthetic_frame(90 + k, 180 + 23 * k, 240 + 19 * k) for k in range(8)]
+    labels = torch.tensor([0, 1, 0, 1, 1, 0, 1, 0])
+    args = TC.get_args(["--dataset", "synthetic", "--batch-size", "4", "--log-interval", "0"])
+    losses = []
+    for mode in ("frames", "tensors"):
+        torch.manual_seed(3)
+        m = models.ViT_from_MAE(None, True, 2, False, None, embed_dim=768, depth=12, num_heads=12, out_token="cls").to(dev()).train()
+        eng = ClassifierEngine(m, lr=1e-4, weight_decay=0.05)
+        torch.manual_seed(11)
+        if mode == "frames":
+            loader = [(frames[:4], labels[:4]), (frames[4:], labels[4:])]
+        else:
+            t = torch.from_numpy(np.stack([IO.transform_finetune_train(f)[0] for f in frames]))
+            loader = [(t[:4], labels[:4]), (t[4:], labels[4:])]
+        mean, steps = TC.train_epoch(eng, loader, dev(), 0, args, lr=1e-4)
+        assert steps == 2 and np.isfinite(mean)
+        losses.append(mean)
+    assert losses[0] == losses[1], losses

@@ -520,3 +520,135 @@ def test_crop_resize_other_output_sizes_match_the_oracle(size):
     got = _run_crop([frame], [(7, 9, 300, 380, True)], size=size)[0]
     want = IO.to_tensor_normalize(IO.crop_resize_u8(frame, 7, 9, 300, 380, size), True)
     assert got.shape == (3, size, size) and np.array_equal(got.view(np.uint32), want.view(np.uint32))
+
+
+# ---------------------------------------------------------------------------------------------- fine-tune TRAIN augmentations
+def _aug_params(n, order=(4, 4, 4, 4), hue=0, hflip=0, vflip=0, mode=1, coef=(0,) * 6, b=1.0, c=1.0, s=1.0):
+    import numpy as np
+    p = np.zeros((n, 32), np.int32)
+    p[:, 0:4] = order
+    p[:, 4], p[:, 5], p[:, 6], p[:, 7] = hue, hflip, vflip, mode
+    p[:, 8:14] = coef
+    p[:, 16:19] = np.array([b, c, s], np.float32).view(np.int32)
+    return torch.from_numpy(p).cuda()
+
+
+def test_hue_shift_all_16m_colours_bit_exact():
+    """adjust_hue = Pillow's RGB -> HSV -> RGB round trip (Convert.c) with a uint8 wrap-around shift: every one of the 2^24
+    colours, for a zero shift (still lossy) and for the shifts ColorJitter(hue=0.01) can draw (0, +-1, +-2)."""
+    import numpy as np
+    from oracle import input_oracle as IO
+    from ssl4polyp_b200 import ops
+    g = np.arange(256, dtype=np.uint8)
+    allrgb = np.ascontiguousarray(np.stack(np.meshgrid(g, g, g, indexing="ij"), -1).reshape(256, 256, 256, 3))   # 256 images of 256 x 256
+    dev_img = torch.from_numpy(allrgb).cuda()
+    hsv0 = IO.rgb2hsv_u8(allrgb.reshape(4096, 4096, 3))
+    for shift in (0, 2, 254, 100):
+        got = ops.color_jitter_u8(dev_img, _aug_params(256, order=(3, 4, 4, 4), hue=shift)).cpu().numpy()
+        hsv = hsv0.copy()
+        hsv[..., 0] = hsv[..., 0] + np.uint8(shift)
+        want = IO.hsv2rgb_u8(hsv).reshape(256, 256, 256, 3)
+        assert np.array_equal(got, want), (shift, int((got != want).any(-1).sum()))
+
+
+@pytest.mark.parametrize("S", [224, 64])
+def test_colour_operations_match_the_oracle(S):
+    import numpy as np
+    from oracle import input_oracle as IO
+    from ssl4polyp_b200 import ops
+    rng = np.random.default_rng(S)
+    imgs = np.stack([IO.synthetic_frame(40 + k, S, S) if k % 2 else rng.integers(0, 256, (S, S, 3), dtype=np.uint8) for k in range(4)])
+    imgs[3] = imgs[3] // 4 + 100                                         # low contrast: the blend extrapolates less
+    d = torch.from_numpy(imgs).cuda()
+    for f in (0.6, 0.9999, 1.0, 1.0001, 1.4, 0.5, 1.5, 0.0):
+        for op, fn in ((0, IO.adjust_brightness), (1, IO.adjust_contrast), (2, IO.adjust_saturation)):
+            got = ops.color_jitter_u8(d, _aug_params(4, order=(op, 4, 4, 4), b=f, c=f, s=f)).cpu().numpy()
+            for k in range(4):
+                assert np.array_equal(got[k], fn(imgs[k], float(np.float32(f)))), (op, f, k)
+    # the four operations chained in every order ColorJitter.get_params can draw, per-image parameters, in place
+    import itertools
+    orders = list(itertools.permutations(range(4)))
+    big = np.stack([imgs[k % 4] for k in range(24)])
+    prm = _aug_params(24, b=0.7, c=1.3, s=0.8, hue=255)
+    prm[:, 0:4] = torch.tensor(orders, dtype=torch.int32)
+    dd = torch.from_numpy(big).cuda()
+    got = ops.color_jitter_u8(dd, prm, out=dd).cpu().numpy()
+    for k, o in enumerate(orders):
+        want = IO.color_jitter(big[k], o, float(np.float32(0.7)), float(np.float32(1.3)), float(np.float32(0.8)), -0.005)   # int32(-0.005 * 255) = -1 -> 255
+        assert np.array_equal(got[k], want), o
+
+
+@pytest.mark.parametrize("S,sigmas", [(224, (0.001, 0.3, 1.0, 2.0)), (64, (0.7, 1.9)), (30, (1.3,))])
+def test_gaussian_blur_matches_the_oracle_bit_for_bit(S, sigmas):
+    """Same float64 operations in the same order as oracle.gaussian_blur_u8 (itself <= 1 grey level from torchvision)."""
+    import numpy as np
+    from oracle import input_oracle as IO
+    from ssl4polyp_b200 import ops
+    imgs = np.stack([IO.synthetic_frame(60 + k, S, S) for k in range(len(sigmas))])
+    taps = torch.zeros(len(sigmas), 32)
+    for k, sg in enumerate(sigmas):
+        taps[k, :25] = torch.from_numpy(IO.gaussian_kernel1d(25, sg))
+    got = ops.gaussian_blur_u8(torch.from_numpy(imgs).cuda(), taps.cuda(), 25).cpu().numpy()
+    for k, sg in enumerate(sigmas):
+        assert np.array_equal(got[k], IO.gaussian_blur_u8(imgs[k], IO.gaussian_kernel1d(25, sg))), sg
+
+
+def test_flip_rotate_normalize_matches_the_oracle():
+    import numpy as np
+    from oracle import input_oracle as IO
+    from ssl4polyp_b200 import ops
+    from ssl4polyp_b200.input_pipeline import _rotate_coeffs
+    S = 224
+    angles = [0.0, 180.0, -180.0, 90.0, -90.0, 270.0, 45.0, 1e-9, 118.42686462402344, -0.3, 179.999, -91.5]
+    rng = np.random.default_rng(3)
+    angles += [float(a) for a in rng.uniform(-180, 180, 12)]
+    n = len(angles)
+    imgs = np.stack([IO.synthetic_frame(80 + (k % 3), S, S) for k in range(n)])
+    prm = _aug_params(n)
+    for k, a in enumerate(angles):
+        mode, coef = _rotate_coeffs(a, S, S)
+        assert (mode, tuple(coef)) == IO.rotate_coeffs(a, S, S)
+        prm[k, 5], prm[k, 6], prm[k, 7] = k & 1, (k >> 1) & 1, mode
+        prm[k, 8:14] = torch.tensor(coef, dtype=torch.int32)
+    out, u8 = ops.flip_rotate_normalize_u8(torch.from_numpy(imgs).cuda(), prm, IO.IMAGENET_MEAN, IO.IMAGENET_STD, want_u8=True)
+    out, u8 = out.cpu().numpy(), u8.cpu().numpy()
+    for k, a in enumerate(angles):
+        img = imgs[k]
+        if k & 1:
+            img = img[:, ::-1]
+        if (k >> 1) & 1:
+            img = img[::-1]
+        want = IO.rotate_nearest(np.ascontiguousarray(img), a)
+        assert np.array_equal(u8[k], want), a
+        assert np.array_equal(out[k].view(np.uint32), IO.to_tensor_normalize(want, False).view(np.uint32)), a
+
+
+def test_train_augment_reproduces_the_compose_under_one_seed():
+    """input_pipeline.TrainAugment (host RNG draws + uint8 H2D + five kernels) against (a) the oracle's stage-'train'
+    transform, bit for bit, and (b) what the installed torchvision Compose produced under the same seed
+    (tests/golden/augment_golden.npz): the same draws, <= 1 grey level apart on exactly the recorded number of values
+    (torchvision's float32 blur rounding)."""
+    import numpy as np
+    from oracle import input_oracle as IO
+    from ssl4polyp_b200.input_pipeline import TrainAugment
+    import os
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "augment_golden.npz"))
+    seeds = (0, 1, 4, 6, 8, 9)
+    frames = [IO.synthetic_frame(sd, *(int(v) for v in g[f"frame_{sd}"])) for sd in seeds]
+    tf = TrainAugment(224)
+    torch.manual_seed(int(g["seed"][0]))
+    out, u8 = tf(frames, want_u8=True)
+    out, u8 = out.cpu().numpy(), u8.cpu().numpy()
+    torch.manual_seed(int(g["seed"][0]))
+    bad = 0
+    for k, sd in enumerate(seeds):
+        want_t, want_u8, p = IO.transform_finetune_train(frames[k])
+        assert tf.last_augment[k] == p
+        assert np.array_equal(u8[k], want_u8), sd
+        assert np.array_equal(out[k].view(np.uint32), want_t.view(np.uint32)), sd
+        d = np.abs(u8[k].astype(int) - g[f"u8_{sd}"].astype(int))
+        assert d.max() <= 1
+        bad += int((d > 0).sum())
+    assert bad == int(g["blur_mismatch_values"][0])
+    # feeds the classifier like a DataLoader batch would
+    assert out.shape == (6, 3, 224, 224) and np.isfinite(out).all()
