@@ -165,12 +165,6 @@ size_t ssl4p_layernorm_bwd_workspace_bytes(int M, int D);
 int ssl4p_attention_fwd(const void* qkv, void* out, float* lse, int B, int T, int H, int hd, float scale, void* stream);
 int ssl4p_attention_bwd(const void* qkv, const void* out, const void* dout, const float* lse, void* dqkv,
                         int B, int T, int H, int hd, float scale, void* stream);
-/* Same contract on warp-level mma.sync (the first revision of the kernels; kept as an independent on-device
- * cross-check of the tcgen05 kernels in tests, T <= 208). */
-int ssl4p_attention_fwd_mma(const void* qkv, void* out, float* lse, int B, int T, int H, int hd, float scale, void* stream);
-int ssl4p_attention_bwd_mma(const void* qkv, const void* out, const void* dout, const float* lse, void* dqkv,
-                            int B, int T, int H, int hd, float scale, void* stream);
-
 /* Decoder input assembly (models_mae.py:177-183):
  *   x[n,0,:]   = y[n,0,:] + dpos[0]
  *   x[n,1+i,:] = (ids_restore[n,i] < Te-1 ? y[n,1+ids_restore[n,i],:] : mask_token) + dpos[1+i]

@@ -11,15 +11,15 @@ flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
 for (B, T, H, hd) in [(256, 197, 16, 32), (256, 50, 12, 64), (128, 197, 12, 64)]:
     qkv = torch.randn(B * T, 3 * H * hd, device=dev).bfloat16()
     do = torch.randn(B * T, H * hd, device=dev).bfloat16()
-    for impl in ("tcgen05", "mma"):
+    for impl in ("tcgen05",):
         tf, tb = [], []
         for _ in range(reps):
             flush.zero_()
             e = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
             e[0].record()
-            out, lse = ops.attention_fwd(qkv, B, T, H, hd, hd ** -0.5, impl=impl)
+            out, lse = ops.attention_fwd(qkv, B, T, H, hd, hd ** -0.5)
             e[1].record()
-            dqkv = ops.attention_bwd(qkv, out, do, lse, B, T, H, hd, hd ** -0.5, impl=impl)
+            dqkv = ops.attention_bwd(qkv, out, do, lse, B, T, H, hd, hd ** -0.5)
             e[2].record()
             torch.cuda.synchronize()
             tf.append(e[0].elapsed_time(e[1]) * 1e3); tb.append(e[1].elapsed_time(e[2]) * 1e3)

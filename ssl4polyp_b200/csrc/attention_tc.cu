@@ -99,6 +99,7 @@ attention_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    pdl_wait_then_trigger();
 
     if (warp == 8) {
         // ===================== TMA producer =====================
@@ -494,6 +495,7 @@ attention_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    pdl_wait_then_trigger();
 
     if (warp == 8) {
         // ===================== TMA producer =====================
@@ -882,7 +884,8 @@ static int launch_fwd_tc(const void* qkv, void* out, float* lse, int B, int T, i
     static bool attr = false;
     if (!attr) { SSL4P_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kFwdSmem)); attr = true; }
     const int grid = p.items < num_sms() ? p.items : num_sms();
-    kern<<<grid, kAttnThreads, kFwdSmem, s>>>(tm, tm64, p);
+    cudaError_t e = launch_ex(kern, dim3((unsigned)grid), dim3(kAttnThreads), (size_t)kFwdSmem, s, 1, tm, tm64, p);
+    if (e != cudaSuccess) { set_error("attention_fwd_tc_kernel launch failed: %s", cudaGetErrorString(e)); return SSL4P_ERR_CUDA; }
     return check_launch("attention_fwd_tc_kernel");
 }
 
@@ -909,7 +912,8 @@ static int launch_bwd_tc(const void* qkv, const void* out, const void* dout, con
     static bool attr = false;
     if (!attr) { SSL4P_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kBwdSmem)); attr = true; }
     const int grid = p.items < num_sms() ? p.items : num_sms();
-    kern<<<grid, kAttnThreads, kBwdSmem, s>>>(tmQ, tmD, tmQ64, tmD64, p);
+    cudaError_t e = launch_ex(kern, dim3((unsigned)grid), dim3(kAttnThreads), (size_t)kBwdSmem, s, 1, tmQ, tmD, tmQ64, tmD64, p);
+    if (e != cudaSuccess) { set_error("attention_bwd_tc_kernel launch failed: %s", cudaGetErrorString(e)); return SSL4P_ERR_CUDA; }
     return check_launch("attention_bwd_tc_kernel");
 }
 

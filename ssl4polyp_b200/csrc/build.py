@@ -17,8 +17,12 @@ PKG = os.path.dirname(HERE)
 ROOT = os.path.dirname(PKG)
 OBJ_DIR = os.path.join(HERE, "build")
 LIB_PATH = os.path.join(PKG, "libssl4p.so")
-SOURCES = ["api.cu", "gemm_tcgen05.cu", "tokens.cu", "layernorm.cu", "attention.cu", "attention_tc.cu", "loss.cu", "optim.cu", "input_pipeline.cu", "augment.cu"]
+SOURCES = ["api.cu", "gemm_tcgen05.cu", "tokens.cu", "layernorm.cu", "attention_tc.cu", "loss.cu", "optim.cu", "input_pipeline.cu", "augment.cu"]
 HEADERS = [os.path.join(HERE, "common.cuh"), os.path.join(HERE, "attn_common.cuh"), os.path.join(ROOT, "include", "ssl4p.h")]
+# test infrastructure: an independent on-device implementation the product kernels are cross-checked against (tests only)
+CHECK_DIR = os.path.join(ROOT, "tests", "csrc")
+CHECK_SOURCES = ["attention_mma.cu"]
+CHECK_LIB_PATH = os.path.join(ROOT, "tests", "libssl4p_check.so")
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
          "-Xcompiler", "-fPIC", "-I" + os.path.join(ROOT, "include"), "-I" + HERE]
@@ -31,11 +35,11 @@ def _stale(target: str, deps: list[str]) -> bool:
     return any(os.path.getmtime(d) > t for d in deps)
 
 
-def _compile(src: str, force: bool) -> str:
+def _compile(src: str, force: bool, src_dir: str = HERE) -> str:
     obj = os.path.join(OBJ_DIR, src.replace(".cu", ".o"))
-    path = os.path.join(HERE, src)
+    path = os.path.join(src_dir, src)
     if force or _stale(obj, [path] + HEADERS):
-        cmd = [NVCC] + FLAGS + ["-c", path, "-o", obj]
+        cmd = [NVCC] + FLAGS + ["-I" + src_dir, "-c", path, "-o", obj]
         r = subprocess.run(cmd, capture_output=True, text=True)
         if r.returncode != 0:
             raise RuntimeError(f"nvcc failed for {src}:\n{r.stdout}\n{r.stderr}")
@@ -59,6 +63,15 @@ def build(force: bool = False, verbose: bool = True) -> str:
             print(f"built {LIB_PATH}")
     elif verbose:
         print(f"up to date: {LIB_PATH}")
+    if os.path.isdir(CHECK_DIR):                              # tests/libssl4p_check.so (skipped in a source tree without tests/)
+        cobjs = [_compile(s, force, CHECK_DIR) for s in CHECK_SOURCES]
+        if force or _stale(CHECK_LIB_PATH, cobjs):
+            r = subprocess.run([NVCC, "-shared", "-o", CHECK_LIB_PATH] + cobjs + ["-gencode", "arch=compute_100a,code=sm_100a"],
+                               capture_output=True, text=True)
+            if r.returncode != 0:
+                raise RuntimeError(f"link failed:\n{r.stdout}\n{r.stderr}")
+            if verbose:
+                print(f"built {CHECK_LIB_PATH}")
     return LIB_PATH
 
 

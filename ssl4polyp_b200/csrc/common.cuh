@@ -27,6 +27,31 @@ int check_launch(const char* what);          // cudaGetLastError → SSL4P_ERR_C
         ::ssl4p::set_error("%s failed: %s", #call, cudaGetErrorString(e__)); return SSL4P_ERR_CUDA; } } while (0)
 
 int num_sms();                               // SM count of the current device (cached)
+bool pdl_enabled();                          // programmatic dependent launch for the kernels of the step (SSL4P_PDL=1; default off)
+
+// Launch with optional cluster dimension and, when enabled, programmatic stream serialisation: the kernel may be scheduled
+// while its predecessor in the stream is still draining (its CTAs take SMs as the predecessor's CTAs retire and run their
+// prologue - barrier init, TMEM allocation, descriptor prefetch); it must execute pdl_wait_then_trigger() before its first
+// global-memory access.  Without the attribute the two device instructions are no-ops.
+template <typename... KArgs>
+inline cudaError_t launch_ex(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, int cluster_x, KArgs... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+    cudaLaunchAttribute attr[2];
+    unsigned n = 0;
+    if (cluster_x > 1) {
+        attr[n].id = cudaLaunchAttributeClusterDimension;
+        attr[n].val.clusterDim.x = (unsigned)cluster_x; attr[n].val.clusterDim.y = 1; attr[n].val.clusterDim.z = 1;
+        ++n;
+    }
+    if (pdl_enabled()) {
+        attr[n].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[n].val.programmaticStreamSerializationAllowed = 1;
+        ++n;
+    }
+    cfg.attrs = attr; cfg.numAttrs = n;
+    return cudaLaunchKernelEx(&cfg, kern, args...);
+}
 
 // ---- small device utilities ---------------------------------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
@@ -42,6 +67,13 @@ __device__ __forceinline__ bool elect_one() {
         "selp.u32 %0, 1, 0, P;\n\t}\n"
         : "=r"(pred));
     return pred != 0;
+}
+
+// Programmatic dependent launch: wait until every grid this one depends on has completed and its memory is visible, then
+// let the NEXT kernel of the stream be scheduled (it blocks at the same point until this grid has completed).
+__device__ __forceinline__ void pdl_wait_then_trigger() {
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
 }
 
 __device__ __forceinline__ float warp_sum(float v) {

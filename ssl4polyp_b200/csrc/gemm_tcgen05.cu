@@ -310,6 +310,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     if constexpr (CG == 2) cluster_sync_all(); else __syncthreads();      // barriers of BOTH CTAs initialised before any TMA / commit
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    pdl_wait_then_trigger();                                  // everything above overlapped the previous kernel's tail
 
     if (warp == 0) {
         // ===================== TMA producer =====================
@@ -561,17 +562,7 @@ static int launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensor
     const int total = mt * nt * p.splits;
     const int units = num_sms() / CG;                          // CTAs or CTA pairs (one pair = the two SMs of a TPC)
     const int grid = (total < units ? total : units) * CG;
-    cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3((unsigned)grid);
-    cfg.blockDim = dim3((unsigned)gemm_threads(EPI));
-    cfg.dynamicSmemBytes = L::kTotal;
-    cfg.stream = stream;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeClusterDimension;
-    attr[0].val.clusterDim.x = CG; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
-    cfg.attrs = attr;
-    cfg.numAttrs = CG == 2 ? 1 : 0;
-    cudaError_t e = cudaLaunchKernelEx(&cfg, kern, tmA, tmB, tmC, p);
+    cudaError_t e = launch_ex(kern, dim3((unsigned)grid), dim3((unsigned)gemm_threads(EPI)), (size_t)L::kTotal, stream, CG, tmA, tmB, tmC, p);
     if (e != cudaSuccess) { set_error("gemm_tcgen05_kernel launch failed: %s", cudaGetErrorString(e)); return SSL4P_ERR_CUDA; }
     return check_launch("gemm_tcgen05_kernel");
 }

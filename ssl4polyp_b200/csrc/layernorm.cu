@@ -17,6 +17,7 @@ layernorm_fwd_kernel(const float* __restrict__ x, const float* __restrict__ gamm
                      __nv_bfloat16* __restrict__ y, float* __restrict__ mean_out, float* __restrict__ rstd_out, int M, int D) {
     const int lane = lane_id();
     const int row = blockIdx.x * kLnWarps + (threadIdx.x >> 5);
+    pdl_wait_then_trigger();
     if (row >= M) return;
     const float4* xr = reinterpret_cast<const float4*>(x + (size_t)row * D);
     const float4* g4 = reinterpret_cast<const float4*>(gamma);
@@ -78,6 +79,7 @@ layernorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const float* __restri
     extern __shared__ float s_red[];                           // [kLnWarps][3*D]
     const int lane = lane_id();
     const int warp = threadIdx.x >> 5;
+    pdl_wait_then_trigger();
     const float inv_d = 1.0f / (float)D;
     const float4* g4 = reinterpret_cast<const float4*>(gamma);
     static_assert(NV > 0, "register-resident variant only");
@@ -141,6 +143,7 @@ layernorm_bwd_generic_kernel(const __nv_bfloat16* __restrict__ dy, const float* 
     extern __shared__ float s_red[];                           // [kLnWarps][3*D]
     const int lane = lane_id();
     const int warp = threadIdx.x >> 5;
+    pdl_wait_then_trigger();
     const float inv_d = 1.0f / (float)D;
     float* my = s_red + (size_t)warp * 3 * D;
     for (int j = lane; j < 3 * D; j += 32) my[j] = 0.f;
@@ -180,6 +183,7 @@ __global__ void __launch_bounds__(256)
 ln_param_grad_reduce_kernel(const float* __restrict__ part, int G, int D, float* __restrict__ dgamma,
                             float* __restrict__ dbeta, float* __restrict__ dxsum, int accumulate, int accumulate_dxsum) {
     __shared__ float sh[8][33];
+    pdl_wait_then_trigger();
     const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
     const int j = blockIdx.x * 32 + tx;
     const int W = 3 * D;
@@ -216,12 +220,9 @@ extern "C" int ssl4p_layernorm_fwd(const float* x, const float* gamma, const flo
     if (M == 0) return SSL4P_OK;
     const int grid = (M + kLnWarps - 1) / kLnWarps, threads = kLnWarps * 32;
     __nv_bfloat16* yb = (__nv_bfloat16*)y;
-    switch (D) {
-        case 512: layernorm_fwd_kernel<4><<<grid, threads, 0, STREAM>>>(x, gamma, beta, eps, yb, mean, rstd, M, D); break;
-        case 768: layernorm_fwd_kernel<6><<<grid, threads, 0, STREAM>>>(x, gamma, beta, eps, yb, mean, rstd, M, D); break;
-        case 1024: layernorm_fwd_kernel<8><<<grid, threads, 0, STREAM>>>(x, gamma, beta, eps, yb, mean, rstd, M, D); break;
-        default: layernorm_fwd_kernel<0><<<grid, threads, 0, STREAM>>>(x, gamma, beta, eps, yb, mean, rstd, M, D); break;
-    }
+    auto kern = D == 512 ? layernorm_fwd_kernel<4> : D == 768 ? layernorm_fwd_kernel<6> : D == 1024 ? layernorm_fwd_kernel<8> : layernorm_fwd_kernel<0>;
+    cudaError_t e = launch_ex(kern, dim3(grid), dim3(threads), (size_t)0, STREAM, 1, x, gamma, beta, eps, yb, mean, rstd, M, D);
+    if (e != cudaSuccess) { set_error("layernorm_fwd_kernel launch failed: %s", cudaGetErrorString(e)); return SSL4P_ERR_CUDA; }
     return check_launch("layernorm_fwd_kernel");
 }
 
@@ -243,11 +244,12 @@ extern "C" int ssl4p_layernorm_bwd(const void* dy, const float* x, const float* 
     float* part = (float*)workspace;
     const __nv_bfloat16* dyb = (const __nv_bfloat16*)dy;
     __nv_bfloat16* dxbb = (__nv_bfloat16*)dxb;
+    cudaError_t le = cudaSuccess;
 #define LN_BWD(NV_)                                                                                                        \
     {                                                                                                                      \
         static bool attr = false;                                                                                          \
         if (!attr && smem > 48 * 1024) { SSL4P_CUDA(cudaFuncSetAttribute(layernorm_bwd_kernel<NV_>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); attr = true; } \
-        layernorm_bwd_kernel<NV_><<<grid, threads, smem, STREAM>>>(dyb, x, mean, rstd, gamma, residual_grad, dx_out, dxbb, part, M, D); \
+        le = launch_ex(layernorm_bwd_kernel<NV_>, dim3(grid), dim3(threads), smem, STREAM, 1, dyb, x, mean, rstd, gamma, residual_grad, dx_out, dxbb, part, M, D); \
     }
     switch (D) {
         case 512: LN_BWD(4) break;
@@ -255,12 +257,14 @@ extern "C" int ssl4p_layernorm_bwd(const void* dy, const float* x, const float* 
         case 1024: LN_BWD(8) break;
         default: {
             SSL4P_REQUIRE(smem <= 48 * 1024, "layernorm_bwd: generic path supports D <= 512");
-            layernorm_bwd_generic_kernel<<<grid, threads, smem, STREAM>>>(dyb, x, mean, rstd, gamma, residual_grad, dx_out, dxbb, part, M, D);
+            le = launch_ex(layernorm_bwd_generic_kernel, dim3(grid), dim3(threads), smem, STREAM, 1, dyb, x, mean, rstd, gamma, residual_grad, dx_out, dxbb, part, M, D);
         }
     }
 #undef LN_BWD
+    if (le != cudaSuccess) { set_error("layernorm_bwd_kernel launch failed: %s", cudaGetErrorString(le)); return SSL4P_ERR_CUDA; }
     int rc = check_launch("layernorm_bwd_kernel");
     if (rc) return rc;
-    ln_param_grad_reduce_kernel<<<(3 * D + 31) / 32, 256, 0, STREAM>>>(part, grid, D, dgamma, dbeta, dx_colsum, accumulate, accumulate_colsum);
+    le = launch_ex(ln_param_grad_reduce_kernel, dim3((3 * D + 31) / 32), dim3(256), (size_t)0, STREAM, 1, (const float*)part, grid, D, dgamma, dbeta, dx_colsum, accumulate, accumulate_colsum);
+    if (le != cudaSuccess) { set_error("ln_param_grad_reduce_kernel launch failed: %s", cudaGetErrorString(le)); return SSL4P_ERR_CUDA; }
     return check_launch("ln_param_grad_reduce_kernel");
 }

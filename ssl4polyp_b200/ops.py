@@ -415,23 +415,21 @@ def layernorm_bwd(dy, x, mean, rstd, gamma, residual_grad, dgamma, dbeta, *, wan
     return dx_out, dxb
 
 
-def attention_fwd(qkv, B, T, H, hd, scale, impl="tcgen05"):
+def attention_fwd(qkv, B, T, H, hd, scale):
     """qkv bf16 [B*T, 3*H*hd] -> (out bf16 [B*T, H*hd], lse fp32 [B,H,T])"""
     lib = _lib.load()
     _req(qkv, bf16, "qkv")
     out = torch.empty(B * T, H * hd, dtype=bf16, device=qkv.device)
     lse = torch.empty(B, H, T, dtype=f32, device=qkv.device)
-    fn = {"tcgen05": lib.ssl4p_attention_fwd, "mma": lib.ssl4p_attention_fwd_mma}[impl]
-    _lib.check(fn(qkv.data_ptr(), out.data_ptr(), lse.data_ptr(), B, T, H, hd, float(scale), _stream()), "attention_fwd")
+    _lib.check(lib.ssl4p_attention_fwd(qkv.data_ptr(), out.data_ptr(), lse.data_ptr(), B, T, H, hd, float(scale), _stream()), "attention_fwd")
     return out, lse
 
 
-def attention_bwd(qkv, out, dout, lse, B, T, H, hd, scale, impl="tcgen05"):
+def attention_bwd(qkv, out, dout, lse, B, T, H, hd, scale):
     lib = _lib.load()
     _req(dout, bf16, "dout")
     dqkv = torch.empty_like(qkv)
-    fn = lib.ssl4p_attention_bwd_mma if impl == "mma" else lib.ssl4p_attention_bwd
-    _lib.check(fn(qkv.data_ptr(), out.data_ptr(), dout.data_ptr(), lse.data_ptr(), dqkv.data_ptr(), B, T, H, hd, float(scale),
+    _lib.check(lib.ssl4p_attention_bwd(qkv.data_ptr(), out.data_ptr(), dout.data_ptr(), lse.data_ptr(), dqkv.data_ptr(), B, T, H, hd, float(scale),
                                        _stream()), "attention_bwd")
     return dqkv
 

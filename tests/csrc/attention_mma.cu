@@ -1,3 +1,7 @@
+// TEST INFRASTRUCTURE ONLY: built into tests/libssl4p_check.so (never into the product library libssl4p.so).  The first
+// revision of the attention kernels, on warp-level mma.sync; kept as an independent ON-DEVICE cross-check of the tcgen05
+// kernels (tests/test_ops_gpu.py::test_attention_fwd_bwd) and as the comparison arm of scripts/attn_bench.py.
+//
 // Fused multi-head self-attention forward/backward for the short sequences of the MAE path
 // (timm 0.4.12 Attention.forward as used by /root/reference/src/ssl4polyp/models/mae/models_mae.py:166,186:
 //  softmax(q k^T * hd^-0.5) v with T = 50 (encoder), 197 (decoder / classifier), hd = 64 / 32).
@@ -8,9 +12,24 @@
 // Backward recomputes P from the saved log-sum-exp in two register-resident passes (dQ by query tile, dK/dV by key
 // tile), so there are no atomics and the result is deterministic.
 #include "common.cuh"
-#include "ssl4p.h"
+#include "ssl4p_check.h"
+#include <stdarg.h>
 
 namespace ssl4p {
+
+// the plumbing the product library keeps in api.cu, restated so that this library stands alone
+static thread_local char g_check_err[512] = "";
+void set_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_check_err, sizeof(g_check_err), fmt, ap);
+    va_end(ap);
+}
+int check_launch(const char* what) {
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) { set_error("%s: launch failed: %s", what, cudaGetErrorString(e)); return SSL4P_ERR_CUDA; }
+    return SSL4P_OK;
+}
 
 __device__ __forceinline__ void mma_bf16(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
     asm volatile(
@@ -395,6 +414,8 @@ static int launch_bwd(const void* qkv, const void* out, const void* dout, const 
 }  // namespace ssl4p
 
 using namespace ssl4p;
+
+extern "C" const char* ssl4p_check_last_error(void) { return g_check_err; }
 
 static int attn_check(int B, int T, int H, int hd) {
     SSL4P_REQUIRE(B > 0 && H > 0 && T > 0, "attention: bad shape");

@@ -287,6 +287,35 @@ def test_layernorm_fwd_bwd(M, D):
 
 
 # ---------------------------------------------------------------------------------------------- attention
+def _mma_check():
+    """tests/libssl4p_check.so: the mma.sync attention kernels, an independent on-device implementation (test infrastructure,
+    not part of the product library)."""
+    import ctypes as C
+    import os
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "libssl4p_check.so")
+    lib = C.CDLL(path)
+    vp, i32, f32 = C.c_void_p, C.c_int, C.c_float
+    lib.ssl4p_attention_fwd_mma.argtypes = [vp, vp, vp, i32, i32, i32, i32, f32, vp]
+    lib.ssl4p_attention_bwd_mma.argtypes = [vp, vp, vp, vp, vp, i32, i32, i32, i32, f32, vp]
+    lib.ssl4p_check_last_error.restype = C.c_char_p
+    return lib
+
+
+def _attention_mma(qkv, B, T, H, hd, scale, out=None, dout=None, lse=None):
+    lib = _mma_check()
+    st = torch.cuda.current_stream().cuda_stream
+    if dout is None:
+        out = torch.empty(B * T, H * hd, dtype=torch.bfloat16, device=qkv.device)
+        lse = torch.empty(B, H, T, dtype=torch.float32, device=qkv.device)
+        rc = lib.ssl4p_attention_fwd_mma(qkv.data_ptr(), out.data_ptr(), lse.data_ptr(), B, T, H, hd, scale, st)
+        assert rc == 0, lib.ssl4p_check_last_error()
+        return out, lse
+    dqkv = torch.empty_like(qkv)
+    rc = lib.ssl4p_attention_bwd_mma(qkv.data_ptr(), out.data_ptr(), dout.data_ptr(), lse.data_ptr(), dqkv.data_ptr(), B, T, H, hd, scale, st)
+    assert rc == 0, lib.ssl4p_check_last_error()
+    return dqkv
+
+
 @pytest.mark.parametrize("impl", ["tcgen05", "tcgen05-alias", "tcgen05-sep", "tcgen05-nopair", "mma"])
 @pytest.mark.parametrize("B,T,H,hd", [(2, 50, 12, 64), (2, 197, 16, 32), (1, 197, 12, 64), (3, 5, 2, 32), (2, 17, 2, 32), (2, 64, 4, 64),
                                       (40, 50, 12, 64), (21, 197, 16, 32), (3, 128, 2, 64), (2, 129, 4, 32), (1, 256, 2, 32), (300, 208, 2, 32), (5, 209, 2, 64), (160, 16, 2, 32),
@@ -312,13 +341,14 @@ def test_attention_fwd_bwd(B, T, H, hd, impl, monkeypatch):
     a = ((q @ k.transpose(-2, -1)) * scale).softmax(-1)
     o_ref = (a @ v).transpose(1, 2).reshape(B, T, H * hd)
     qkv_d = qkv.reshape(B * T, 3 * H * hd).to(dev())
-    out, lse = ops.attention_fwd(qkv_d, B, T, H, hd, scale, impl=impl)
+    out, lse = _attention_mma(qkv_d, B, T, H, hd, scale) if impl == "mma" else ops.attention_fwd(qkv_d, B, T, H, hd, scale)
     assert rel_err(out.cpu().reshape(B, T, H * hd), o_ref.detach()) < 1e-2
     lse_ref = torch.logsumexp((q @ k.transpose(-2, -1)) * scale, dim=-1)
     assert torch.allclose(lse.cpu(), lse_ref.detach(), atol=2e-3, rtol=1e-3)
     do = torch.randn(B, T, H * hd).bfloat16()
     o_ref.backward(do.float())
-    dqkv = ops.attention_bwd(qkv_d, out, do.reshape(B * T, H * hd).to(dev()), lse, B, T, H, hd, scale, impl=impl)
+    do_d = do.reshape(B * T, H * hd).to(dev())
+    dqkv = _attention_mma(qkv_d, B, T, H, hd, scale, out=out, dout=do_d, lse=lse) if impl == "mma" else ops.attention_bwd(qkv_d, out, do_d, lse, B, T, H, hd, scale)
     dqkv = dqkv.cpu().float().reshape(B, T, 3, H, hd).permute(2, 0, 3, 1, 4)
     for i, (name, t) in enumerate((("dq", q), ("dk", k), ("dv", v))):
         assert rel_err(dqkv[i], t.grad) < 2e-2, (name, rel_err(dqkv[i], t.grad))
