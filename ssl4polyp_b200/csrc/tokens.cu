@@ -194,14 +194,20 @@ __global__ void mask_token_grad_partial_kernel(const float* __restrict__ dx, con
                                                int NL, int L, int D) {
     const int d = blockIdx.y * blockDim.x + threadIdx.x;
     if (d >= D) return;
-    float acc = 0.f;
-    for (int r = blockIdx.x; r < NL; r += gridDim.x) {
-        if (mask[r] != 0.f) {
-            const int n = r / L, i = r % L;
-            acc += dx[((size_t)n * (1 + L) + 1 + i) * D + d];
+    // four independent accumulators (rows r, r+G, r+2G, r+3G of a round): the loads of a round are in flight together
+    float acc[4] = {0.f, 0.f, 0.f, 0.f};
+    const int G = gridDim.x;
+    for (int r0 = blockIdx.x; r0 < NL; r0 += 4 * G) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const int r = r0 + k * G;
+            if (r < NL && mask[r] != 0.f) {
+                const int n = r / L, i = r % L;
+                acc[k] += dx[((size_t)n * (1 + L) + 1 + i) * D + d];
+            }
         }
     }
-    part[(size_t)blockIdx.x * D + d] = acc;
+    part[(size_t)blockIdx.x * D + d] = (acc[0] + acc[1]) + (acc[2] + acc[3]);
 }
 __global__ void reduce_rows_kernel(const float* __restrict__ part, int G, int D, float* __restrict__ out, int accumulate) {
     const int d = blockIdx.x * blockDim.x + threadIdx.x;
@@ -387,9 +393,10 @@ extern "C" int ssl4p_decoder_unshuffle_fwd(const void* y, const float* mask_toke
     return check_launch("decoder_unshuffle_fwd_kernel");
 }
 
+constexpr int kMaskTokenGroups = 1184;         // stage-1 blocks of dmask_token (8 per SM: 42 rows each at B = 256)
 extern "C" size_t ssl4p_decoder_unshuffle_bwd_workspace_bytes(int N, int L, int Dd) {
     (void)N; (void)L;
-    return (size_t)256 * Dd * sizeof(float);
+    return (size_t)(kMaskTokenGroups + 32) * Dd * sizeof(float);
 }
 extern "C" int ssl4p_decoder_unshuffle_bwd(const float* dx, const int64_t* ids_keep, const float* mask, void* dy, float* dmask_token,
                                            int N, int Te, int L, int Dd, int accumulate, void* workspace, size_t workspace_bytes, void* stream) {
@@ -399,12 +406,19 @@ extern "C" int ssl4p_decoder_unshuffle_bwd(const float* dx, const int64_t* ids_k
     decoder_unshuffle_bwd_kernel<<<N * Te, 128, 0, STREAM>>>(dx, ids_keep, (__nv_bfloat16*)dy, Te, L, Dd / 4);
     int rc = check_launch("decoder_unshuffle_bwd_kernel");
     if (rc) return rc;
-    const int G = 256;
+    const int G = kMaskTokenGroups;
     dim3 grid(G, (Dd + 127) / 128);
-    mask_token_grad_partial_kernel<<<grid, 128, 0, STREAM>>>(dx, mask, (float*)workspace, N * L, L, Dd);
+    float* part = (float*)workspace;
+    mask_token_grad_partial_kernel<<<grid, 128, 0, STREAM>>>(dx, mask, part, N * L, L, Dd);
     rc = check_launch("mask_token_grad_partial_kernel");
     if (rc) return rc;
-    reduce_rows_kernel<<<(Dd + 127) / 128, 128, 0, STREAM>>>((const float*)workspace, G, Dd, dmask_token, accumulate);
+    const int rows_per_slab = (G + 31) / 32;                   // two fixed-order stages: 1184 -> 32 -> 1 rows
+    const int S = (G + rows_per_slab - 1) / rows_per_slab;
+    float* part2 = part + (size_t)G * Dd;
+    reduce_rows_slab_kernel<<<dim3((Dd + 127) / 128, S), 128, 0, STREAM>>>(part, G, Dd, rows_per_slab, part2);
+    rc = check_launch("reduce_rows_slab_kernel");
+    if (rc) return rc;
+    reduce_rows_kernel<<<(Dd + 127) / 128, 128, 0, STREAM>>>(part2, S, Dd, dmask_token, accumulate);
     return check_launch("reduce_rows_kernel");
 }
 
