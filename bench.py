@@ -349,8 +349,8 @@ def b200_arm(args):
     f_step = WORKLOADS[head][1]
     step_tflops = f_step * 1e9 * B / (ms_per_step / 1e3) / 1e12
     roofline = {"bound": "tensor", "kernel": "gemm_tcgen05_kernel", "achieved": achieved, "peak": pk["tflops_sustained"],
-                "unit": "TFLOP/s", "frac": achieved / pk["tflops_sustained"], "traffic": gemm_traffic(args.model, B),
-                "traffic_source": "profiles/*_gemm_traffic.json (committed ncu capture of this workload; not re-measured by this run)",
+                "unit": "TFLOP/s", "frac": achieved / pk["tflops_sustained"], "traffic": gemm_traffic(args.model, B)[0],
+                "traffic_source": f"profiles/{gemm_traffic(args.model, B)[1]} (committed ncu capture of this workload: dram__bytes_read.sum + dram__bytes_write.sum averaged over the GEMM launches of one step; not re-measured by this run)",
                 "peak_source": f"{pk['source']} (bf16 sustained; burst {pk['tflops_burst']})",
                 "gemm_launches_per_step": len(prof), "gemm_ms_per_step": g_ms, "gemm_share_of_step": g_ms / ms_per_step,
                 "step_tflops_per_gpu": step_tflops, "step_frac_of_peak": step_tflops / pk["tflops_sustained"]}
@@ -418,13 +418,13 @@ def gemm_traffic(model: str, batch: int):
     """DRAM bytes per gemm_tcgen05_kernel launch (read + write, average over the launches of one step) from the committed
     ncu capture of this workload (profiles/r01l_gemm_traffic.{csv,json}); null for a workload that was not captured."""
     if model != "base" or batch != 256:
-        return None
+        return None, None
     for name in ("r02_gemm_traffic.json", "r01l_gemm_traffic.json"):
         path = os.path.join(ROOT, "profiles", name)
         if os.path.exists(path):
             with open(path) as f:
-                return json.load(f)["traffic_per_launch"]
-    return None
+                return json.load(f)["traffic_per_launch"], name
+    return None, None
 
 
 def main():

@@ -59,6 +59,12 @@ int ssl4p_gemm_bf16(const void* A, const void* B, void* C, void* C2, const float
  * staging its 128 rows of A and half of B.  ssl4p_gemm_set_cta_group sets the process-wide policy (0 = per shape,
  * 1 = never, 2 = wherever M > 128) and returns the previous one; the environment variable SSL4P_GEMM_CG seeds it. */
 int ssl4p_gemm_set_cta_group(int mode);
+/* Dynamic tile scheduling for the persistent GEMM grids: hand the library a ZERO-INITIALISED device buffer (32-byte aligned,
+ * 32 bytes per launch slot; 2 MB is plenty) that stays alive as long as GEMMs are launched on the current device; NULL
+ * switches back to static tile lists (the default).  With it a CTA takes its tiles off a per-launch counter, so a CTA that
+ * is placed late - the SMs it needs are held by the NCCL kernels of the overlapped gradient all-reduce - finds the queue
+ * drained and exits instead of running its whole share as a second wave.  Results do not depend on the setting. */
+int ssl4p_gemm_set_scheduler_buffer(void* zeroed_device_buffer, size_t bytes);
 int ssl4p_gemm_pick_splits(int M, int N, int K);
 size_t ssl4p_gemm_workspace_bytes(int M, int N, int K, int layout, int epilogue);
 /* out[j] (+)= sum_g part[g*N + j], g < G  (two fixed-order stages: deterministic); workspace >= 32*N floats */

@@ -126,28 +126,31 @@ __device__ __forceinline__ f32x2 f2_add(f32x2 a, f32x2 b) { f32x2 d; asm("add.rn
 __device__ __forceinline__ f32x2 f2_splat(float v) { return f2_pack(v, v); }
 
 // The same GELU / GELU' for two elements at once: the polynomial, the products and the final combinations run on
-// FFMA2 (13 packed issue slots per pair instead of 2 x 16 scalar ones); rcp / ex2 / |x| / copysign stay scalar.
+// FFMA2 (12 packed issue slots per pair instead of 2 x 16 scalar ones); rcp / ex2 / copysign stay scalar.
+// Folded constants: e' = phi(x) = exp(-x^2/2) / sqrt(2 pi) comes straight out of ex2 (the log2 of the factor rides on the
+// FFMA that scales x^2), and the polynomial carries -sqrt(2 pi) / 2, so that  s = 0.5 erf(|x|/sqrt 2) = 0.5 + (P(t) t) e'.
 __device__ __forceinline__ void gelu_and_grad_f2(float x0, float x1, float& g0, float& g1, float& d0, float& d1) {
+    constexpr float kA = -1.2533141373155003f;            // -sqrt(2 pi) / 2
     const f32x2 x = f2_pack(x0, x1);
     const f32x2 ax = f2_pack(fabsf(x0), fabsf(x1));
     float u0, u1, t0, t1, e0, e1, q0, q1;
     f2_unpack(f2_fma(ax, f2_splat(0.3275911f * 0.70710678118654752f), f2_splat(1.0f)), u0, u1);
-    f2_unpack(f2_mul(f2_mul(x, x), f2_splat(-0.72134752044448170f)), q0, q1);
+    f2_unpack(f2_fma(f2_mul(x, x), f2_splat(-0.72134752044448170f), f2_splat(-1.3257480647361593f)), q0, q1);   // log2(1/sqrt(2 pi))
     asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t0) : "f"(u0));
     asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t1) : "f"(u1));
     asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e0) : "f"(q0));
     asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e1) : "f"(q1));
-    const f32x2 t = f2_pack(t0, t1), e = f2_pack(e0, e1);
-    f32x2 poly = f2_fma(t, f2_splat(1.061405429f), f2_splat(-1.453152027f));
-    poly = f2_fma(poly, t, f2_splat(1.421413741f));
-    poly = f2_fma(poly, t, f2_splat(-0.284496736f));
-    poly = f2_fma(poly, t, f2_splat(0.254829592f));
-    const f32x2 erf_abs = f2_fma(f2_mul(poly, t), f2_mul(e, f2_splat(-1.0f)), f2_splat(1.0f));   // erf(|x|/sqrt 2)
+    const f32x2 t = f2_pack(t0, t1), e = f2_pack(e0, e1);  // e = phi(x)
+    f32x2 poly = f2_fma(t, f2_splat(kA * 1.061405429f), f2_splat(kA * -1.453152027f));
+    poly = f2_fma(poly, t, f2_splat(kA * 1.421413741f));
+    poly = f2_fma(poly, t, f2_splat(kA * -0.284496736f));
+    poly = f2_fma(poly, t, f2_splat(kA * 0.254829592f));
+    const f32x2 half_erf = f2_fma(f2_mul(poly, t), e, f2_splat(0.5f));                            // 0.5 erf(|x|/sqrt 2)
     float a0, a1;
-    f2_unpack(erf_abs, a0, a1);
-    const f32x2 cdf = f2_fma(f2_pack(copysignf(a0, x0), copysignf(a1, x1)), f2_splat(0.5f), f2_splat(0.5f));
+    f2_unpack(half_erf, a0, a1);
+    const f32x2 cdf = f2_add(f2_pack(copysignf(a0, x0), copysignf(a1, x1)), f2_splat(0.5f));     // Phi(x)
     f2_unpack(f2_mul(x, cdf), g0, g1);
-    f2_unpack(f2_fma(f2_mul(x, e), f2_splat(0.3989422804014327f), cdf), d0, d1);
+    f2_unpack(f2_fma(x, e, cdf), d0, d1);                                                         // Phi(x) + x phi(x)
 }
 
 // ---- explicit state-space accesses: a pointer computed from the dynamic shared-memory base or taken out of a
@@ -272,6 +275,20 @@ __device__ __forceinline__ uint32_t mapa_u32(uint32_t smem_addr, uint32_t rank) 
 }
 __device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
     asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
+// wait with cluster-scope acquire: pairs with a remote mbar_arrive_cluster (release.cluster) that publishes remote stores
+__device__ __forceinline__ void mbar_wait_cluster(uint64_t* bar, uint32_t parity) {
+    uint32_t ok;
+    do {
+        asm volatile(
+            "{\n\t.reg .pred P;\n\t"
+            "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 P, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, P;\n\t}\n"
+            : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+    } while (!ok);
+}
+__device__ __forceinline__ void st_cluster_u32(uint32_t cluster_addr, uint32_t v) {
+    asm volatile("st.shared::cluster.u32 [%0], %1;" ::"r"(cluster_addr), "r"(v) : "memory");
 }
 // 2-D tiled load into THIS CTA's shared memory whose completion bytes are counted on a barrier that may live in the
 // peer CTA (bar_cluster_addr: a shared::cluster address, e.g. the leader's full barrier)

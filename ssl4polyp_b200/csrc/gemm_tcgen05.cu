@@ -45,6 +45,7 @@ struct GemmParams {
     const float* bias;           // [N] or null
     const void* aux;             // residual (fp32 [M,ldaux]) or pre-activation (bf16 [M,ldaux])
     long long split_stride;      // elements between split-K partial planes of C
+    int* sched;                  // dynamic tile scheduler slot {next tile, finished units} (zero between launches) or null = static
 };
 
 template <int BN, bool A_MN, bool B_MN, int EPI, int CG>
@@ -171,7 +172,10 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, uint32_t stg
         for (int i = 0; i < 4; ++i) {
             const int row = row_base + 8 * i + (lane >> 2);
             const float4 lo = t[2 * i], hi = t[2 * i + 1];
-            float v[8] = {lo.x + b0.x, lo.y + b0.y, lo.z + b0.z, lo.w + b0.w, hi.x + b1.x, hi.y + b1.y, hi.z + b1.z, hi.w + b1.w};
+            float v[8] = {lo.x, lo.y, lo.z, lo.w, hi.x, hi.y, hi.z, hi.w};
+            if constexpr (kHasBias) {                              // (x + 0.0f is not a no-op for the compiler: -0.0f)
+                v[0] += b0.x; v[1] += b0.y; v[2] += b0.z; v[3] += b0.w; v[4] += b1.x; v[5] += b1.y; v[6] += b1.z; v[7] += b1.w;
+            }
             if constexpr (EPI == SSL4P_EPI_DGELU_BF16) {
                 const uint32_t hw[4] = {aux.v[i].x, aux.v[i].y, aux.v[i].z, aux.v[i].w};
 #pragma unroll
@@ -280,6 +284,15 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     uint64_t* tmem_full = bars + 2 * kStages;                // [2]
     uint64_t* tmem_empty = bars + 2 * kStages + 2;           // [2]
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * kStages + 4);
+    // Tile queue: ONE thread per unit (the producer of the CTA / of the pair's leader) takes tiles off a global counter and
+    // hands them to every other role through this ring.  A persistent grid with a static tile list stalls whenever some of
+    // its CTAs cannot be placed - the NCCL all-reduce kernels of the overlapped gradient exchange hold SMs for ~150 us and a
+    // CTA that needs a whole SM's shared memory cannot share one with them: the late CTAs then run their full share as a
+    // second wave.  With the counter a late CTA finds the queue drained and leaves at once.
+    constexpr int kTQ = 4;
+    uint64_t* tq_full = bars + 2 * kStages + 5;              // [kTQ]
+    uint64_t* tq_empty = bars + 2 * kStages + 5 + kTQ;       // [kTQ] (CG = 2: the leader's copy is the one in use)
+    volatile int* tq_tile = reinterpret_cast<volatile int*>(bars + 2 * kStages + 5 + 2 * kTQ);   // [kTQ]
     uint8_t* epi_stage = smem + kStages * L::kStageBytes + L::kBarBytes;   // kEpiWarps x 4 KB
 
     const int warp = threadIdx.x >> 5;
@@ -292,14 +305,20 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     const int unit = CG == 2 ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;       // tile-processing unit (CTA or CTA pair)
     const int nunits = CG == 2 ? (int)(gridDim.x >> 1) : (int)gridDim.x;
 
+    int first_tile = unit;                                    // scheduler thread only
     if (warp == 0 && lane_id() == 0) {
         tma_prefetch_desc(&tmA);
         tma_prefetch_desc(&tmB);
+        // the first tile comes off the counter too (a CTA that starts late must not own any tile); the round trip hides
+        // behind the barrier initialisation and the TMEM allocation below
+        if (p.sched != nullptr && rank == 0) first_tile = atomicAdd(p.sched, 1);
     }
     if (warp == 1) {
         if (lane_id() == 0) {
             for (int i = 0; i < kStages; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], 1); }
             for (int i = 0; i < 2; ++i) { mbar_init(&tmem_full[i], 1); mbar_init(&tmem_empty[i], kEpiWarps * CG); }
+            // consumers of a queue slot: the MMA warp and the epilogue warps (CG = 2: of both CTAs, plus the peer's producer)
+            for (int i = 0; i < kTQ; ++i) { mbar_init(&tq_full[i], 1); mbar_init(&tq_empty[i], CG == 2 ? 2 + 2 * kEpiWarps : 1 + kEpiWarps); }
             mbar_fence_init();
             fence_proxy_async();
         }
@@ -312,8 +331,22 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     const uint32_t tmem_base = *tmem_slot;
     pdl_wait_then_trigger();                                  // everything above overlapped the previous kernel's tail
 
+    // next tile of this unit for a consumer role (-1 = no more); `single`: called by one thread instead of a whole warp
+    int tq_slot = 0; uint32_t tq_phase = 0;
+    auto next_tile = [&](bool single) -> int {
+        if (CG == 2 && rank != 0) mbar_wait_cluster(&tq_full[tq_slot], tq_phase); else mbar_wait(&tq_full[tq_slot], tq_phase);
+        const int t = tq_tile[tq_slot];
+        if (!single) __syncwarp();
+        if (single || lane_id() == 0) {
+            if constexpr (CG == 2) mbar_arrive_cluster(mapa_u32(smem_u32(&tq_empty[tq_slot]), 0));
+            else mbar_arrive(&tq_empty[tq_slot]);
+        }
+        if (++tq_slot == kTQ) { tq_slot = 0; tq_phase ^= 1; }
+        return t;
+    };
+
     if (warp == 0) {
-        // ===================== TMA producer =====================
+        // ===================== TMA producer (and, in the unit's leader CTA, the tile scheduler) =====================
         if (lane_id() == 0) {
             int stage = 0; uint32_t phase = 0;
             // the barrier that counts this CTA's bytes: its own (CG = 1) or the leader's (CG = 2)
@@ -321,7 +354,28 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                 if constexpr (CG == 2) tma_load_2d_cg2(dst, m, mapa_u32(smem_u32(&full_bar[st]), 0), c0, c1);
                 else tma_load_2d(dst, m, &full_bar[st], c0, c1);
             };
-            for (int tile = unit; tile < total_tiles; tile += nunits) {
+            const bool scheduler = CG == 1 || rank == 0;
+            int tile = first_tile;
+            while (true) {
+                int next = 0;
+                if (scheduler) {
+                    const int pub = tile < total_tiles ? tile : -1;
+                    // every consumer (of both CTAs) has read the slot's last tile
+                    if constexpr (CG == 2) mbar_wait_cluster(&tq_empty[tq_slot], tq_phase ^ 1); else mbar_wait(&tq_empty[tq_slot], tq_phase ^ 1);
+                    tq_tile[tq_slot] = pub;
+                    if constexpr (CG == 2) {
+                        st_cluster_u32(mapa_u32(smem_u32(const_cast<int*>(&tq_tile[tq_slot])), 1), (uint32_t)pub);
+                        mbar_arrive_cluster(mapa_u32(smem_u32(&tq_full[tq_slot]), 1));
+                    }
+                    mbar_arrive(&tq_full[tq_slot]);
+                    if (++tq_slot == kTQ) { tq_slot = 0; tq_phase ^= 1; }
+                    if (pub < 0) break;
+                    // the tile after this one: requested now, needed after this tile's loads
+                    next = p.sched != nullptr ? atomicAdd(p.sched, 1) : tile + nunits;
+                } else {
+                    tile = next_tile(true);
+                    if (tile < 0) break;
+                }
                 const int split = tile / tiles_mn;
                 const int t = tile - split * tiles_mn;
                 const int m0 = (t / nt) * TM + (int)rank * BM;                         // this CTA's A rows
@@ -349,6 +403,13 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                     }
                     if (++stage == kStages) { stage = 0; phase ^= 1; }
                 }
+                tile = next;
+            }
+            if (scheduler && p.sched != nullptr) {
+                // the unit that finishes last puts the slot back to zero for the next launch (every other unit has made its
+                // final request by then)
+                __threadfence();
+                if (atomicAdd(p.sched + 1, 1) == nunits - 1) { atomicExch(p.sched, 0); atomicExch(p.sched + 1, 0); }
             }
         }
         __syncwarp();
@@ -365,7 +426,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         const bool leader = lane_id() == 0;     // tcgen05.commit tracks the issuing thread: one fixed lane issues all
         int stage = 0; uint32_t phase = 0;
         int acc = 0; uint32_t acc_phase = 0;
-        for (int tile = unit; tile < total_tiles; tile += nunits) {
+        while (true) {
+            const int tile = next_tile(false);
+            if (tile < 0) break;
             const int split = tile / tiles_mn;
             const int k_begin = split * p.k_per_split;
             const int k_end = min(p.K, k_begin + p.k_per_split);
@@ -405,7 +468,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         const int q = warp & 3;                                       // TMEM lane quarter this warp may access
         const int chunk0 = ((warp - 2) >> 2) * 32;                    // the quarter's two warps interleave 32-column chunks
         int acc = 0; uint32_t acc_phase = 0;
-        for (int tile = unit; tile < total_tiles; tile += nunits) {
+        while (true) {
+            const int tile = next_tile(false);
+            if (tile < 0) break;
             const int split = tile / tiles_mn;
             const int t = tile - split * tiles_mn;
             const int m0 = (t / nt) * TM + (int)rank * BM, n0 = (t % nt) * BN;
@@ -591,6 +656,34 @@ static int dispatch(int layout, int epi, const CUtensorMap& a, const CUtensorMap
     return SSL4P_ERR_UNSUPPORTED;
 }
 
+// ---- dynamic tile scheduler slots (ssl4p_gemm_set_scheduler_buffer) ---------------------------------------------------
+// A caller-owned, zero-initialised device buffer of 32-byte slots; every launch takes one ({next tile, finished units}, put
+// back to zero by the kernel itself).  Launches recorded into a CUDA graph keep their slot for the life of the graph, so
+// they draw from the first half of the buffer and never hand a slot out twice (exhausted -> static tile lists); eager
+// launches rotate through the second half.
+struct SchedBuffer { int* base = nullptr; long long slots = 0; int device = -1; long long captured = 0; long long eager = 0; };
+static SchedBuffer g_sched;
+static std::mutex g_sched_mutex;
+constexpr int kSchedSlotInts = 8;
+
+static int* take_sched_slot(cudaStream_t stream) {
+    std::lock_guard<std::mutex> lock(g_sched_mutex);
+    if (g_sched.base == nullptr || g_sched.slots < 2) return nullptr;
+    int dev = -1;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev != g_sched.device) return nullptr;
+    cudaStreamCaptureStatus st = cudaStreamCaptureStatusNone;
+    if (cudaStreamIsCapturing(stream, &st) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    const long long half = g_sched.slots / 2;
+    long long idx;
+    if (st == cudaStreamCaptureStatusActive) {
+        if (g_sched.captured >= half) return nullptr;
+        idx = g_sched.captured++;
+    } else {
+        idx = half + (g_sched.eager++ % (g_sched.slots - half));
+    }
+    return g_sched.base + idx * kSchedSlotInts;
+}
+
 // 0 = choose per shape, 1 = cta_group::1 only, 2 = the CTA pair wherever the shape allows it
 // (ssl4p_gemm_set_cta_group; initial value from the environment variable SSL4P_GEMM_CG)
 static int& cta_group_mode() {
@@ -650,6 +743,18 @@ extern "C" size_t ssl4p_gemm_workspace_bytes(int M, int N, int K, int layout, in
     return (size_t)SSL4P_MAX_SPLITS * (size_t)M * (size_t)N * sizeof(float);
 }
 
+extern "C" int ssl4p_gemm_set_scheduler_buffer(void* zeroed_device_buffer, size_t bytes) {
+    std::lock_guard<std::mutex> lock(g_sched_mutex);
+    if (zeroed_device_buffer == nullptr || bytes < 2 * kSchedSlotInts * sizeof(int)) { g_sched = SchedBuffer(); return SSL4P_OK; }
+    SSL4P_REQUIRE((reinterpret_cast<uintptr_t>(zeroed_device_buffer) & 31) == 0, "gemm scheduler buffer must be 32-byte aligned");
+    int dev = -1;
+    SSL4P_CUDA(cudaGetDevice(&dev));
+    g_sched.base = (int*)zeroed_device_buffer;
+    g_sched.slots = (long long)(bytes / (kSchedSlotInts * sizeof(int)));
+    g_sched.device = dev; g_sched.captured = 0; g_sched.eager = 0;
+    return SSL4P_OK;
+}
+
 extern "C" int ssl4p_gemm_set_cta_group(int mode) {
     const int prev = cta_group_mode();
     if (mode >= 0 && mode <= 2) cta_group_mode() = mode;
@@ -706,6 +811,7 @@ extern "C" int ssl4p_gemm_bf16(const void* A, const void* B, void* C, void* C2, 
     p.k_per_split = ((kb + splits - 1) / splits) * BK;
     p.C = C; p.C2 = C2; p.bias = bias; p.aux = aux;
     p.split_stride = (long long)M * ldc;
+    p.sched = take_sched_slot(stream);
 
     CUtensorMap tmA, tmB;
     int rc;

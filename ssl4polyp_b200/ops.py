@@ -4,6 +4,8 @@ missing library raises.
 """
 from __future__ import annotations
 
+import os
+
 import torch
 
 from . import _lib
@@ -59,7 +61,25 @@ def workspace(nbytes: int, device, tag: str = "ws") -> torch.Tensor:
 GEMM_PROFILE = None      # bench.py sets this to a list to time every GEMM launch with CUDA events (roofline leg)
 
 
+_sched_buffers: dict = {}
+
+
+def _ensure_gemm_scheduler(lib) -> None:
+    """Once per process: hand the library the zeroed device buffer its dynamic tile scheduler draws launch slots from
+    (include/ssl4p.h: ssl4p_gemm_set_scheduler_buffer).  SSL4P_GEMM_SCHED=0 keeps the static tile lists."""
+    dev = torch.cuda.current_device()
+    if dev in _sched_buffers:
+        return
+    if os.environ.get("SSL4P_GEMM_SCHED", "1") == "0" or _sched_buffers:      # the library keeps one buffer (one device per process)
+        _sched_buffers[dev] = None
+        return
+    buf = torch.zeros(2 << 20, dtype=torch.uint8, device=torch.device("cuda", dev))
+    _lib.check(lib.ssl4p_gemm_set_scheduler_buffer(buf.data_ptr(), buf.numel()), "gemm_set_scheduler_buffer")
+    _sched_buffers[dev] = buf
+
+
 def _gemm_launch(lib, M, N, K, layout, epilogue, *args):
+    _ensure_gemm_scheduler(lib)
     if GEMM_PROFILE is None:
         return lib.ssl4p_gemm_bf16(*args)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
