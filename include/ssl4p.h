@@ -59,6 +59,8 @@ int ssl4p_gemm_bf16(const void* A, const void* B, void* C, void* C2, const float
  * staging its 128 rows of A and half of B.  ssl4p_gemm_set_cta_group sets the process-wide policy (0 = per shape,
  * 1 = never, 2 = wherever M > 128) and returns the previous one; the environment variable SSL4P_GEMM_CG seeds it. */
 int ssl4p_gemm_set_cta_group(int mode);
+/* CTA pairs the device can keep resident at once (cudaOccupancyMaxActiveClusters, known after the first pair launch; 0 before) */
+int ssl4p_gemm_max_cta_pairs(void);
 /* Dynamic tile scheduling for the persistent GEMM grids: hand the library a ZERO-INITIALISED device buffer (32-byte aligned,
  * 32 bytes per launch slot; 2 MB is plenty) that stays alive as long as GEMMs are launched on the current device; NULL
  * switches back to static tile lists (the default).  With it a CTA takes its tiles off a per-launch counter, so a CTA that

@@ -11,7 +11,12 @@ dev = torch.device("cuda:0")
 flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
 Me, Md = 256 * 50, 256 * 197
 cases = []
-for tag, M, D in (("enc", Me, 768), ("dec", Md, 512)):
+groups = (("enc", Me, 768), ("dec", Md, 512))
+if os.environ.get("GEMM_CASES") == "cls":          # the classifier fine-tune step: 128 images x 197 tokens, D = 768
+    groups = (("enc", 128 * 197, 768),)
+if os.environ.get("GEMM_CASES") == "large":        # ViT-L/16 pretraining: encoder D = 1024, decoder D = 512
+    groups = (("enc", Me, 1024), ("dec", Md, 512))
+for tag, M, D in groups:
     cases += [(f"{tag} qkv   NT bias", GEMM_NT, EPI_BIAS_BF16, M, 3 * D, D),
               (f"{tag} proj  NT resid", GEMM_NT, EPI_BIAS_RESIDUAL_F32, M, D, D),
               (f"{tag} fc1   NT gelu", GEMM_NT, EPI_BIAS_GELU_BF16, M, 4 * D, D),
@@ -24,7 +29,8 @@ for tag, M, D in (("enc", Me, 768), ("dec", Md, 512)):
               (f"{tag} wfc2  TN", GEMM_TN, EPI_PARTIAL_F32, D, 4 * D, M),
               (f"{tag} wqkv  TN", GEMM_TN, EPI_PARTIAL_F32, 3 * D, D, M),
               (f"{tag} wproj TN", GEMM_TN, EPI_PARTIAL_F32, D, D, M)]
-cases.append(("dec pred  NT f32", GEMM_NT, EPI_BIAS_F32, Md, 768, 512))
+if os.environ.get("GEMM_CASES") != "cls":
+    cases.append(("dec pred  NT f32", GEMM_NT, EPI_BIAS_F32, Md, 768, 512))
 tot = 0.0
 totals = {}
 only = os.environ.get("GEMM_ONLY")          # e.g. GEMM_ONLY="dec fc1,dec dfc2" (ncu captures)
@@ -69,5 +75,7 @@ for name, layout, epi, M, N, K in cases:
         tot += t * n_per_step
         totals[force_bn] = totals.get(force_bn, 0.0) + t * n_per_step
         print(f"{name:18s} cg={force_bn >> 16} bn={force_bn & 0xffff:3d} M={M:6d} N={N:5d} K={K:6d} s={splits:2d}  {t:8.1f} us  {2.0 * M * N * K / t / 1e6:7.1f} TF/s  {byt / t / 1e3:6.0f} GB/s   x{n_per_step}")
+from ssl4polyp_b200 import _lib as _L
+print("max resident CTA pairs:", _L.load().ssl4p_gemm_max_cta_pairs(), "SMs:", torch.cuda.get_device_properties(0).multi_processor_count)
 for k, v in totals.items():
     print(f"sum over the step's block GEMMs (cg={k >> 16} bn={k & 0xffff}): {v / 1e3:.2f} ms")

@@ -22,6 +22,7 @@ SIGNATURES = {
     "ssl4p_launch_count": (C.c_ulonglong, []),
     "ssl4p_gemm_bf16": (i32, [vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, i32, i32, i32, i32, vp]),
     "ssl4p_gemm_set_cta_group": (i32, [i32]),
+    "ssl4p_gemm_max_cta_pairs": (i32, []),
     "ssl4p_gemm_set_scheduler_buffer": (i32, [vp, sz]),
     "ssl4p_gemm_pick_splits": (i32, [i32, i32, i32]),
     "ssl4p_gemm_workspace_bytes": (sz, [i32, i32, i32, i32, i32]),

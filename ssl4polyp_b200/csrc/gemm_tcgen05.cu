@@ -355,22 +355,29 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                 else tma_load_2d(dst, m, &full_bar[st], c0, c1);
             };
             const bool scheduler = CG == 1 || rank == 0;
+            // scheduler: the request for tile i+1 goes out before the loads of tile i and its answer is published from
+            // INSIDE that tile's k loop (after the third k-block), never at the tile boundary: the peer CTA's producer needs
+            // the index the moment the leader's producer turns to the next tile (a hand-off at the boundary cost ~0.5 us per
+            // tile).  One tile of look-ahead only: a unit that asked for two tiles up front would starve its neighbours in
+            // the one-wave split-K launches.
+            auto publish = [&](int t) {
+                const int pub = t < total_tiles ? t : -1;
+                // every consumer (of both CTAs) has read the slot's last tile
+                if constexpr (CG == 2) mbar_wait_cluster(&tq_empty[tq_slot], tq_phase ^ 1); else mbar_wait(&tq_empty[tq_slot], tq_phase ^ 1);
+                tq_tile[tq_slot] = pub;
+                if constexpr (CG == 2) {
+                    st_cluster_u32(mapa_u32(smem_u32(const_cast<int*>(&tq_tile[tq_slot])), 1), (uint32_t)pub);
+                    mbar_arrive_cluster(mapa_u32(smem_u32(&tq_full[tq_slot]), 1));
+                }
+                mbar_arrive(&tq_full[tq_slot]);
+                if (++tq_slot == kTQ) { tq_slot = 0; tq_phase ^= 1; }
+            };
             int tile = first_tile;
+            if (scheduler) publish(tile);
             while (true) {
                 int next = 0;
                 if (scheduler) {
-                    const int pub = tile < total_tiles ? tile : -1;
-                    // every consumer (of both CTAs) has read the slot's last tile
-                    if constexpr (CG == 2) mbar_wait_cluster(&tq_empty[tq_slot], tq_phase ^ 1); else mbar_wait(&tq_empty[tq_slot], tq_phase ^ 1);
-                    tq_tile[tq_slot] = pub;
-                    if constexpr (CG == 2) {
-                        st_cluster_u32(mapa_u32(smem_u32(const_cast<int*>(&tq_tile[tq_slot])), 1), (uint32_t)pub);
-                        mbar_arrive_cluster(mapa_u32(smem_u32(&tq_full[tq_slot]), 1));
-                    }
-                    mbar_arrive(&tq_full[tq_slot]);
-                    if (++tq_slot == kTQ) { tq_slot = 0; tq_phase ^= 1; }
-                    if (pub < 0) break;
-                    // the tile after this one: requested now, needed after this tile's loads
+                    if (tile >= total_tiles) break;
                     next = p.sched != nullptr ? atomicAdd(p.sched, 1) : tile + nunits;
                 } else {
                     tile = next_tile(true);
@@ -382,6 +389,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                 const int n0 = (t % nt) * BN + (int)rank * L::kBRows;                  // this CTA's share of B
                 const int k_begin = split * p.k_per_split;
                 const int k_end = min(p.K, k_begin + p.k_per_split);
+                const int k_pub = min(k_begin + 2 * BK, k_end - BK);                   // k-block after which `next` is published
+                bool published = !scheduler;
                 for (int k = k_begin; k < k_end; k += BK) {
                     mbar_wait(&empty_bar[stage], phase ^ 1);
                     if (CG == 1 || rank == 0) mbar_expect_tx(&full_bar[stage], L::kStageBytes * CG);   // both CTAs' bytes
@@ -402,7 +411,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                             load(sb + c * (BK * 128), &tmB, stage, n0 + c * 64, k);
                     }
                     if (++stage == kStages) { stage = 0; phase ^= 1; }
+                    if (!published && k >= k_pub) { publish(next); published = true; }
                 }
+                if (!published) publish(next);                                        // (empty split-K range)
                 tile = next;
             }
             if (scheduler && p.sched != nullptr) {
@@ -614,6 +625,15 @@ static int make_tmap_out(CUtensorMap* out, void* ptr, long long cols, long long 
     return SSL4P_OK;
 }
 
+// CTA pairs that can be resident at once (cudaOccupancyMaxActiveClusters of the first pair kernel launched; 0 = not queried
+// yet).  Not every board places 74 two-CTA clusters: SM harvesting can leave TPCs with a single SM.
+static int g_max_pairs = 0;
+static int pair_units() {
+    const int by_sms = num_sms() / 2;
+    return g_max_pairs > 0 && g_max_pairs < by_sms ? g_max_pairs : by_sms;
+}
+extern "C" int ssl4p_gemm_max_cta_pairs(void) { return g_max_pairs; }
+
 template <int BN, bool A_MN, bool B_MN, int EPI, int CG>
 static int launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC, const GemmParams& p, cudaStream_t stream) {
     using L = SmemLayout<BN, A_MN, B_MN, EPI, CG>;
@@ -623,9 +643,19 @@ static int launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensor
         SSL4P_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal));
         attr_set = true;
     }
+    if (CG == 2 && g_max_pairs == 0) {
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(2 * 74); cfg.blockDim = dim3((unsigned)gemm_threads(EPI)); cfg.dynamicSmemBytes = L::kTotal;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeClusterDimension;
+        attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+        cfg.attrs = attr; cfg.numAttrs = 1;
+        int n = 0;
+        if (cudaOccupancyMaxActiveClusters(&n, kern, &cfg) == cudaSuccess && n > 0) g_max_pairs = n; else { cudaGetLastError(); g_max_pairs = 1 << 20; }
+    }
     const int mt = (p.M + BM * CG - 1) / (BM * CG), nt = (p.N + BN - 1) / BN;
     const int total = mt * nt * p.splits;
-    const int units = num_sms() / CG;                          // CTAs or CTA pairs (one pair = the two SMs of a TPC)
+    const int units = CG == 2 ? pair_units() : num_sms();      // CTAs or CTA pairs (one pair = the two SMs of a TPC)
     const int grid = (total < units ? total : units) * CG;
     cudaError_t e = launch_ex(kern, dim3((unsigned)grid), dim3((unsigned)gemm_threads(EPI)), (size_t)L::kTotal, stream, CG, tmA, tmB, tmC, p);
     if (e != cudaSuccess) { set_error("gemm_tcgen05_kernel launch failed: %s", cudaGetErrorString(e)); return SSL4P_ERR_CUDA; }
@@ -696,15 +726,17 @@ static int& cta_group_mode() {
 // throughput of the configuration (smaller N tiles re-read A from shared memory per MMA; a CTA pair fills
 // (128 + bn/2) x 64 operands per k-block and SM instead of (128 + bn) x 64).
 // bn_fixed / cg_fixed != 0 restrict the search (force_bn of the C-ABI call).
-// Policy 0 (per shape): the pair pays where the main loop is the bound.  Measured on B200 (profiles/r02b_gemm_bench.txt):
-// long-K shapes gain 8-14 % (dec dfc1 1160 -> 1308 TF/s, wgrads 1087 -> 1244), while at K = 512..768 the tile time is the
-// epilogue's and coupling two epilogues to one accumulator hand-off loses 3-8 % (dec fc1 + GELU 132 -> 140 us).
-static bool pair_pays(int K, int epi) {
-    switch (epi) {
-        case SSL4P_EPI_PARTIAL_F32: return true;
-        case SSL4P_EPI_BIAS_BF16: case SSL4P_EPI_DGELU_BF16: return K >= 768;
-        default: return K >= 1024;                  // GELU, residual and fp32 outputs: heavier epilogues
-    }
+// Policy 0 (per shape): both groups go through the same wave-quantisation cost, the single-CTA tile scaled by its measured
+// throughput relative to the pair at equal quantisation (profiles/r02n_gemm_{mae,cls,large}.txt, one board, both groups back
+// to back): split-K wgrads 0.83-0.93 (-> 0.87), K >= 1536 0.93-0.95, K = 1024 about even, K <= 768 the pair LOSES 4-28 % (the
+// tile time is the epilogue's and two epilogues share one accumulator hand-off).  The quantisation term then decides cases
+// like the classifier's M = 25 216 (197 single-CTA row tiles x 3 = 3.99 waves of 148, but 99 pair tiles x 3 = 4.01 waves of
+// 74: the pair was 20-23 % slower there although K = 2304 / 3072).
+static double single_rate(int K, int epi) {
+    if (epi == SSL4P_EPI_PARTIAL_F32) return 0.87;
+    if (K >= 1536) return 0.93;
+    if (K >= 1024) return 0.98;
+    return 1.12;
 }
 
 static void pick_config(int M, int N, int K, int epi, int splits, int bn_fixed, int cg_fixed, int& bn_out, int& cg_out) {
@@ -712,20 +744,20 @@ static void pick_config(int M, int N, int K, int epi, int splits, int bn_fixed, 
     static const int cands[4] = {256, 192, 128, 64};
     static const double rate1[4] = {1.00, 0.95, 0.85, 0.60};
     static const double rate2[4] = {1.00, 0.95, 0.85, 0.0};
-    int mode = cg_fixed ? cg_fixed : cta_group_mode();
-    if (mode == 0) mode = pair_pays(K, epi) ? 2 : 1;
+    const int mode = cg_fixed ? cg_fixed : cta_group_mode();
     const bool pair_ok = M > BM && sms >= 2 && bn_fixed != 64;
+    const double r1 = single_rate(K, epi);
     double best_cost = 1e30;
     bn_out = bn_fixed ? bn_fixed : 128; cg_out = 1;
     for (int cg = 1; cg <= 2; ++cg) {
         if (cg == 2 && (mode == 1 || !pair_ok)) continue;
         if (cg == 1 && mode == 2 && pair_ok) continue;
         for (int i = 0; i < 4; ++i) {
-            const double rate = cg == 2 ? rate2[i] : rate1[i];
+            const double rate = cg == 2 ? rate2[i] : rate1[i] * r1;
             const int bn = cands[i];
             if (rate <= 0.0 || (bn_fixed && bn != bn_fixed)) continue;
             const long long tiles = (long long)((M + BM * cg - 1) / (BM * cg)) * ((N + bn - 1) / bn) * splits;
-            const long long units = sms / cg;
+            const long long units = cg == 2 ? pair_units() : sms;
             const long long waves = (tiles + units - 1) / units;
             const double cost = (double)waves * (bn / rate + 24.0);
             if (cost < best_cost) { best_cost = cost; bn_out = bn; cg_out = cg; }
@@ -767,7 +799,7 @@ extern "C" int ssl4p_gemm_pick_splits(int M, int N, int K) {
     // each split keeps >= 4 K-blocks.
     // With the CTA pair the unit is a 256x256 tile on one of sms/2 pairs.
     const bool pair = cta_group_mode() != 1 && M > BM;
-    const int sms = pair ? num_sms() / 2 : num_sms();
+    const int sms = pair ? pair_units() : num_sms();
     const int tiles = ((M + (pair ? 2 * BM : BM) - 1) / (pair ? 2 * BM : BM)) * ((N + 255) / 256);
     int s = sms / tiles;
     const int kb = (K + BK - 1) / BK;

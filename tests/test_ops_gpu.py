@@ -164,6 +164,50 @@ def test_gemm_cta_group_policy_switch():
     assert torch.equal(o1, o2)
 
 
+def test_gemm_dynamic_tile_scheduler_slots_reset_themselves():
+    """ssl4p_gemm_set_scheduler_buffer: with a 4-slot buffer (2 for captured launches, 2 rotating for eager ones) every eager
+    slot is reused after two launches, so the results only stay right if each kernel puts its {next tile, finished units}
+    pair back to zero; static tile lists (NULL) give the same bits; a captured launch keeps its slot across replays."""
+    from ssl4polyp_b200 import ops, _lib
+    lib = _lib.load()
+    a = torch.randn(12800, 768, device=dev()).bfloat16()
+    w = (torch.randn(2304, 768, device=dev()) / 28).bfloat16()
+    dy = torch.randn(12800, 768, device=dev()).bfloat16()
+    ref = ops.gemm(a, w, ops.GEMM_NT, ops.EPI_BIAS_BF16)                  # whatever the process-wide setting is
+    ref_w = ops.gemm(dy, a, ops.GEMM_TN, ops.EPI_PARTIAL_F32, splits=ops.pick_splits(768, 768, 12800))
+    small = torch.zeros(4 * 32, dtype=torch.uint8, device=dev())
+    try:
+        _lib.check(lib.ssl4p_gemm_set_scheduler_buffer(small.data_ptr(), small.numel()), "set_scheduler_buffer")
+        for _ in range(7):
+            assert torch.equal(ops.gemm(a, w, ops.GEMM_NT, ops.EPI_BIAS_BF16), ref)
+            assert torch.equal(ops.gemm(dy, a, ops.GEMM_TN, ops.EPI_PARTIAL_F32, splits=ops.pick_splits(768, 768, 12800)), ref_w)
+        torch.cuda.synchronize()
+        assert int(small.view(torch.int32).abs().sum()) == 0               # every slot is back to zero
+        out = torch.empty_like(ref)
+        g = torch.cuda.CUDAGraph()
+        s = torch.cuda.Stream()
+        s.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(s):
+            ops.gemm(a, w, ops.GEMM_NT, ops.EPI_BIAS_BF16, out=out)       # warm-up outside the capture
+            with torch.cuda.graph(g, stream=s):
+                ops.gemm(a, w, ops.GEMM_NT, ops.EPI_BIAS_BF16, out=out)
+        torch.cuda.current_stream().wait_stream(s)
+        for _ in range(3):
+            out.zero_()
+            g.replay()
+            torch.cuda.synchronize()
+            assert torch.equal(out, ref)
+        _lib.check(lib.ssl4p_gemm_set_scheduler_buffer(None, 0), "set_scheduler_buffer")
+        assert torch.equal(ops.gemm(a, w, ops.GEMM_NT, ops.EPI_BIAS_BF16), ref)   # static tile lists
+    finally:
+        buf = ops._sched_buffers.get(torch.cuda.current_device())
+        if buf is not None:
+            lib.ssl4p_gemm_set_scheduler_buffer(buf.data_ptr(), buf.numel())
+        else:
+            lib.ssl4p_gemm_set_scheduler_buffer(None, 0)
+        del g
+
+
 def test_gemm_strided_views():
     """A operand as a row-strided view (qkv slices), C as a strided view."""
     from ssl4polyp_b200 import ops
