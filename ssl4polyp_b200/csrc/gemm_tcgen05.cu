@@ -45,6 +45,7 @@ struct GemmParams {
     const float* bias;           // [N] or null
     const void* aux;             // residual (fp32 [M,ldaux]) or pre-activation (bf16 [M,ldaux])
     long long split_stride;      // elements between split-K partial planes of C
+    int resid_prefetch;          // RESIDUAL epilogue: bulk-prefetch the tile's residual rows into L2 (K <= 1024; SSL4P_GEMM_RESID_PREFETCH)
     int* sched;                  // dynamic tile scheduler slot {next tile, finished units} (zero between launches) or null = static
 };
 
@@ -502,6 +503,17 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                     if (c < BN && n0 + c < p.N) load_aux<EPI>(p, row_base, n0 + c, aux_all[ci]);
                 }
             } else if constexpr (kAux) {
+                // the residual of the whole tile row (up to 1 KB, contiguous) is pulled into L2 now, one row per lane, by the
+                // first warp of each lane quarter: the chunk-by-chunk register loads below (one chunk of look-ahead) then pay
+                // L2 latency, not HBM latency - they were the stall of this epilogue (ncu r02d: long scoreboard on aux)
+                if (chunk0 == 0 && p.resid_prefetch) {
+                    const int row = row_base + (int)lane_id();
+                    const int ncols = min(BN, p.N - n0);
+                    if (row < p.M && ncols > 0) {
+                        const float* src = reinterpret_cast<const float*>(p.aux) + (size_t)row * p.ldaux + n0;
+                        asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(src), "r"(ncols * 4) : "memory");
+                    }
+                }
                 load_aux<EPI>(p, row_base, n0 + chunk0, aux_cur);      // in flight while the MMAs of the tile finish
             }
             constexpr bool kBias = EPI == SSL4P_EPI_BIAS_BF16 || EPI == SSL4P_EPI_BIAS_GELU_BF16 || EPI == SSL4P_EPI_BIAS_RESIDUAL_F32 ||
@@ -844,6 +856,10 @@ extern "C" int ssl4p_gemm_bf16(const void* A, const void* B, void* C, void* C2, 
     p.C = C; p.C2 = C2; p.bias = bias; p.aux = aux;
     p.split_stride = (long long)M * ldc;
     p.sched = take_sched_slot(stream);
+    // measured (scripts/r02_ab3.sh): dec proj (K = 512) 63.5 -> 58.4 us, enc proj (K = 768) unchanged, but dec fc2 (K = 2048,
+    // main-loop bound) 95.7 -> 99.3 us: the prefetches compete with the operand loads -> short K only
+    static const int resid_prefetch = [] { const char* e = getenv("SSL4P_GEMM_RESID_PREFETCH"); return e ? atoi(e) : -1; }();
+    p.resid_prefetch = resid_prefetch >= 0 ? resid_prefetch : (K <= 1024 ? 1 : 0);
 
     CUtensorMap tmA, tmB;
     int rc;

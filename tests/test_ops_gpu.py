@@ -428,6 +428,16 @@ def test_colsum_cast_adamw():
     x = torch.randn(1000, 768).bfloat16()
     out = ops.colsum(x.to(dev()))
     assert rel_err(out.cpu(), x.float().sum(0)) < 1e-4
+    # the 8-columns-per-lane kernel (N, ld multiples of 8) on ragged row counts, a strided view and an accumulate; the
+    # 2-columns-per-lane kernel for the rest
+    for M, N in ((50432, 1536), (12800, 2304), (37, 8), (1003, 264), (999, 770)):
+        y = torch.randn(M, N, generator=torch.Generator().manual_seed(M)).bfloat16()
+        assert rel_err(ops.colsum(y.to(dev())).cpu(), y.float().sum(0)) < 1e-4, (M, N)
+    big = torch.randn(777, 3 * 512).bfloat16().to(dev())
+    view = big[:, 512:1024]
+    acc = torch.ones(512, device=dev())
+    ops.colsum(view, out=acc, accumulate=True)
+    assert rel_err(acc.cpu(), 1 + view.float().sum(0).cpu()) < 1e-4
     src = torch.randn(100003)
     assert torch.equal(ops.cast_bf16(src.to(dev())).float().cpu(), src.bfloat16().float())
     n = 256 * 40
