@@ -424,9 +424,19 @@ __device__ __forceinline__ void store_row32_bf16(__nv_bfloat16* dst, const uint3
 
 // TMEM column map (512 columns): two score buffers of a HALF block (128 keys x 64 queries), buffer u at 128 u:
 // S^T [0,64) dP^T [64,128);  then dV [256,320)  dK [320,384)  dQ[qt] [384 + 64 qt, +64).
-// Half blocks are numbered j = 0,1,2,... in issue order and use buffer j & 1, so the tensor pipe computes the scores of
+// Half blocks are numbered j = 0,1,2,... in issue order and use buffer j % kNBuf, so the tensor pipe computes the scores of
 // half block j+1 (and the dV/dK/dQ updates of j-1) while the element-wise warps turn half block j into P^T / dS^T.
-constexpr uint32_t kColST = 0, kColDP = 64, kColBuf = 128, kColDV = 256, kColDK = 320, kColDQ = 384;
+constexpr uint32_t kColST = 0, kColDP = 64, kColBuf = 128;
+// Gradient accumulators behind the first two score buffers: dV, dK (HD columns each) and dQ per query tile (HD columns).  At
+// head_dim 32 the gradient MMAs run with N = 32 (one head: the B operand starts 64 bytes into the 128-byte swizzle row), so
+// they end at column 384 and a THIRD score buffer fits at [384, 512): the tensor pipe can then be two half blocks ahead of the
+// element-wise warps, which used to wait ~1/3 of the time for scores (MMA -> commit -> mbarrier -> wake-up is ~450 clk and
+// sat between every two half blocks).  At head_dim 64 the accumulators take [256, 512) and there are two buffers.
+template <int HD> struct BwdCols {
+    static constexpr int kNBuf = HD == 32 ? 3 : 2;
+    static constexpr uint32_t kDV = 256, kDK = 256 + HD, kDQ = 256 + 2 * HD;       // dQ of query tile qt at kDQ + qt * HD
+    __device__ __forceinline__ static uint32_t buf(int i) { return i < 2 ? (uint32_t)i * kColBuf : 384u; }
+};
 
 // Position of a half block inside one work item: head of the pair, key tile, query tile, half of the query tile.
 struct HalfBlk {
@@ -462,14 +472,16 @@ attention_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 12 * kTileBytes + 4096);
     uint64_t* in_full = bars;                                    // [2] operand stages: one-tile sequences (T <= 128) use the two
     uint64_t* in_empty = bars + 2;                               // [2] tiles of every operand buffer as a 2-deep ring of items
-    uint64_t* st_full = bars + 4;                                // [2] scores of half block j in TMEM buffer j & 1
-    uint64_t* pt_full = bars + 6;                                // [2] P^T / dS^T of half block j in shared memory, buffer drained
-    uint64_t* blk_done = bars + 8;                               // all tensor reads of a block's P^T / dS^T retired
-    uint64_t* dvk_full = bars + 9;
-    uint64_t* dvk_empty = bars + 10;
-    uint64_t* dq_full = bars + 11;
-    uint64_t* dq_empty = bars + 12;
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 13);
+    using Cols = BwdCols<HD>;
+    constexpr int kNBuf = Cols::kNBuf;                           // score buffers in TMEM: half block j uses buffer j % kNBuf
+    uint64_t* st_full = bars + 4;                                // [3] scores of half block j in its TMEM buffer
+    uint64_t* pt_full = bars + 7;                                // [3] P^T / dS^T of half block j in shared memory, buffer drained
+    uint64_t* blk_done = bars + 10;                              // all tensor reads of a block's P^T / dS^T retired
+    uint64_t* dvk_full = bars + 11;
+    uint64_t* dvk_empty = bars + 12;
+    uint64_t* dq_full = bars + 13;
+    uint64_t* dq_empty = bars + 14;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 15);
     const bool ring = p.NB == 1;                                 // item il lives in stage il & 1, otherwise always stage 0
 
     const int warp = threadIdx.x >> 5;
@@ -481,7 +493,7 @@ attention_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_
     if (warp == 9) {
         if (lane == 0) {
             for (int i = 0; i < 2; ++i) { mbar_init(&in_full[i], 1); mbar_init(&in_empty[i], 1); }
-            for (int i = 0; i < 2; ++i) { mbar_init(&st_full[i], 1); mbar_init(&pt_full[i], 256); }
+            for (int i = 0; i < kNBuf; ++i) { mbar_init(&st_full[i], 1); mbar_init(&pt_full[i], 256); }
             mbar_init(blk_done, 1);
             mbar_init(dvk_full, 1); mbar_init(dvk_empty, 256);
             mbar_init(dq_full, 1); mbar_init(dq_empty, 256);
@@ -544,14 +556,14 @@ attention_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_
             uint32_t sQa = smem_u32(sQ), sKa = smem_u32(sK), sVa = smem_u32(sV), sDOa = smem_u32(sDO);   // + stage offset per item
             const uint32_t sQ0 = sQa, sK0 = sKa, sV0 = sVa, sDO0 = sDOa;
             const uint32_t sPTa = smem_u32(sPT), sDSa = smem_u32(sDS);
-            const uint32_t idesc_acc = idesc_rt(128, 64, false, true);     // A K-major (P^T / dS^T rows = keys), B MN-major
-            const uint32_t idesc_dq = idesc_rt(128, 64, true, true);       // A MN-major (dS^T read as [keys][queries]), B MN-major
+            const uint32_t idesc_acc = idesc_rt(128, HD, false, true);     // A K-major (P^T / dS^T rows = keys), B MN-major (N = one head)
+            const uint32_t idesc_dq = idesc_rt(128, HD, true, true);       // A MN-major (dS^T read as [keys][queries]), B MN-major
             int j = 0, nkt = 0, nhead = 0;                       // half blocks, key tiles, heads issued so far (all items)
-            // scores of one half block: S^T = K[kt] Q[qt,h]^T and dP^T = V[kt] dO[qt,h]^T into TMEM buffer jj & 1
+            // scores of one half block: S^T = K[kt] Q[qt,h]^T and dP^T = V[kt] dO[qt,h]^T into TMEM buffer jj % kNBuf
             auto issue_scores = [&](const HalfBlk& x, int jj) {
                 const uint32_t koff = x.hh * (HD * 2);
                 const uint32_t idesc_s = idesc_rt(128, x.nqh(p.Npad), false, false);
-                const uint32_t tb = tmem_base + (uint32_t)(jj & 1) * kColBuf;
+                const uint32_t tb = tmem_base + Cols::buf(jj % kNBuf);
                 const uint32_t qoff = x.qt * kTileBytes + x.h * (64 * 128) + koff;
 #pragma unroll
                 for (int kk = 0; kk < HD / 16; ++kk)
@@ -561,7 +573,7 @@ attention_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_
                 for (int kk = 0; kk < HD / 16; ++kk)
                     umma_bf16(tb + kColDP, umma_smem_desc(sVa + x.kt * kTileBytes + koff + kk * 32, 16, 1024),
                               umma_smem_desc(sDOa + qoff + kk * 32, 16, 1024), idesc_s, kk > 0);
-                umma_commit(&st_full[jj & 1]);
+                umma_commit(&st_full[jj % kNBuf]);
             };
             for (int il = 0; il < my_items; ++il) {
                 const int stage = ring ? (il & 1) : 0, use = ring ? (il >> 1) : il;
@@ -570,31 +582,32 @@ attention_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_
                 sQa = sQ0 + stage * kTileBytes; sKa = sK0 + stage * kTileBytes; sVa = sV0 + stage * kTileBytes; sDOa = sDO0 + stage * kTileBytes;
                 HalfBlk ahead{0, 0, 0, 0};                        // next half block whose scores have not been issued
                 int ja = j;
-                for (int i = 0; i < 2 && ahead.hh < HP; ++i) { issue_scores(ahead, ja++); ahead.next(p.Npad, p.NB); }
+                for (int i = 0; i < kNBuf && ahead.hh < HP; ++i) { issue_scores(ahead, ja++); ahead.next(p.Npad, p.NB); }
                 for (HalfBlk c{0, 0, 0, 0}; c.hh < HP; c.next(p.Npad, p.NB), ++j) {
                     if (c.qt == 0 && c.h == 0) {
                         if (c.kt == 0) { mbar_wait(dq_empty, (nhead & 1) ^ 1); }      // previous head's dQ has been read out
                         mbar_wait(dvk_empty, (nkt & 1) ^ 1);                          // previous key tile's dV/dK have been read out
                     }
-                    mbar_wait(&pt_full[j & 1], (j >> 1) & 1);     // P^T / dS^T of this half block written, its TMEM buffer drained
+                    mbar_wait(&pt_full[j % kNBuf], (j / kNBuf) & 1);   // P^T / dS^T of this half block written, its TMEM buffer drained
                     tc_fence_after();
+                    const uint32_t hoff = HD == 32 ? (uint32_t)c.hh * 64u : 0u;   // hd 32: the head's 32 columns inside the 64-wide MN-major row
                     const int ks0 = c.h * 4, ks1 = ks0 + (c.nqh(p.Npad) >> 4);
                     for (int ks = ks0; ks < ks1; ++ks) {
                         const uint32_t aoff = (ks >> 2) * kTileBytes + (ks & 3) * 32;
                         // dV[kt] += P^T dO[qt]
-                        umma_bf16(tmem_base + kColDV, umma_smem_desc(sPTa + aoff, 16, 1024),
-                                  umma_smem_desc(sDOa + c.qt * kTileBytes + ks * 2048, kTileBytes, 1024), idesc_acc, (c.qt > 0) || (ks > 0));
+                        umma_bf16(tmem_base + Cols::kDV, umma_smem_desc(sPTa + aoff, 16, 1024),
+                                  umma_smem_desc(sDOa + c.qt * kTileBytes + ks * 2048 + hoff, kTileBytes, 1024), idesc_acc, (c.qt > 0) || (ks > 0));
                         // dK[kt] += dS^T Q[qt]
-                        umma_bf16(tmem_base + kColDK, umma_smem_desc(sDSa + aoff, 16, 1024),
-                                  umma_smem_desc(sQa + c.qt * kTileBytes + ks * 2048, kTileBytes, 1024), idesc_acc, (c.qt > 0) || (ks > 0));
+                        umma_bf16(tmem_base + Cols::kDK, umma_smem_desc(sDSa + aoff, 16, 1024),
+                                  umma_smem_desc(sQa + c.qt * kTileBytes + ks * 2048 + hoff, kTileBytes, 1024), idesc_acc, (c.qt > 0) || (ks > 0));
                     }
                     const bool last_half = c.h + 1 == HalfBlk::halves(p.Npad, c.qt);
                     if (last_half) {
                         // dQ[qt] += dS K[kt] : A = dS^T tile read MN-major (M = queries: 2 chunks of 64, 16 KB apart; K = keys)
 #pragma unroll
                         for (int ks = 0; ks < 8; ++ks)
-                            umma_bf16(tmem_base + kColDQ + c.qt * 64, umma_smem_desc(sDSa + ks * 2048, kTileBytes, 1024),
-                                      umma_smem_desc(sKa + c.kt * kTileBytes + ks * 2048, kTileBytes, 1024), idesc_dq, (c.kt > 0) || (ks > 0));
+                            umma_bf16(tmem_base + Cols::kDQ + c.qt * HD, umma_smem_desc(sDSa + ks * 2048, kTileBytes, 1024),
+                                      umma_smem_desc(sKa + c.kt * kTileBytes + ks * 2048 + hoff, kTileBytes, 1024), idesc_dq, (c.kt > 0) || (ks > 0));
                         umma_commit(blk_done);
                         if (c.qt == p.NB - 1) {
                             umma_commit(dvk_full); ++nkt;
@@ -638,7 +651,7 @@ attention_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_
             const int head = pend_sl * HP + pend_kt_hh;
             mbar_wait(dvk_full, wkt & 1);
             tc_fence_after();
-            const uint32_t col = half == 0 ? kColDV : kColDK;
+            const uint32_t col = half == 0 ? Cols::kDV : Cols::kDK;
             __nv_bfloat16* dst = p.dqkv + (size_t)(pb_ * p.T + key) * (3 * HHD) + (half == 0 ? 2 * HHD : HHD) + head * HD;
             if constexpr (HD == 64) {
 #pragma unroll
@@ -650,7 +663,7 @@ attention_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_
                 }
             } else {
                 uint32_t r[32];
-                tmem_ld_32x32(tlane + col + pend_kt_hh * 32, r);
+                tmem_ld_32x32(tlane + col, r);
                 tmem_ld_wait();
                 if (ok) store_row32_bf16(dst, r);
             }
@@ -671,13 +684,13 @@ attention_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_
 #pragma unroll
                     for (int h2 = 0; h2 < 2; ++h2) {
                         uint32_t r[32];
-                        tmem_ld_32x32(tlane + kColDQ + half * 64 + h2 * 32, r);
+                        tmem_ld_32x32(tlane + Cols::kDQ + half * 64 + h2 * 32, r);
                         tmem_ld_wait();
                         if (ok) store_row32_bf16(dst + h2 * 32, r);
                     }
                 } else {
                     uint32_t r[32];
-                    tmem_ld_32x32(tlane + kColDQ + half * 64 + pend_dq_hh * 32, r);
+                    tmem_ld_32x32(tlane + Cols::kDQ + half * 32, r);
                     tmem_ld_wait();
                     if (ok) store_row32_bf16(dst, r);
                 }
@@ -741,11 +754,11 @@ attention_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_
                             // pair mode: half block h holds the queries of image h; key rows of the other image stay zero
                             const bool active = c < nqh && (!p.pair || img == h);
                             uint32_t pw[16], dw[16];
-                            mbar_wait(&st_full[j & 1], (j >> 1) & 1);
+                            mbar_wait(&st_full[j % kNBuf], (j / kNBuf) & 1);
                             tc_fence_after();
                             if (active) {
                                 uint32_t rs[32], rd[32];
-                                const uint32_t tb = tlane + (uint32_t)(j & 1) * kColBuf;
+                                const uint32_t tb = tlane + Cols::buf(j % kNBuf);
                                 tmem_ld_32x32(tb + kColST + c, rs);
                                 tmem_ld_32x32(tb + kColDP + c, rd);
                                 const int q0 = qt * 128 + h * 64 + c;                // slot of the first query in the statistics arrays
@@ -789,7 +802,7 @@ attention_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_
                             }
                             fence_proxy_async();
                             tc_fence_before();
-                            mbar_arrive(&pt_full[j & 1]);
+                            mbar_arrive(&pt_full[j % kNBuf]);
                         }
                     }
                     pend_kt = kt; pend_kt_hh = hh; pend_b = b; pend_sl = sl;
