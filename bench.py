@@ -338,11 +338,12 @@ def b200_arm(args):
     # ---- roofline leg: every GEMM launch of one step timed with CUDA events on the launching stream ---------
     resident0 = tuple(t.to(dev) for t in host[0])
     overlap, eng.sink.overlap = eng.sink.overlap, False               # one stream: each GEMM is timed alone, not while sharing the
-    ops.GEMM_PROFILE = []                                             # SMs with the side stream's weight-gradient kernels
+    bucketed, eng.bucket_adamw = eng.bucket_adamw, False              # SMs / HBM with the side stream's weight-gradient kernels
+    ops.GEMM_PROFILE = []                                             # or the optimiser stream's per-bucket AdamW
     eng.step(*resident0)
     torch.cuda.synchronize()
     prof, ops.GEMM_PROFILE = ops.GEMM_PROFILE, None
-    eng.sink.overlap = overlap
+    eng.sink.overlap, eng.bucket_adamw = overlap, bucketed
     g_ms = sum(a.elapsed_time(b) for a, b, _, _ in prof)
     g_flops = sum(f for _, _, f, _ in prof)
     achieved = g_flops / (g_ms / 1e3) / 1e12 if g_ms > 0 else 0.0
