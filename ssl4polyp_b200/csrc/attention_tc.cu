@@ -402,6 +402,7 @@ struct AttnBwdParams {
     int B, pair;                               // pair: two images per 128-row tile (T <= 64); half block h = queries of image h
     int T, H, items, slices_per_img;
     int Npad, NB;
+    int debug;                                 // timing experiments only (SSL4P_ATTN_DEBUG; results are WRONG with a bit set): 1 = no blk_done wait, 2 = no shared-memory stores of P^T / dS^T, 4 = no exponentials
     float scale;
     const __nv_bfloat16* out;                  // [B*T, H*hd]
     const __nv_bfloat16* dout;                 // [B*T, H*hd]
@@ -454,8 +455,13 @@ struct HalfBlk {
     }
 };
 
+// Backward: one more warp than the forward - the MMA issue is split over TWO threads (warps 9 and 10).  With a single issuer the
+// kernel was bound by that thread's instruction stream (about 20 descriptor-building MMA issues and 3-4 commits per half block:
+// with the element-wise work switched off entirely the decoder shape still took 329 of 349 us, SSL4P_ATTN_DEBUG ablation).
+constexpr int kAttnBwdThreads = kAttnThreads + 32;
+
 template <int HD>
-__global__ void __launch_bounds__(kAttnThreads, 1)
+__global__ void __launch_bounds__(kAttnBwdThreads, 1)
 attention_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CUtensorMap tmDO,
                         const __grid_constant__ CUtensorMap tmQKV64, const __grid_constant__ CUtensorMap tmDO64, const AttnBwdParams p) {
     constexpr int HP = 64 / HD;
@@ -492,9 +498,9 @@ attention_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_
     if (warp == 8 && lane == 0) { tma_prefetch_desc(&tmQKV); tma_prefetch_desc(&tmDO); tma_prefetch_desc(&tmQKV64); tma_prefetch_desc(&tmDO64); }
     if (warp == 9) {
         if (lane == 0) {
-            for (int i = 0; i < 2; ++i) { mbar_init(&in_full[i], 1); mbar_init(&in_empty[i], 1); }
+            for (int i = 0; i < 2; ++i) { mbar_init(&in_full[i], 1); mbar_init(&in_empty[i], 2); }   // both issuers release a stage
             for (int i = 0; i < kNBuf; ++i) { mbar_init(&st_full[i], 1); mbar_init(&pt_full[i], 256); }
-            mbar_init(blk_done, 1);
+            mbar_init(blk_done, 2);                              // dV / dK issuer + dQ issuer
             mbar_init(dvk_full, 1); mbar_init(dvk_empty, 256);
             mbar_init(dq_full, 1); mbar_init(dq_empty, 256);
             mbar_fence_init();
@@ -551,14 +557,47 @@ attention_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_
         }
         __syncwarp();
     } else if (warp == 9) {
-        // ===================== MMA issuer =====================
+        // ===================== MMA issuer A: dV += P^T dO, dK += dS^T Q =====================
+        if (lane == 0) {
+            const uint32_t sQ0 = smem_u32(sQ), sDO0 = smem_u32(sDO);
+            const uint32_t sPTa = smem_u32(sPT), sDSa = smem_u32(sDS);
+            const uint32_t idesc_acc = idesc_rt(128, HD, false, true);     // A K-major (P^T / dS^T rows = keys), B MN-major (N = one head)
+            int j = 0, nkt = 0;                                  // half blocks, key tiles issued so far (all items)
+            for (int il = 0; il < my_items; ++il) {
+                const int stage = ring ? (il & 1) : 0, use = ring ? (il >> 1) : il;
+                mbar_wait(&in_full[stage], use & 1);
+                tc_fence_after();
+                const uint32_t sQa = sQ0 + stage * kTileBytes, sDOa = sDO0 + stage * kTileBytes;
+                for (HalfBlk c{0, 0, 0, 0}; c.hh < HP; c.next(p.Npad, p.NB), ++j) {
+                    if (c.qt == 0 && c.h == 0) mbar_wait(dvk_empty, (nkt & 1) ^ 1);   // previous key tile's dV/dK have been read out
+                    mbar_wait(&pt_full[j % kNBuf], (j / kNBuf) & 1);   // P^T / dS^T of this half block written
+                    tc_fence_after();
+                    const uint32_t hoff = HD == 32 ? (uint32_t)c.hh * 64u : 0u;   // hd 32: the head's 32 columns inside the 64-wide MN-major row
+                    const int ks0 = c.h * 4, ks1 = ks0 + (c.nqh(p.Npad) >> 4);
+                    for (int ks = ks0; ks < ks1; ++ks) {
+                        const uint32_t aoff = (ks >> 2) * kTileBytes + (ks & 3) * 32;
+                        umma_bf16(tmem_base + Cols::kDV, umma_smem_desc(sPTa + aoff, 16, 1024),
+                                  umma_smem_desc(sDOa + c.qt * kTileBytes + ks * 2048 + hoff, kTileBytes, 1024), idesc_acc, (c.qt > 0) || (ks > 0));
+                        umma_bf16(tmem_base + Cols::kDK, umma_smem_desc(sDSa + aoff, 16, 1024),
+                                  umma_smem_desc(sQa + c.qt * kTileBytes + ks * 2048 + hoff, kTileBytes, 1024), idesc_acc, (c.qt > 0) || (ks > 0));
+                    }
+                    if (c.h + 1 == HalfBlk::halves(p.Npad, c.qt)) {
+                        umma_commit(blk_done);                   // (one of two arrivals: issuer B commits its dQ MMAs)
+                        if (c.qt == p.NB - 1) { umma_commit(dvk_full); ++nkt; }
+                    }
+                }
+                umma_commit(&in_empty[stage]);
+            }
+        }
+        __syncwarp();
+    } else if (warp == 10) {
+        // ===================== MMA issuer B: scores (S^T, dP^T) and dQ += dS K =====================
         if (lane == 0) {
             uint32_t sQa = smem_u32(sQ), sKa = smem_u32(sK), sVa = smem_u32(sV), sDOa = smem_u32(sDO);   // + stage offset per item
             const uint32_t sQ0 = sQa, sK0 = sKa, sV0 = sVa, sDO0 = sDOa;
-            const uint32_t sPTa = smem_u32(sPT), sDSa = smem_u32(sDS);
-            const uint32_t idesc_acc = idesc_rt(128, HD, false, true);     // A K-major (P^T / dS^T rows = keys), B MN-major (N = one head)
+            const uint32_t sDSa = smem_u32(sDS);
             const uint32_t idesc_dq = idesc_rt(128, HD, true, true);       // A MN-major (dS^T read as [keys][queries]), B MN-major
-            int j = 0, nkt = 0, nhead = 0;                       // half blocks, key tiles, heads issued so far (all items)
+            int j = 0, nhead = 0;                                // half blocks, heads issued so far (all items)
             // scores of one half block: S^T = K[kt] Q[qt,h]^T and dP^T = V[kt] dO[qt,h]^T into TMEM buffer jj % kNBuf
             auto issue_scores = [&](const HalfBlk& x, int jj) {
                 const uint32_t koff = x.hh * (HD * 2);
@@ -584,38 +623,21 @@ attention_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_
                 int ja = j;
                 for (int i = 0; i < kNBuf && ahead.hh < HP; ++i) { issue_scores(ahead, ja++); ahead.next(p.Npad, p.NB); }
                 for (HalfBlk c{0, 0, 0, 0}; c.hh < HP; c.next(p.Npad, p.NB), ++j) {
-                    if (c.qt == 0 && c.h == 0) {
-                        if (c.kt == 0) { mbar_wait(dq_empty, (nhead & 1) ^ 1); }      // previous head's dQ has been read out
-                        mbar_wait(dvk_empty, (nkt & 1) ^ 1);                          // previous key tile's dV/dK have been read out
-                    }
-                    mbar_wait(&pt_full[j % kNBuf], (j / kNBuf) & 1);   // P^T / dS^T of this half block written, its TMEM buffer drained
+                    if (c.qt == 0 && c.h == 0 && c.kt == 0) mbar_wait(dq_empty, (nhead & 1) ^ 1);   // previous head's dQ has been read out
+                    mbar_wait(&pt_full[j % kNBuf], (j / kNBuf) & 1);   // dS^T of this half block written, its TMEM buffer drained
                     tc_fence_after();
-                    const uint32_t hoff = HD == 32 ? (uint32_t)c.hh * 64u : 0u;   // hd 32: the head's 32 columns inside the 64-wide MN-major row
-                    const int ks0 = c.h * 4, ks1 = ks0 + (c.nqh(p.Npad) >> 4);
-                    for (int ks = ks0; ks < ks1; ++ks) {
-                        const uint32_t aoff = (ks >> 2) * kTileBytes + (ks & 3) * 32;
-                        // dV[kt] += P^T dO[qt]
-                        umma_bf16(tmem_base + Cols::kDV, umma_smem_desc(sPTa + aoff, 16, 1024),
-                                  umma_smem_desc(sDOa + c.qt * kTileBytes + ks * 2048 + hoff, kTileBytes, 1024), idesc_acc, (c.qt > 0) || (ks > 0));
-                        // dK[kt] += dS^T Q[qt]
-                        umma_bf16(tmem_base + Cols::kDK, umma_smem_desc(sDSa + aoff, 16, 1024),
-                                  umma_smem_desc(sQa + c.qt * kTileBytes + ks * 2048 + hoff, kTileBytes, 1024), idesc_acc, (c.qt > 0) || (ks > 0));
-                    }
-                    const bool last_half = c.h + 1 == HalfBlk::halves(p.Npad, c.qt);
-                    if (last_half) {
+                    if (c.h + 1 == HalfBlk::halves(p.Npad, c.qt)) {
                         // dQ[qt] += dS K[kt] : A = dS^T tile read MN-major (M = queries: 2 chunks of 64, 16 KB apart; K = keys)
+                        const uint32_t hoff = HD == 32 ? (uint32_t)c.hh * 64u : 0u;
 #pragma unroll
                         for (int ks = 0; ks < 8; ++ks)
                             umma_bf16(tmem_base + Cols::kDQ + c.qt * HD, umma_smem_desc(sDSa + ks * 2048, kTileBytes, 1024),
                                       umma_smem_desc(sKa + c.kt * kTileBytes + ks * 2048 + hoff, kTileBytes, 1024), idesc_dq, (c.kt > 0) || (ks > 0));
                         umma_commit(blk_done);
-                        if (c.qt == p.NB - 1) {
-                            umma_commit(dvk_full); ++nkt;
-                            if (c.kt == p.NB - 1) { umma_commit(dq_full); ++nhead; }
-                        }
+                        if (c.qt == p.NB - 1 && c.kt == p.NB - 1) { umma_commit(dq_full); ++nhead; }
                     }
-                    // refill the buffer just drained (issuing these BEFORE the gradient MMAs was measured slower: 346 -> 367 us
-                    // at B=256, T=197, hd 32 - the gradient MMAs gate blk_done, which the element-wise warps wait for first)
+                    // refill the buffer just drained (after the dQ MMAs: they gate blk_done, which the element-wise warps wait
+                    // for first)
                     if (ahead.hh < HP) { issue_scores(ahead, ja++); ahead.next(p.Npad, p.NB); }
                 }
                 umma_commit(&in_empty[stage]);
@@ -776,7 +798,7 @@ attention_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_
                                         float pv[4], ev[4];
 #pragma unroll
                                         for (int u = 0; u < 4; ++u) {
-                                            pv[u] = fast_exp2(fmaf(__uint_as_float(rs[jj + u]), sl2, -lq[u]));
+                                            pv[u] = (p.debug & 4) ? fmaf(__uint_as_float(rs[jj + u]), sl2, -lq[u]) : fast_exp2(fmaf(__uint_as_float(rs[jj + u]), sl2, -lq[u]));
                                             ev[u] = pv[u] * fmaf(__uint_as_float(rd[jj + u]), p.scale, -dq_[u]);
                                             if (decltype(mask_keys)::value && !key_ok) { pv[u] = 0.f; ev[u] = 0.f; }
                                         }
@@ -789,8 +811,8 @@ attention_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_
                             if (pend_kt >= 0) write_dvk();
                             if (pend_dq_hh >= 0) write_dq();
                             // the P^T / dS^T tiles are single buffered: the tensor reads of the previous block must have retired
-                            if (h == 0 && nblk > 0) mbar_wait(blk_done, (nblk - 1) & 1);
-                            if (active) {
+                            if (h == 0 && nblk > 0 && !(p.debug & 1)) mbar_wait(blk_done, (nblk - 1) & 1);
+                            if (active && !(p.debug & 2)) {
                                 const uint32_t tile = (uint32_t)h * kTileBytes;
                                 const int sub = c >> 3;
 #pragma unroll
@@ -921,11 +943,13 @@ static int launch_bwd_tc(const void* qkv, const void* out, const void* dout, con
     p.items = (p.pair ? (B + 1) / 2 : B) * p.slices_per_img;
     p.Npad = p.pair ? 128 : (T + 15) / 16 * 16; p.NB = (T + 127) / 128;
     p.scale = scale; p.out = (const __nv_bfloat16*)out; p.dout = (const __nv_bfloat16*)dout; p.lse = lse; p.dqkv = (__nv_bfloat16*)dqkv;
+    p.debug = 0;
+    if (const char* e = getenv("SSL4P_ATTN_DEBUG")) p.debug = atoi(e);
     auto kern = attention_bwd_tc_kernel<HD>;
     static bool attr = false;
     if (!attr) { SSL4P_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kBwdSmem)); attr = true; }
     const int grid = p.items < num_sms() ? p.items : num_sms();
-    cudaError_t e = launch_ex(kern, dim3((unsigned)grid), dim3(kAttnThreads), (size_t)kBwdSmem, s, 1, tmQ, tmD, tmQ64, tmD64, p);
+    cudaError_t e = launch_ex(kern, dim3((unsigned)grid), dim3(kAttnBwdThreads), (size_t)kBwdSmem, s, 1, tmQ, tmD, tmQ64, tmD64, p);
     if (e != cudaSuccess) { set_error("attention_bwd_tc_kernel launch failed: %s", cudaGetErrorString(e)); return SSL4P_ERR_CUDA; }
     return check_launch("attention_bwd_tc_kernel");
 }
