@@ -402,7 +402,7 @@ struct AttnBwdParams {
     int B, pair;                               // pair: two images per 128-row tile (T <= 64); half block h = queries of image h
     int T, H, items, slices_per_img;
     int Npad, NB;
-    int debug;                                 // timing experiments only (SSL4P_ATTN_DEBUG; results are WRONG with a bit set): 1 = no blk_done wait, 2 = no shared-memory stores of P^T / dS^T, 4 = no exponentials
+    int debug;                                 // timing experiments only (SSL4P_ATTN_DEBUG; results are WRONG with a bit set): 1 = no blk_done wait, 2 = no shared-memory stores of P^T / dS^T, 4 = no exponentials, 8 = no dV / dK MMAs, 16 = no dQ MMAs, 32 = no score MMAs, 64 = no per-item statistics loads
     float scale;
     const __nv_bfloat16* out;                  // [B*T, H*hd]
     const __nv_bfloat16* dout;                 // [B*T, H*hd]
@@ -499,10 +499,11 @@ attention_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_
     if (warp == 9) {
         if (lane == 0) {
             for (int i = 0; i < 2; ++i) { mbar_init(&in_full[i], 1); mbar_init(&in_empty[i], 2); }   // both issuers release a stage
-            for (int i = 0; i < kNBuf; ++i) { mbar_init(&st_full[i], 1); mbar_init(&pt_full[i], 256); }
+            // one arrival per element-wise WARP (its lanes meet at __syncwarp first): 8 arrivals on a barrier instead of 256
+            for (int i = 0; i < kNBuf; ++i) { mbar_init(&st_full[i], 1); mbar_init(&pt_full[i], 8); }
             mbar_init(blk_done, 2);                              // dV / dK issuer + dQ issuer
-            mbar_init(dvk_full, 1); mbar_init(dvk_empty, 256);
-            mbar_init(dq_full, 1); mbar_init(dq_empty, 256);
+            mbar_init(dvk_full, 1); mbar_init(dvk_empty, 8);
+            mbar_init(dq_full, 1); mbar_init(dq_empty, 8);
             mbar_fence_init();
             fence_proxy_async();
         }
@@ -558,7 +559,12 @@ attention_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_
         __syncwarp();
     } else if (warp == 9) {
         // ===================== MMA issuer A: dV += P^T dO, dK += dS^T Q =====================
-        if (lane == 0) {
+        // The whole warp runs the loop (uniform bookkeeping, every lane waits on the barriers); the tcgen05 instructions sit
+        // under elect.sync, which the compiler knows to be single-threaded: with `if (lane == 0)` around the loop it wrapped
+        // every UTCHMMA / UTCBAR in an ELECT + BRA.U.ANY retry loop (the operands live in uniform registers).
+        {
+            auto mma = [&](uint32_t d, uint64_t ad, uint64_t bd, uint32_t id, uint32_t acc) { if (elect_one()) umma_bf16(d, ad, bd, id, acc); };
+            auto commit = [&](uint64_t* bar) { if (elect_one()) umma_commit(bar); };
             const uint32_t sQ0 = smem_u32(sQ), sDO0 = smem_u32(sDO);
             const uint32_t sPTa = smem_u32(sPT), sDSa = smem_u32(sDS);
             const uint32_t idesc_acc = idesc_rt(128, HD, false, true);     // A K-major (P^T / dS^T rows = keys), B MN-major (N = one head)
@@ -574,25 +580,27 @@ attention_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_
                     tc_fence_after();
                     const uint32_t hoff = HD == 32 ? (uint32_t)c.hh * 64u : 0u;   // hd 32: the head's 32 columns inside the 64-wide MN-major row
                     const int ks0 = c.h * 4, ks1 = ks0 + (c.nqh(p.Npad) >> 4);
-                    for (int ks = ks0; ks < ks1; ++ks) {
+                    for (int ks = ks0; ks < ks1 && !(p.debug & 8); ++ks) {
                         const uint32_t aoff = (ks >> 2) * kTileBytes + (ks & 3) * 32;
-                        umma_bf16(tmem_base + Cols::kDV, umma_smem_desc(sPTa + aoff, 16, 1024),
+                        mma(tmem_base + Cols::kDV, umma_smem_desc(sPTa + aoff, 16, 1024),
                                   umma_smem_desc(sDOa + c.qt * kTileBytes + ks * 2048 + hoff, kTileBytes, 1024), idesc_acc, (c.qt > 0) || (ks > 0));
-                        umma_bf16(tmem_base + Cols::kDK, umma_smem_desc(sDSa + aoff, 16, 1024),
+                        mma(tmem_base + Cols::kDK, umma_smem_desc(sDSa + aoff, 16, 1024),
                                   umma_smem_desc(sQa + c.qt * kTileBytes + ks * 2048 + hoff, kTileBytes, 1024), idesc_acc, (c.qt > 0) || (ks > 0));
                     }
                     if (c.h + 1 == HalfBlk::halves(p.Npad, c.qt)) {
-                        umma_commit(blk_done);                   // (one of two arrivals: issuer B commits its dQ MMAs)
-                        if (c.qt == p.NB - 1) { umma_commit(dvk_full); ++nkt; }
+                        commit(blk_done);                   // (one of two arrivals: issuer B commits its dQ MMAs)
+                        if (c.qt == p.NB - 1) { commit(dvk_full); ++nkt; }
                     }
                 }
-                umma_commit(&in_empty[stage]);
+                commit(&in_empty[stage]);
             }
         }
         __syncwarp();
     } else if (warp == 10) {
         // ===================== MMA issuer B: scores (S^T, dP^T) and dQ += dS K =====================
-        if (lane == 0) {
+        {
+            auto mma = [&](uint32_t d, uint64_t ad, uint64_t bd, uint32_t id, uint32_t acc) { if (elect_one()) umma_bf16(d, ad, bd, id, acc); };
+            auto commit = [&](uint64_t* bar) { if (elect_one()) umma_commit(bar); };
             uint32_t sQa = smem_u32(sQ), sKa = smem_u32(sK), sVa = smem_u32(sV), sDOa = smem_u32(sDO);   // + stage offset per item
             const uint32_t sQ0 = sQa, sK0 = sKa, sV0 = sVa, sDO0 = sDOa;
             const uint32_t sDSa = smem_u32(sDS);
@@ -604,15 +612,16 @@ attention_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_
                 const uint32_t idesc_s = idesc_rt(128, x.nqh(p.Npad), false, false);
                 const uint32_t tb = tmem_base + Cols::buf(jj % kNBuf);
                 const uint32_t qoff = x.qt * kTileBytes + x.h * (64 * 128) + koff;
+                if (p.debug & 32) { commit(&st_full[jj % kNBuf]); return; }
 #pragma unroll
                 for (int kk = 0; kk < HD / 16; ++kk)
-                    umma_bf16(tb + kColST, umma_smem_desc(sKa + x.kt * kTileBytes + koff + kk * 32, 16, 1024),
+                    mma(tb + kColST, umma_smem_desc(sKa + x.kt * kTileBytes + koff + kk * 32, 16, 1024),
                               umma_smem_desc(sQa + qoff + kk * 32, 16, 1024), idesc_s, kk > 0);
 #pragma unroll
                 for (int kk = 0; kk < HD / 16; ++kk)
-                    umma_bf16(tb + kColDP, umma_smem_desc(sVa + x.kt * kTileBytes + koff + kk * 32, 16, 1024),
+                    mma(tb + kColDP, umma_smem_desc(sVa + x.kt * kTileBytes + koff + kk * 32, 16, 1024),
                               umma_smem_desc(sDOa + qoff + kk * 32, 16, 1024), idesc_s, kk > 0);
-                umma_commit(&st_full[jj % kNBuf]);
+                commit(&st_full[jj % kNBuf]);
             };
             for (int il = 0; il < my_items; ++il) {
                 const int stage = ring ? (il & 1) : 0, use = ring ? (il >> 1) : il;
@@ -629,18 +638,19 @@ attention_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_
                     if (c.h + 1 == HalfBlk::halves(p.Npad, c.qt)) {
                         // dQ[qt] += dS K[kt] : A = dS^T tile read MN-major (M = queries: 2 chunks of 64, 16 KB apart; K = keys)
                         const uint32_t hoff = HD == 32 ? (uint32_t)c.hh * 64u : 0u;
+                        if (!(p.debug & 16))
 #pragma unroll
                         for (int ks = 0; ks < 8; ++ks)
-                            umma_bf16(tmem_base + Cols::kDQ + c.qt * HD, umma_smem_desc(sDSa + ks * 2048, kTileBytes, 1024),
+                            mma(tmem_base + Cols::kDQ + c.qt * HD, umma_smem_desc(sDSa + ks * 2048, kTileBytes, 1024),
                                       umma_smem_desc(sKa + c.kt * kTileBytes + ks * 2048 + hoff, kTileBytes, 1024), idesc_dq, (c.kt > 0) || (ks > 0));
-                        umma_commit(blk_done);
-                        if (c.qt == p.NB - 1 && c.kt == p.NB - 1) { umma_commit(dq_full); ++nhead; }
+                        commit(blk_done);
+                        if (c.qt == p.NB - 1 && c.kt == p.NB - 1) { commit(dq_full); ++nhead; }
                     }
                     // refill the buffer just drained (after the dQ MMAs: they gate blk_done, which the element-wise warps wait
                     // for first)
                     if (ahead.hh < HP) { issue_scores(ahead, ja++); ahead.next(p.Npad, p.NB); }
                 }
-                umma_commit(&in_empty[stage]);
+                commit(&in_empty[stage]);
             }
         }
         __syncwarp();
@@ -690,7 +700,8 @@ attention_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_
                 if (ok) store_row32_bf16(dst, r);
             }
             tc_fence_before();
-            mbar_arrive(dvk_empty);
+            __syncwarp();
+            if (lane == 0) mbar_arrive(dvk_empty);
             ++wkt; pend_kt = -1;
         };
         auto write_dq = [&]() {                                  // dQ of head pend_dq_hh: warps 0-3 take query tile 0, warps 4-7 tile 1
@@ -718,7 +729,8 @@ attention_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_
                 }
             }
             tc_fence_before();
-            mbar_arrive(dq_empty);
+            __syncwarp();
+            if (lane == 0) mbar_arrive(dq_empty);
             ++whd; pend_dq_hh = -1;
         };
         for (int il = 0; il < my_items; ++il) {
@@ -732,7 +744,7 @@ attention_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_
                 const int qt_ = p.pair ? (q & 63) : q;
                 uint4 ra[HP][HD / 8], rd[HP][HD / 8];
                 float lv[HP], dv[HP];
-                if (qt_ < p.T && qb < p.B && (!p.pair || q < 128)) {
+                if (qt_ < p.T && qb < p.B && (!p.pair || q < 128) && !(p.debug & 64)) {
 #pragma unroll
                     for (int hh = 0; hh < HP; ++hh) {
                         const size_t off = ((size_t)(qb * p.T + qt_) * p.H + sl * HP + hh) * HD;
@@ -755,6 +767,18 @@ attention_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_
                 } else {
 #pragma unroll
                     for (int hh = 0; hh < HP; ++hh) { lv[hh] = INFINITY; dv[hh] = 0.f; }
+                }
+                // the NEXT item's O rows (128 contiguous bytes per query: both heads) go to L2 now; dO is already covered by the
+                // producer's tile prefetch.  The statistics loads of the next item then cost an L2 round trip, not HBM's.
+                if (il + 1 < my_items) {
+                    const int item2 = item + gridDim.x;
+                    const int b2 = item2 / p.slices_per_img, s2 = item2 % p.slices_per_img;
+                    const int qb2 = p.pair ? 2 * b2 + (q >> 6) : b2;
+                    if (qt_ < p.T && qb2 < p.B && (!p.pair || q < 128)) {
+                        const __nv_bfloat16* nxt = p.out + ((size_t)(qb2 * p.T + qt_) * p.H + s2 * HP) * HD;
+                        asm volatile("prefetch.global.L2 [%0];" ::"l"(nxt));
+                        asm volatile("prefetch.global.L2 [%0];" ::"l"(p.lse + ((size_t)qb2 * p.H + s2 * HP) * p.T + qt_));
+                    }
                 }
                 named_bar_sync(1, 256);                          // every thread is done reading the previous item's statistics
 #pragma unroll
@@ -824,7 +848,8 @@ attention_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_
                             }
                             fence_proxy_async();
                             tc_fence_before();
-                            mbar_arrive(&pt_full[j % kNBuf]);
+                            __syncwarp();
+                            if (lane == 0) mbar_arrive(&pt_full[j % kNBuf]);
                         }
                     }
                     pend_kt = kt; pend_kt_hh = hh; pend_b = b; pend_sl = sl;
