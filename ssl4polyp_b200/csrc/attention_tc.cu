@@ -28,6 +28,14 @@
 
 namespace ssl4p {
 
+// Timing ablations of the backward (SSL4P_ATTN_DEBUG, scripts/r02_attn_dbg.sh) are compiled in only with -DSSL4P_ATTN_ABLATION:
+// in the shipped kernel the switches are constant-false and cost nothing (the forward lost 18 us to such tests).
+#ifdef SSL4P_ATTN_ABLATION
+#define ABLATE(bit) ((p.debug & (bit)) != 0)
+#else
+#define ABLATE(bit) false
+#endif
+
 struct AttnFwdParams {
     int B, pair;                               // pair: two images share one 128-row tile (T <= 64), item = (image pair, slice)
     int T, H, items, slices_per_img;           // slices_per_img = H*hd/64
@@ -585,7 +593,7 @@ attention_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_
                     tc_fence_after();
                     const uint32_t hoff = HD == 32 ? (uint32_t)c.hh * 64u : 0u;   // hd 32: the head's 32 columns inside the 64-wide MN-major row
                     const int ks0 = c.h * 4, ks1 = ks0 + (c.nqh(p.Npad) >> 4);
-                    for (int ks = ks0; ks < ks1 && !(p.debug & 8); ++ks) {
+                    for (int ks = ks0; ks < ks1 && !ABLATE(8); ++ks) {
                         const uint32_t aoff = (ks >> 2) * kTileBytes + (ks & 3) * 32;
                         mma(tmem_base + Cols::kDV, umma_smem_desc(sPTa + aoff, 16, 1024),
                                   umma_smem_desc(sDOa + c.qt * kTileBytes + ks * 2048 + hoff, kTileBytes, 1024), idesc_acc, (c.qt > 0) || (ks > 0));
@@ -617,7 +625,7 @@ attention_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_
                 const uint32_t idesc_s = idesc_rt(128, x.nqh(p.Npad), false, false);
                 const uint32_t tb = tmem_base + Cols::buf(jj % kNBuf);
                 const uint32_t qoff = x.qt * kTileBytes + x.h * (64 * 128) + koff;
-                if (p.debug & 32) { commit(&st_full[jj % kNBuf]); return; }
+                if ABLATE(32) { commit(&st_full[jj % kNBuf]); return; }
 #pragma unroll
                 for (int kk = 0; kk < HD / 16; ++kk)
                     mma(tb + kColST, umma_smem_desc(sKa + x.kt * kTileBytes + koff + kk * 32, 16, 1024),
@@ -643,7 +651,7 @@ attention_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_
                     if (c.h + 1 == HalfBlk::halves(p.Npad, c.qt)) {
                         // dQ[qt] += dS K[kt] : A = dS^T tile read MN-major (M = queries: 2 chunks of 64, 16 KB apart; K = keys)
                         const uint32_t hoff = HD == 32 ? (uint32_t)c.hh * 64u : 0u;
-                        if (!(p.debug & 16))
+                        if (!ABLATE(16))
 #pragma unroll
                         for (int ks = 0; ks < 8; ++ks)
                             mma(tmem_base + Cols::kDQ + c.qt * HD, umma_smem_desc(sDSa + ks * 2048, kTileBytes, 1024),
@@ -749,7 +757,7 @@ attention_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_
                 const int qt_ = p.pair ? (q & 63) : q;
                 uint4 ra[HP][HD / 8], rd[HP][HD / 8];
                 float lv[HP], dv[HP];
-                if (qt_ < p.T && qb < p.B && (!p.pair || q < 128) && !(p.debug & 64)) {
+                if (qt_ < p.T && qb < p.B && (!p.pair || q < 128) && !ABLATE(64)) {
 #pragma unroll
                     for (int hh = 0; hh < HP; ++hh) {
                         const size_t off = ((size_t)(qb * p.T + qt_) * p.H + sl * HP + hh) * HD;
@@ -827,7 +835,7 @@ attention_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_
                                         float pv[4], ev[4];
 #pragma unroll
                                         for (int u = 0; u < 4; ++u) {
-                                            pv[u] = (p.debug & 4) ? fmaf(__uint_as_float(rs[jj + u]), sl2, -lq[u]) : fast_exp2(fmaf(__uint_as_float(rs[jj + u]), sl2, -lq[u]));
+                                            pv[u] = ABLATE(4) ? fmaf(__uint_as_float(rs[jj + u]), sl2, -lq[u]) : fast_exp2(fmaf(__uint_as_float(rs[jj + u]), sl2, -lq[u]));
                                             ev[u] = pv[u] * fmaf(__uint_as_float(rd[jj + u]), p.scale, -dq_[u]);
                                             if (decltype(mask_keys)::value && !key_ok) { pv[u] = 0.f; ev[u] = 0.f; }
                                         }
@@ -840,8 +848,8 @@ attention_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_
                             if (pend_kt >= 0) write_dvk();
                             if (pend_dq_hh >= 0) write_dq();
                             // the P^T / dS^T tiles are single buffered: the tensor reads of the previous block must have retired
-                            if (h == 0 && nblk > 0 && !(p.debug & 1)) mbar_wait(blk_done, (nblk - 1) & 1);
-                            if (active && !(p.debug & 2)) {
+                            if (h == 0 && nblk > 0 && !ABLATE(1)) mbar_wait(blk_done, (nblk - 1) & 1);
+                            if (active && !ABLATE(2)) {
                                 const uint32_t tile = (uint32_t)h * kTileBytes;
                                 const int sub = c >> 3;
 #pragma unroll
