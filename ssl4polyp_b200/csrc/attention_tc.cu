@@ -625,7 +625,7 @@ attention_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_
                 const uint32_t idesc_s = idesc_rt(128, x.nqh(p.Npad), false, false);
                 const uint32_t tb = tmem_base + Cols::buf(jj % kNBuf);
                 const uint32_t qoff = x.qt * kTileBytes + x.h * (64 * 128) + koff;
-                if ABLATE(32) { commit(&st_full[jj % kNBuf]); return; }
+                if (ABLATE(32)) { commit(&st_full[jj % kNBuf]); return; }
 #pragma unroll
                 for (int kk = 0; kk < HD / 16; ++kk)
                     mma(tb + kColST, umma_smem_desc(sKa + x.kt * kTileBytes + koff + kk * 32, 16, 1024),

@@ -64,8 +64,17 @@ masked_mse_fwd_kernel(const float* __restrict__ imgs, const float* __restrict__ 
 // loss = sum(per_patch) / sum(mask); also stores sum(mask) at per_patch[NL] for the backward.  One block, fixed order.
 __global__ void masked_mse_finalize_kernel(float* __restrict__ per_patch, const float* __restrict__ mask, int NL, float* __restrict__ loss) {
     __shared__ float s_a[32], s_b[32];
+    // four strided elements per round, all eight loads issued before the first add (one block: the loads' latency is the cost)
     float a = 0.f, b = 0.f;
-    for (int i = threadIdx.x; i < NL; i += blockDim.x) { a += per_patch[i]; b += mask[i]; }
+    const int bd = blockDim.x;
+    int i = threadIdx.x;
+    for (; i + 3 * bd < NL; i += 4 * bd) {
+        const float p0 = per_patch[i], p1 = per_patch[i + bd], p2 = per_patch[i + 2 * bd], p3 = per_patch[i + 3 * bd];
+        const float m0 = mask[i], m1 = mask[i + bd], m2 = mask[i + 2 * bd], m3 = mask[i + 3 * bd];
+        a += (p0 + p1) + (p2 + p3);
+        b += (m0 + m1) + (m2 + m3);
+    }
+    for (; i < NL; i += bd) { a += per_patch[i]; b += mask[i]; }
     a = warp_sum(a); b = warp_sum(b);
     if (lane_id() == 0) { s_a[threadIdx.x >> 5] = a; s_b[threadIdx.x >> 5] = b; }
     __syncthreads();
