@@ -70,6 +70,8 @@ def _ensure_gemm_scheduler(lib) -> None:
     dev = torch.cuda.current_device()
     if dev in _sched_buffers:
         return
+    if torch.cuda.is_current_stream_capturing():      # never allocate the buffer from a graph's private pool: static tile lists
+        return                                        # for this capture, try again on the next eager call
     if os.environ.get("SSL4P_GEMM_SCHED", "1") == "0" or _sched_buffers:      # the library keeps one buffer (one device per process)
         _sched_buffers[dev] = None
         return
