@@ -57,7 +57,9 @@ struct AttnFwdParams {
 // current one is complete (before P V), and the warpgroup reads O of tile g out only after the exponentials of tile
 // g+2: both round trips (commit -> mbarrier -> wake-up) that used to sit between two tiles are hidden.
 // Otherwise (`sep` = 0) O is accumulated over the dead S columns and read out before the next S may be issued.
-template <int HD>
+// PAIR (two images per tile, T <= 64) and SEP (O in its own TMEM columns) are compile-time: the softmax loop is sensitive to
+// every extra live value and branch (a handful of runtime switches cost the backward 5 %, the forward 14 %).
+template <int HD, bool PAIR, bool SEP>
 __global__ void __launch_bounds__(kAttnThreads, 1)
 attention_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CUtensorMap tmQKV64, const AttnFwdParams p) {
     constexpr int HP = 64 / HD;                                  // heads per work item
@@ -74,7 +76,7 @@ attention_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_
     uint64_t* v_empty = bars + 11;                               // all P V MMAs of the item retired
     // one-tile sequences (T <= 128): the two tiles of each operand buffer form a 2-deep ring of items; stage 1 barriers:
     uint64_t* qk_full1 = bars + 12; uint64_t* qk_empty1 = bars + 13; uint64_t* v_full1 = bars + 14; uint64_t* v_empty1 = bars + 15;
-    const bool ring = p.NB == 1 && p.NKB == 1;
+    const bool ring = PAIR || (p.NB == 1 && p.NKB == 1);          // (pair mode: always one tile per operand)
     uint64_t* s_full = bars + 2;                                 // [2]
     uint64_t* p_full = bars + 4;                                 // [2]
     uint64_t* o_full = bars + 6;                                 // [2]
@@ -85,7 +87,7 @@ attention_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_
     const int lane = lane_id();
     const int NT = HP * p.NB;                                    // tiles per item
     const int my_items = p.items > (int)blockIdx.x ? (p.items - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
-    const bool sep = p.sep != 0;
+    constexpr bool sep = SEP;
 
     if (warp == 8 && lane == 0) { tma_prefetch_desc(&tmQKV); tma_prefetch_desc(&tmQKV64); }
     if (warp == 9) {
@@ -124,7 +126,7 @@ attention_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_
                 const int so = stage * kTileBytes;
                 mbar_wait(qe, (use & 1) ^ 1);
                 mbar_expect_tx(qf, (uint32_t)(p.NB + p.NKB) * kTileBytes);
-                if (p.pair) {
+                if (PAIR) {
                     // images 2b and 2b+1 in rows [0,64) and [64,128) of every operand tile (64-row boxes; rows t >= T and a
                     // second image beyond the batch are zero-filled by TMA)
                     for (int im = 0; im < 2; ++im) {
@@ -232,15 +234,15 @@ attention_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_
         const int row = q4 * 32 + lane;
         const uint32_t tlanes = tmem_base + ((uint32_t)(q4 * 32) << 16);
         // pair mode: rows [0,64) are image 0 and see key columns [0,64), rows [64,128) image 1 / columns [64,128)
-        const int img = p.pair ? (q4 >> 1) : 0;
+        const int img = PAIR ? (q4 >> 1) : 0;
         const int kbase = img * 64;                              // first key column of this row's image
-        const int klen = p.pair ? 64 : p.Npad;                   // key columns this row reads
-        const int lrow = p.pair ? (row & 63) : row;              // query index inside the image (before the tile offset)
+        const int klen = PAIR ? 64 : p.Npad;                   // key columns this row reads
+        const int lrow = PAIR ? (row & 63) : row;              // query index inside the image (before the tile offset)
         const uint32_t taddr = tlanes + (sep ? (uint32_t)(wg * p.s_stride) : (uint32_t)wg * 256u) + (uint32_t)kbase;   // S of this chain
         const uint32_t oaddr = tlanes + (sep ? (uint32_t)(2 * p.s_stride + wg * HD) : (uint32_t)wg * 256u);            // O of this chain
         const uint32_t pw = smem_u32(sP) + wg * 4 * kTileBytes;
         const float sl2 = p.scale * kLog2eF;
-        if (p.pair) {
+        if (PAIR) {
             // P is block diagonal: the key chunk of the OTHER image is never written by this row and must read as zero
             const uint32_t other = pw + (uint32_t)(1 - img) * kTileBytes;
 #pragma unroll
@@ -288,7 +290,7 @@ attention_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_
         for (int il = 0; il < my_items; ++il) {
             const int item = blockIdx.x + il * gridDim.x;
             const int b0 = item / p.slices_per_img, sl = item % p.slices_per_img;
-            const int b = p.pair ? 2 * b0 + img : b0;
+            const int b = PAIR ? 2 * b0 + img : b0;
             for (int t = 0; t < NT; ++t) {
                 const int g = il * NT + t;
                 if ((g & 1) != wg) continue;
@@ -473,7 +475,7 @@ struct HalfBlk {
 // with the element-wise work switched off entirely the decoder shape still took 329 of 349 us, SSL4P_ATTN_DEBUG ablation).
 constexpr int kAttnBwdThreads = kAttnThreads + 32;
 
-template <int HD>
+template <int HD, bool PAIR>
 __global__ void __launch_bounds__(kAttnBwdThreads, 1)
 attention_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CUtensorMap tmDO,
                         const __grid_constant__ CUtensorMap tmQKV64, const __grid_constant__ CUtensorMap tmDO64, const AttnBwdParams p) {
@@ -501,7 +503,7 @@ attention_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_
     uint64_t* dq_full = bars + 13;
     uint64_t* dq_empty = bars + 14;
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 15);
-    const bool ring = p.NB == 1;                                 // item il lives in stage il & 1, otherwise always stage 0
+    const bool ring = PAIR || p.NB == 1;                         // item il lives in stage il & 1, otherwise always stage 0
 
     const int warp = threadIdx.x >> 5;
     const int lane = lane_id();
@@ -538,7 +540,7 @@ attention_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_
                 const int stage = ring ? (il & 1) : 0, use = ring ? (il >> 1) : il;
                 mbar_wait(&in_empty[stage], (use & 1) ^ 1);
                 mbar_expect_tx(&in_full[stage], (uint32_t)(4 * p.NB) * kTileBytes);
-                if (p.pair) {                                     // images 2b, 2b+1 -> rows [0,64), [64,128) of every operand tile
+                if (PAIR) {                                     // images 2b, 2b+1 -> rows [0,64), [64,128) of every operand tile
                     for (int im = 0; im < 2; ++im) {
                         const int slot = stage * kTileBytes + im * (kTileBytes / 2);
                         tma_load_3d(sQ + slot, &tmQKV64, &in_full[stage], sl * 64, 0, 2 * b + im);
@@ -680,9 +682,9 @@ attention_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_
         // Deferred read-out of the TMEM gradient accumulators: it is done inside the NEXT half block, between its
         // arithmetic and its shared-memory stores, so the wait for the last dV/dK (dQ) MMAs hides behind useful work.
         int pend_kt = -1, pend_kt_hh = 0, pend_dq_hh = -1, pend_b = 0, pend_sl = 0;
-        const int img = p.pair ? (q4 >> 1) : 0;                  // pair mode: image of this thread's tile row
-        const int lrow = p.pair ? (row & 63) : row;              // token index of the row inside its image (before the tile offset)
-        if (p.pair) {
+        const int img = PAIR ? (q4 >> 1) : 0;                  // pair mode: image of this thread's tile row
+        const int lrow = PAIR ? (row & 63) : row;              // token index of the row inside its image (before the tile offset)
+        if (PAIR) {
             // P^T / dS^T are block diagonal: chunk h (queries of image h) is only ever written by the key rows of image h; the
             // rows of the other image must read as zero.  Warps 0-3 clear P^T, warps 4-7 dS^T.
             const uint32_t base = (half == 0 ? sPTa : sDSa) + (uint32_t)(1 - img) * kTileBytes;
@@ -691,7 +693,7 @@ attention_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_
         }
         auto write_dvk = [&]() {                                 // dV / dK of key tile pend_kt: warps 0-3 write dV, warps 4-7 dK
             const int key = pend_kt * 128 + lrow;
-            const int pb_ = p.pair ? 2 * pend_b + img : pend_b;
+            const int pb_ = PAIR ? 2 * pend_b + img : pend_b;
             const bool ok = key < p.T && pb_ < p.B;
             const int head = pend_sl * HP + pend_kt_hh;
             mbar_wait(dvk_full, wkt & 1);
@@ -723,7 +725,7 @@ attention_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_
             tc_fence_after();
             if (half < p.NB) {
                 const int q = half * 128 + lrow;
-                const int pb_ = p.pair ? 2 * pend_b + img : pend_b;
+                const int pb_ = PAIR ? 2 * pend_b + img : pend_b;
                 const bool ok = q < p.T && pb_ < p.B;
                 __nv_bfloat16* dst = p.dqkv + (size_t)(pb_ * p.T + q) * (3 * HHD) + head * HD;
                 if constexpr (HD == 64) {
@@ -753,11 +755,11 @@ attention_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_
             // thread are issued before the first use (one memory round trip per item).
             {
                 const int q = tid;                               // slot in the statistics arrays = query row of the tile(s)
-                const int qb = p.pair ? 2 * b + (q >> 6) : b;     // image and token of that slot
-                const int qt_ = p.pair ? (q & 63) : q;
+                const int qb = PAIR ? 2 * b + (q >> 6) : b;     // image and token of that slot
+                const int qt_ = PAIR ? (q & 63) : q;
                 uint4 ra[HP][HD / 8], rd[HP][HD / 8];
                 float lv[HP], dv[HP];
-                if (qt_ < p.T && qb < p.B && (!p.pair || q < 128) && !ABLATE(64)) {
+                if (qt_ < p.T && qb < p.B && (!PAIR || q < 128) && !ABLATE(64)) {
 #pragma unroll
                     for (int hh = 0; hh < HP; ++hh) {
                         const size_t off = ((size_t)(qb * p.T + qt_) * p.H + sl * HP + hh) * HD;
@@ -786,8 +788,8 @@ attention_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_
                 if (il + 1 < my_items) {
                     const int item2 = item + gridDim.x;
                     const int b2 = item2 / p.slices_per_img, s2 = item2 % p.slices_per_img;
-                    const int qb2 = p.pair ? 2 * b2 + (q >> 6) : b2;
-                    if (qt_ < p.T && qb2 < p.B && (!p.pair || q < 128)) {
+                    const int qb2 = PAIR ? 2 * b2 + (q >> 6) : b2;
+                    if (qt_ < p.T && qb2 < p.B && (!PAIR || q < 128)) {
                         const __nv_bfloat16* nxt = p.out + ((size_t)(qb2 * p.T + qt_) * p.H + s2 * HP) * HD;
                         asm volatile("prefetch.global.L2 [%0];" ::"l"(nxt));
                         asm volatile("prefetch.global.L2 [%0];" ::"l"(p.lse + ((size_t)qb2 * p.H + s2 * HP) * p.T + qt_));
@@ -802,7 +804,7 @@ attention_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_
             for (int hh = 0; hh < HP; ++hh) {
                 for (int kt = 0; kt < p.NB; ++kt) {
                     const int key = kt * 128 + lrow;
-                    const bool key_ok = key < p.T && (!p.pair || 2 * b + img < p.B);
+                    const bool key_ok = key < p.T && (!PAIR || 2 * b + img < p.B);
                     const bool keys_all_ok = __all_sync(0xffffffffu, key_ok);
                     for (int qt = 0; qt < p.NB; ++qt, ++nblk) {
                         const int nq = min(128, p.Npad - qt * 128);
@@ -811,7 +813,7 @@ attention_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_
                             const int nqh = h == 0 ? min(64, nq) : nq - 64;
                             const int c = half * 32;                            // this warp's 32 query columns of the half block
                             // pair mode: half block h holds the queries of image h; key rows of the other image stay zero
-                            const bool active = c < nqh && (!p.pair || img == h);
+                            const bool active = c < nqh && (!PAIR || img == h);
                             uint32_t pw[16], dw[16];
                             mbar_wait(&st_full[j % kNBuf], (j / kNBuf) & 1);
                             tc_fence_after();
@@ -953,9 +955,11 @@ static int launch_fwd_tc(const void* qkv, void* out, float* lse, int B, int T, i
     const bool fits = 2 * p.s_stride + 2 * HD <= 512;
     p.sep = (fits && p.NB >= 2) ? 1 : 0;
     if (const char* e = getenv("SSL4P_ATTN_SEP")) p.sep = (fits && e[0] != '0') ? 1 : 0;      // tests: force either TMEM plan
-    auto kern = attention_fwd_tc_kernel<HD>;
-    static bool attr = false;
-    if (!attr) { SSL4P_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kFwdSmem)); attr = true; }
+    auto kern = p.pair ? (p.sep ? attention_fwd_tc_kernel<HD, true, true> : attention_fwd_tc_kernel<HD, true, false>)
+                       : (p.sep ? attention_fwd_tc_kernel<HD, false, true> : attention_fwd_tc_kernel<HD, false, false>);
+    static bool attr[4] = {false, false, false, false};
+    const int ki = (p.pair ? 2 : 0) + (p.sep ? 1 : 0);
+    if (!attr[ki]) { SSL4P_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kFwdSmem)); attr[ki] = true; }
     const int grid = p.items < num_sms() ? p.items : num_sms();
     cudaError_t e = launch_ex(kern, dim3((unsigned)grid), dim3(kAttnThreads), (size_t)kFwdSmem, s, 1, tm, tm64, p);
     if (e != cudaSuccess) { set_error("attention_fwd_tc_kernel launch failed: %s", cudaGetErrorString(e)); return SSL4P_ERR_CUDA; }
@@ -983,9 +987,9 @@ static int launch_bwd_tc(const void* qkv, const void* out, const void* dout, con
     p.scale = scale; p.out = (const __nv_bfloat16*)out; p.dout = (const __nv_bfloat16*)dout; p.lse = lse; p.dqkv = (__nv_bfloat16*)dqkv;
     p.debug = 0;
     if (const char* e = getenv("SSL4P_ATTN_DEBUG")) p.debug = atoi(e);
-    auto kern = attention_bwd_tc_kernel<HD>;
-    static bool attr = false;
-    if (!attr) { SSL4P_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kBwdSmem)); attr = true; }
+    auto kern = p.pair ? attention_bwd_tc_kernel<HD, true> : attention_bwd_tc_kernel<HD, false>;
+    static bool attr[2] = {false, false};
+    if (!attr[p.pair]) { SSL4P_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kBwdSmem)); attr[p.pair] = true; }
     const int grid = p.items < num_sms() ? p.items : num_sms();
     cudaError_t e = launch_ex(kern, dim3((unsigned)grid), dim3(kAttnBwdThreads), (size_t)kBwdSmem, s, 1, tmQ, tmD, tmQ64, tmD64, p);
     if (e != cudaSuccess) { set_error("attention_bwd_tc_kernel launch failed: %s", cudaGetErrorString(e)); return SSL4P_ERR_CUDA; }
