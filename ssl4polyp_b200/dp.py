@@ -105,6 +105,7 @@ class BucketReducer:
         self.world = dist.get_world_size(group) if (dist.is_available() and dist.is_initialized()) else 1
         self.cuda = flat.is_cuda
         self.comm_stream = torch.cuda.Stream(device=flat.device) if (self.cuda and self.world > 1) else None
+        self.symm_group = getattr(flat, "_ssl4p_symm_group", None)     # symmetric-memory arena: in-switch all-reduce (experiment)
         self.bucket_of = {n: i for i, b in enumerate(buckets) for n in b.names}
         self.launch_order: list[int] = []
         self.producer_streams = None            # streams the gradients are produced on (None: the current stream)
@@ -152,7 +153,10 @@ class BucketReducer:
                     self.comm_stream.wait_event(ev)
                 with torch.cuda.stream(self.comm_stream):
                     if not _SKIP_COLLECTIVE:
-                        dist.all_reduce(view, op=dist.ReduceOp.SUM, group=self.group)
+                        if self.symm_group is not None:
+                            torch.ops.symm_mem.multimem_all_reduce_(view, "sum", self.symm_group)
+                        else:
+                            dist.all_reduce(view, op=dist.ReduceOp.SUM, group=self.group)
                     done = torch.cuda.Event()
                     done.record(self.comm_stream)
                 self._done[i] = [done]

@@ -96,7 +96,7 @@ class TrainEngine:
         dev = store.flat.device
         self.device = dev
         n = store.total
-        self.grads = torch.zeros(n, dtype=torch.float32, device=dev)
+        self.grads = self._alloc_grad_arena(n, dev, process_group)
         self.exp_avg = torch.zeros(n, dtype=torch.float32, device=dev)
         self.exp_avg_sq = torch.zeros(n, dtype=torch.float32, device=dev)
         self.nonfinite = torch.zeros(1, dtype=torch.int32, device=dev)
@@ -174,6 +174,22 @@ class TrainEngine:
             ops.adamw_flat_dev(self.store.flat, self.grads, self.exp_avg, self.exp_avg_sq, self.store.shadow, self.wd_flags,
                                self.hyper, b1, b2, self.eps, self.wd, grad_scale=1.0 / self.world, nonfinite=self.nonfinite)
         self.store.mark_shadow_fresh()
+
+    @staticmethod
+    def _alloc_grad_arena(n, dev, group):
+        """The gradient arena.  SSL4P_DP_SYMM=1 (experiment, world > 1): allocated as symmetric memory and exchanged with
+        torch's in-switch (NVLS multimem) all-reduce instead of NCCL - see dp.BucketReducer."""
+        import torch.distributed as dist
+        if (os.environ.get("SSL4P_DP_SYMM", "0") == "1" and dev.type == "cuda" and dist.is_available() and dist.is_initialized()
+                and dist.get_world_size(group) > 1):
+            import torch.distributed._symmetric_memory as symm_mem
+            g = group if group is not None else dist.group.WORLD
+            t = symm_mem.empty(n, dtype=torch.float32, device=dev)
+            symm_mem.rendezvous(t, g.group_name)
+            t.zero_()
+            t._ssl4p_symm_group = g.group_name
+            return t
+        return torch.zeros(n, dtype=torch.float32, device=dev)
 
     def _adamw_bucket(self, i: int, deps) -> None:
         """AdamW over bucket i's arena range on the optimiser stream, after `deps` (its all-reduce and the backward's
