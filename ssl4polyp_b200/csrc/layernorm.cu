@@ -134,6 +134,77 @@ layernorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const float* __restri
     }
 }
 
+// Same arithmetic (bit-identical sums), but the dgamma/dbeta/column-sum partials live in the warp's shared-memory slice
+// instead of 3*NV float4 registers per lane: <= 128 registers, two CTAs per SM, twice the loads in flight per SM.
+template <int NV>
+__global__ void __launch_bounds__(kLnWarps * 32, 2)
+layernorm_bwd_smem_kernel(const __nv_bfloat16* __restrict__ dy, const float* __restrict__ x, const float* __restrict__ mean_in,
+                          const float* __restrict__ rstd_in, const float* __restrict__ gamma, const float* __restrict__ res_grad,
+                          float* __restrict__ dx_out, __nv_bfloat16* __restrict__ dxb, float* __restrict__ part, int M, int D) {
+    extern __shared__ float s_red[];                           // [kLnWarps][3*D]
+    const int lane = lane_id();
+    const int warp = threadIdx.x >> 5;
+    pdl_wait_then_trigger();
+    const float inv_d = 1.0f / (float)D;
+    const float4* g4 = reinterpret_cast<const float4*>(gamma);
+    float4* sdg = reinterpret_cast<float4*>(s_red + (size_t)warp * 3 * D);
+    float4* sdb = sdg + D / 4;
+    float4* sds = sdg + D / 2;
+    float4 gam[NV];
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+        gam[i] = g4[lane + 32 * i];
+        sdg[lane + 32 * i] = make_float4(0, 0, 0, 0); sdb[lane + 32 * i] = make_float4(0, 0, 0, 0); sds[lane + 32 * i] = make_float4(0, 0, 0, 0);
+    }
+    // every lane only ever touches its own shared-memory words: no synchronisation inside the row loop
+    for (int row = blockIdx.x * kLnWarps + warp; row < M; row += gridDim.x * kLnWarps) {
+        const float4* xr = reinterpret_cast<const float4*>(x + (size_t)row * D);
+        const uint2* dyr = reinterpret_cast<const uint2*>(dy + (size_t)row * D);
+        const float mean = mean_in[row], rstd = rstd_in[row];
+        float4 xh[NV], gy[NV];
+        uint2 u[NV];
+#pragma unroll
+        for (int i = 0; i < NV; ++i) { xh[i] = xr[lane + 32 * i]; u[i] = dyr[lane + 32 * i]; }
+        float c1 = 0.f, c2 = 0.f;
+#pragma unroll
+        for (int i = 0; i < NV; ++i) {
+            const float2 d01 = unpack_bf16(u[i].x), d23 = unpack_bf16(u[i].y);
+            xh[i] = make_float4((xh[i].x - mean) * rstd, (xh[i].y - mean) * rstd, (xh[i].z - mean) * rstd, (xh[i].w - mean) * rstd);
+            float4 a = sdg[lane + 32 * i], b = sdb[lane + 32 * i];
+            a.x += d01.x * xh[i].x; a.y += d01.y * xh[i].y; a.z += d23.x * xh[i].z; a.w += d23.y * xh[i].w;
+            b.x += d01.x; b.y += d01.y; b.z += d23.x; b.w += d23.y;
+            sdg[lane + 32 * i] = a; sdb[lane + 32 * i] = b;
+            gy[i] = make_float4(d01.x * gam[i].x, d01.y * gam[i].y, d23.x * gam[i].z, d23.y * gam[i].w);
+            c1 += (gy[i].x + gy[i].y) + (gy[i].z + gy[i].w);
+            c2 += (gy[i].x * xh[i].x + gy[i].y * xh[i].y) + (gy[i].z * xh[i].z + gy[i].w * xh[i].w);
+        }
+        c1 = warp_sum(c1) * inv_d;
+        c2 = warp_sum(c2) * inv_d;
+        float4* dxr = reinterpret_cast<float4*>(dx_out + (size_t)row * D);
+        const float4* rr = res_grad ? reinterpret_cast<const float4*>(res_grad + (size_t)row * D) : nullptr;
+        uint2* dbr = dxb ? reinterpret_cast<uint2*>(dxb + (size_t)row * D) : nullptr;
+#pragma unroll
+        for (int i = 0; i < NV; ++i) {
+            float4 o;
+            o.x = rstd * (gy[i].x - c1 - xh[i].x * c2); o.y = rstd * (gy[i].y - c1 - xh[i].y * c2);
+            o.z = rstd * (gy[i].z - c1 - xh[i].z * c2); o.w = rstd * (gy[i].w - c1 - xh[i].w * c2);
+            if (rr) { const float4 r = rr[lane + 32 * i]; o.x += r.x; o.y += r.y; o.z += r.z; o.w += r.w; }
+            dxr[lane + 32 * i] = o;
+            float4 s = sds[lane + 32 * i];
+            s.x += o.x; s.y += o.y; s.z += o.z; s.w += o.w;
+            sds[lane + 32 * i] = s;
+            if (dbr) { uint2 b; b.x = pack_bf16(o.x, o.y); b.y = pack_bf16(o.z, o.w); dbr[lane + 32 * i] = b; }
+        }
+    }
+    __syncthreads();
+    for (int j = threadIdx.x; j < 3 * D; j += blockDim.x) {
+        float acc = 0.f;
+#pragma unroll
+        for (int w = 0; w < kLnWarps; ++w) acc += s_red[(size_t)w * 3 * D + j];
+        part[(size_t)blockIdx.x * 3 * D + j] = acc;
+    }
+}
+
 // generic-D backward (small test configurations): one warp per row, partial sums through shared-memory atomics are
 // avoided by giving every block a private [2*D] accumulator updated by one warp at a time in fixed order.
 __global__ void __launch_bounds__(kLnWarps * 32)
@@ -251,16 +322,25 @@ extern "C" int ssl4p_layernorm_bwd(const void* dy, const float* x, const float* 
         if (!attr && smem > 48 * 1024) { SSL4P_CUDA(cudaFuncSetAttribute(layernorm_bwd_kernel<NV_>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); attr = true; } \
         le = launch_ex(layernorm_bwd_kernel<NV_>, dim3(grid), dim3(threads), smem, STREAM, 1, dyb, x, mean, rstd, gamma, residual_grad, dx_out, dxbb, part, M, D); \
     }
+#define LN_BWD_SMEM(NV_)                                                                                                   \
+    {                                                                                                                      \
+        static bool attr = false;                                                                                          \
+        if (!attr) { SSL4P_CUDA(cudaFuncSetAttribute(layernorm_bwd_smem_kernel<NV_>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); attr = true; } \
+        le = launch_ex(layernorm_bwd_smem_kernel<NV_>, dim3(grid), dim3(threads), smem, STREAM, 1, dyb, x, mean, rstd, gamma, residual_grad, dx_out, dxbb, part, M, D); \
+    }
+    // SSL4P_LN_BWD_SMEM=0 keeps the register-resident sums (one CTA per SM) for D >= 768
+    static const bool smem_acc = getenv("SSL4P_LN_BWD_SMEM") ? atoi(getenv("SSL4P_LN_BWD_SMEM")) != 0 : true;
     switch (D) {
         case 512: LN_BWD(4) break;
-        case 768: LN_BWD(6) break;
-        case 1024: LN_BWD(8) break;
+        case 768: if (smem_acc) LN_BWD_SMEM(6) else LN_BWD(6) break;
+        case 1024: if (smem_acc) LN_BWD_SMEM(8) else LN_BWD(8) break;
         default: {
             SSL4P_REQUIRE(smem <= 48 * 1024, "layernorm_bwd: generic path supports D <= 512");
             le = launch_ex(layernorm_bwd_generic_kernel, dim3(grid), dim3(threads), smem, STREAM, 1, dyb, x, mean, rstd, gamma, residual_grad, dx_out, dxbb, part, M, D);
         }
     }
 #undef LN_BWD
+#undef LN_BWD_SMEM
     if (le != cudaSuccess) { set_error("layernorm_bwd_kernel launch failed: %s", cudaGetErrorString(le)); return SSL4P_ERR_CUDA; }
     int rc = check_launch("layernorm_bwd_kernel");
     if (rc) return rc;
