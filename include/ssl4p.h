@@ -167,6 +167,15 @@ int ssl4p_layernorm_bwd(const void* dy_bf16, const float* x, const float* mean, 
                         float* dx_colsum, int M, int D, int accumulate, int accumulate_colsum,
                         void* workspace, size_t workspace_bytes, void* stream);
 size_t ssl4p_layernorm_bwd_workspace_bytes(int M, int D);
+/* Allocation-free variant of ssl4p_layernorm_bwd.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops).  Same arguments and results
+ * minus the workspace: the [grid][3*D] partial sums live in a file-scope device array (3.47 MiB per GPU that loads the
+ * library, held until exit).  Limit: D <= ssl4p_layernorm_bwd_max_static_d() (1024); larger D returns SSL4P_ERR_ARG.
+ * Calls no cudaMalloc/cudaFree.  All calls share the array: calls that overlap on the GPU (different streams) race. */
+int ssl4p_layernorm_bwd_static(const void* dy_bf16, const float* x, const float* mean, const float* rstd, const float* gamma,
+                               const float* residual_grad, float* dx_out, void* dxb_bf16, float* dgamma, float* dbeta,
+                               float* dx_colsum, int M, int D, int accumulate, int accumulate_colsum, void* stream);
+int ssl4p_layernorm_bwd_max_static_d(void);
 
 /* Multi-head self-attention of timm 0.4.12 Attention.forward (softmax(q k^T * scale) v), fused, per (batch, head).
  * qkv: bf16 [B, T, 3, H, hd] (the qkv Linear output as-is); out: bf16 [B, T, H*hd]; lse: fp32 [B, H, T]. */

@@ -348,3 +348,35 @@ extern "C" int ssl4p_layernorm_bwd(const void* dy, const float* x, const float* 
     if (le != cudaSuccess) { set_error("ln_param_grad_reduce_kernel launch failed: %s", cudaGetErrorString(le)); return SSL4P_ERR_CUDA; }
     return check_launch("ln_param_grad_reduce_kernel");
 }
+
+// ---- allocation-free variant (no counterpart in the reference) ----------
+// The [grid][3*D] partial-sum scratch of the backward lives in a file-scope device array, so callers that cannot call
+// cudaMalloc (graph capture, tight serving loops) need no workspace.  Limit: D <= 1024 (and grid <= 296 partial rows), 3.47 MiB
+// held by every GPU that loads the library.  The kernel overwrites every partial row it later reduces, so nothing has to
+// be cleared between calls; all calls share the array, so calls that overlap on the GPU (different streams) race.
+constexpr int kLnStaticMaxD = 1024;
+constexpr int kLnStaticMaxRows = 2 * 148;
+static __device__ __align__(256) float g_ln_bwd_scratch[(size_t)kLnStaticMaxRows * 3 * kLnStaticMaxD];
+
+extern "C" int ssl4p_layernorm_bwd_max_static_d(void) { return kLnStaticMaxD; }
+
+extern "C" int ssl4p_layernorm_bwd_static(const void* dy, const float* x, const float* mean, const float* rstd, const float* gamma,
+                                          const float* residual_grad, float* dx_out, void* dxb, float* dgamma, float* dbeta,
+                                          float* dx_colsum, int M, int D, int accumulate, int accumulate_colsum, void* stream) {
+    SSL4P_REQUIRE(D > 0 && D <= kLnStaticMaxD, "layernorm_bwd_static: D=%d exceeds the static scratch limit (D <= %d); use ssl4p_layernorm_bwd with a caller workspace", D, kLnStaticMaxD);
+    // the array's name is a host-side stand-in: resolve the device address once per device, with that device current
+    constexpr int kMaxDevices = 64;
+    static float* addr[kMaxDevices] = {};
+    int dev = 0;
+    SSL4P_CUDA(cudaGetDevice(&dev));
+    SSL4P_REQUIRE(dev >= 0 && dev < kMaxDevices, "layernorm_bwd_static: device ordinal %d out of range", dev);
+    if (addr[dev] == nullptr) {
+        float* p = nullptr;
+        SSL4P_CUDA(cudaGetSymbolAddress((void**)&p, g_ln_bwd_scratch));
+        SSL4P_REQUIRE(p != nullptr, "layernorm_bwd_static: cudaGetSymbolAddress returned a null address");
+        addr[dev] = p;
+    }
+    // same launches as ssl4p_layernorm_bwd; it rejects a grid whose partial rows would not fit in the array
+    return ssl4p_layernorm_bwd(dy, x, mean, rstd, gamma, residual_grad, dx_out, dxb, dgamma, dbeta, dx_colsum, M, D, accumulate,
+                               accumulate_colsum, addr[dev], sizeof(float) * (size_t)kLnStaticMaxRows * 3 * kLnStaticMaxD, stream);
+}
