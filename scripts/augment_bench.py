@@ -59,6 +59,14 @@ for r in range(5):
     tf(frames, augment=aug, out=out)
 torch.cuda.synchronize()
 e2e_ms = (time.perf_counter() - t0) / 5 * 1e3
+for r in range(2):
+    tf(frames, out=out)
+torch.cuda.synchronize()
+t0 = time.perf_counter()
+for r in range(5):
+    tf(frames, out=out)                                  # parameters drawn per call (9 torch RNG calls per image, torchvision's order)
+torch.cuda.synchronize()
+e2e_draw_ms = (time.perf_counter() - t0) / 5 * 1e3
 from PIL import Image
 import torchvision.transforms as T
 comp = T.Compose([T.Resize((224, 224)), T.ColorJitter(brightness=0.4, contrast=0.5, saturation=0.25, hue=0.01), T.GaussianBlur((25, 25), sigma=(0.001, 2.0)),
@@ -72,6 +80,8 @@ cpu_ms = (time.perf_counter() - t0) / len(pil) * 1e3
 dev_ms = sum(per_kernel.values())
 print(json.dumps({"metric": "fine-tune train augmentation images/s", "frame": args.frame, "batch": args.batch, **per_kernel,
                   "device_ms_per_batch_after_resize": dev_ms, "value": args.batch / dev_ms * 1e3,
-                  "e2e_ms_per_batch": e2e_ms, "e2e_images_per_s": args.batch / e2e_ms * 1e3, "h2d_bytes_per_batch": tf.h2d_bytes,
+                  "e2e_ms_per_batch": e2e_ms, "e2e_images_per_s": args.batch / e2e_ms * 1e3,
+                  "e2e_with_draws_ms_per_batch": e2e_draw_ms, "e2e_with_draws_images_per_s": args.batch / e2e_draw_ms * 1e3,
+                  "pack_threads": tf._pack_threads, "h2d_bytes_per_batch": tf.h2d_bytes,
                   "cpu_baseline": {"kind": "reference (Pillow + torchvision Compose, stage 'train')", "cores": 1, "ms_per_image": cpu_ms,
                                    "images_per_s": 1e3 / cpu_ms, "sample": f"{len(pil)} frames"}}))

@@ -66,6 +66,8 @@ class TrainTransform:
         from concurrent.futures import ThreadPoolExecutor
         nt = 1 if pack_threads is None else int(pack_threads)      # measured: one thread is fastest (scripts/input_bench.py)
         self._pool = ThreadPoolExecutor(max_workers=nt) if nt > 1 else None
+        self._pack_threads = nt
+        self._numpy_pack = False                         # True: pack with numpy slice copies (one core each, GIL released)
         self.last_params = []
         self.h2d_bytes = 0
 
@@ -91,9 +93,10 @@ class TrainTransform:
             return torch.empty(0, 3, self.size, self.size, dtype=torch.float32, device=self.device)
         return ops.crop_resize_normalize(dev, desc_dev, self.size, max_crop, self.mean, self.std, out=out, filter=self.filter)
 
-    def _upload(self, frames, params=None):
+    def _upload(self, frames, params=None, overlap=None):
         """Draw (or take) the crop parameters, pack the crop rectangles into a pinned buffer, one H2D copy.
-        -> (device bytes, device descriptors int64 [N,8], largest crop extent, N)"""
+        -> (device bytes, device descriptors int64 [N,8], largest crop extent, N).  `overlap`: a callable run on the calling
+        thread while the pool threads copy (the copies release the GIL); its result is left in `self._overlap_result`."""
         frames = [f.numpy() if isinstance(f, torch.Tensor) else np.asarray(f) for f in frames]
         for f in frames:
             if f.dtype != np.uint8 or f.ndim != 3 or f.shape[2] != 3:
@@ -112,16 +115,34 @@ class TrainTransform:
         desc = torch.from_numpy(rows)
         k, stage = self._staging(max(total, 1))
 
+        stage_np = stage.numpy() if self._numpy_pack else None
+
         def pack(i):
             top, left, h, w, _flip = params[i]
             o = int(rows[i, 0])
-            stage[o:o + h * w * 3].view(h, w, 3).copy_(torch.from_numpy(frames[i])[top:top + h, left:left + w])
+            if stage_np is not None:
+                stage_np[o:o + h * w * 3].reshape(h, w, 3)[...] = frames[i][top:top + h, left:left + w]
+            else:
+                stage[o:o + h * w * 3].view(h, w, 3).copy_(torch.from_numpy(frames[i])[top:top + h, left:left + w])
 
-        if self._pool is not None and n > 1:
-            list(self._pool.map(pack, range(n)))          # strided memcpys: the GIL is released inside copy_
-        else:
-            for i in range(n):
+        def pack_range(r):
+            for i in r:
                 pack(i)
+
+        self._overlap_result = None
+        if self._pool is not None and n > 1:               # strided memcpys: the GIL is released inside the copies
+            nt = min(self._pack_threads, n)
+            futures = [self._pool.submit(pack_range, range(k * n // nt, (k + 1) * n // nt)) for k in range(nt)]
+            try:
+                if overlap is not None:
+                    self._overlap_result = overlap()
+            finally:
+                for f in futures:
+                    f.result()
+        else:
+            pack_range(range(n))
+            if overlap is not None:
+                self._overlap_result = overlap()
         dev = torch.empty(max(total, 1), dtype=torch.uint8, device=self.device)
         dev.copy_(stage[:max(total, 1)], non_blocking=True)
         desc_dev = desc.pin_memory().to(self.device, non_blocking=True)
@@ -145,10 +166,15 @@ class EvalTransform(TrainTransform):
         return 0, 0, height, width, False
 
 
+_GAUSS_X: dict = {}
+
+
 def _gaussian_kernel1d(ksize: int, sigma: float) -> torch.Tensor:
     """torchvision _get_gaussian_kernel1d, the same float32 CPU ops call for call (25 host-side scalars per image)."""
-    half = (ksize - 1) * 0.5
-    x = torch.linspace(-half, half, steps=ksize, dtype=torch.float32)
+    x = _GAUSS_X.get(ksize)
+    if x is None:
+        half = (ksize - 1) * 0.5
+        x = _GAUSS_X[ksize] = torch.linspace(-half, half, steps=ksize, dtype=torch.float32)
     pdf = torch.exp(-0.5 * (x / sigma).pow(2))
     return pdf / pdf.sum()
 
@@ -188,8 +214,18 @@ class TrainAugment(EvalTransform):
     flip + rotation gather with ToTensor / Normalize).  `last_augment` holds the drawn parameters per image."""
 
     def __init__(self, size: int = 224, brightness=0.4, contrast=0.5, saturation=0.25, hue=0.01, kernel_size=25,
-                 sigma=(0.001, 2.0), degrees=180.0, flip_p: float = 0.5, mean=IMAGENET_MEAN, std=IMAGENET_STD, device=None):
+                 sigma=(0.001, 2.0), degrees=180.0, flip_p: float = 0.5, mean=IMAGENET_MEAN, std=IMAGENET_STD, device=None,
+                 pack_threads=None):
         super().__init__(size, mean=mean, std=std, device=device)
+        # Whole frames travel (1.2 MB each at 576x720): numpy slice copies on up to 8 threads (measured on the B200 host, 16
+        # cores, 128 frames: torch copy_ 4.6 ms, numpy x8 2.9 ms), with the parameter draws and their packing - Python-bound -
+        # on the calling thread meanwhile (scripts/augment_host_probe.py).
+        import os
+        from concurrent.futures import ThreadPoolExecutor
+        nt = min(8, os.cpu_count() or 1) if pack_threads is None else int(pack_threads)
+        self._pack_threads = max(1, nt)
+        self._pool = ThreadPoolExecutor(max_workers=self._pack_threads) if self._pack_threads > 1 else None
+        self._numpy_pack = True
         if kernel_size % 2 == 0 or kernel_size > ops.AUG_MAX_TAPS:
             raise RuntimeError(f"TrainAugment: kernel_size must be odd and <= {ops.AUG_MAX_TAPS}")
         self.brightness = (max(0.0, 1 - brightness), 1 + brightness)      # ColorJitter._check_input
@@ -216,26 +252,34 @@ class TrainAugment(EvalTransform):
         n = len(aug)
         ints = np.zeros((n, ops.AUG_PARAM_INTS), np.int32)
         taps = torch.zeros(n, ops.AUG_MAX_TAPS, dtype=torch.float32)
+        if n == 0:
+            return torch.from_numpy(ints), taps
         S = self.size
-        for i, a in enumerate(aug):
-            ints[i, 0:4] = a["order"]
-            ints[i, 4] = int(np.int32(a["hue"] * 255).astype(np.uint8))    # adjust_hue: truncation toward zero, uint8 wrap
-            ints[i, 5], ints[i, 6] = int(a["hflip"]), int(a["vflip"])
-            mode, coef = _rotate_coeffs(a["angle"], S, S)
-            ints[i, 7] = mode
-            ints[i, 8:14] = coef
-            ints[i, 16:19] = np.array([a["brightness"], a["contrast"], a["saturation"]], np.float32).view(np.int32)
-            taps[i, :self.kernel_size] = _gaussian_kernel1d(self.kernel_size, a["sigma"])
+        ints[:, 0:4] = [a["order"] for a in aug]
+        # adjust_hue: hue * 255 in doubles, truncation toward zero, uint8 wrap
+        ints[:, 4] = (np.array([a["hue"] for a in aug], np.float64) * 255).astype(np.int32).astype(np.uint8)
+        ints[:, 5] = [int(a["hflip"]) for a in aug]
+        ints[:, 6] = [int(a["vflip"]) for a in aug]
+        rot = [_rotate_coeffs(a["angle"], S, S) for a in aug]
+        ints[:, 7] = [m for m, _ in rot]
+        ints[:, 8:14] = [c for _, c in rot]
+        ints[:, 16:19] = np.array([(a["brightness"], a["contrast"], a["saturation"]) for a in aug], np.float32).view(np.int32)
+        # the blur taps stay one torchvision-identical float32 op sequence per image (a batched exp / sum could round differently)
+        taps[:, :self.kernel_size] = torch.stack([_gaussian_kernel1d(self.kernel_size, a["sigma"]) for a in aug])
         return torch.from_numpy(ints), taps
 
     def __call__(self, frames, augment=None, out=None, want_u8=False):
-        dev, desc_dev, max_crop, n = self._upload(frames)
+        frames = list(frames)
+        n_frames = len(frames)
+
+        def draw_and_pack():                             # Python-bound: runs while the pool threads copy the frames
+            aug = augment if augment is not None else [self.draw_augment() for _ in range(n_frames)]
+            return list(aug), self.pack_augment(aug)
+
+        dev, desc_dev, max_crop, n = self._upload(frames, overlap=draw_and_pack)
         if n == 0:
             return torch.empty(0, 3, self.size, self.size, dtype=torch.float32, device=self.device)
-        if augment is None:
-            augment = [self.draw_augment() for _ in range(n)]
-        self.last_augment = list(augment)
-        ints, taps = self.pack_augment(augment)
+        self.last_augment, (ints, taps) = self._overlap_result
         ints_d = ints.pin_memory().to(self.device, non_blocking=True)
         taps_d = taps.pin_memory().to(self.device, non_blocking=True)
         self.h2d_bytes += ints.numel() * 4 + taps.numel() * 4
