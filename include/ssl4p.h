@@ -102,6 +102,14 @@ int ssl4p_crop_resize_normalize_u8(const void* frames, const long long* desc, in
 int ssl4p_crop_resize_u8(const void* frames, const long long* desc, int N, int S, int max_crop, int filter,
                          void* out_u8, void* workspace, size_t workspace_bytes, void* stream);
 
+/* Host side of the upload: copy N rectangles of uint8 rows (rectangle i: rows[i] rows of row_bytes[i] bytes, row r at
+ * src[i] + r * src_pitch[i]) to dst + dst_offset[i], rows packed back to back, with memcpy on `threads` host threads (byte-
+ * balanced, cut at row boundaries).  dst is the caller's pinned staging buffer.  The reference does this work per sample on
+ * DataLoader workers (classification/data/transforms.py:233-258; models/mae/main_pretrain.py:156-175); here it is one call per
+ * batch, so a ctypes caller releases its interpreter lock once and draws the batch's random parameters meanwhile.  No CUDA. */
+int ssl4p_host_pack_rects(const void* const* src, const long long* src_pitch, const long long* rows, const long long* row_bytes,
+                          void* dst, const long long* dst_offset, int n, int threads);
+
 /* ------------------------------------------------------------------------------------------------
  * Fine-tune TRAIN augmentations (classification/data/transforms.py:233-258, stage 'train': ColorJitter(0.4, 0.5, 0.25,
  * 0.01) -> GaussianBlur((25,25), sigma=(0.001,2)) -> RandomHorizontalFlip -> RandomVerticalFlip -> RandomRotation(180) ->

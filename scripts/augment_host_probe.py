@@ -72,3 +72,49 @@ for i in range(N):
 desc = torch.from_numpy(rows).cuda()
 res["resize_ms"] = ev(lambda: ops.crop_resize_u8(dev, desc, 224, max(H, W), filter="bilinear"))
 print(json.dumps(res))
+
+# ---- second part: the Python-bound parameter work, alone and under the copy threads; the device side alone
+from ssl4polyp_b200.input_pipeline import TrainAugment, IMAGENET_MEAN, IMAGENET_STD
+tf = TrainAugment(224)
+torch.manual_seed(0)
+aug = [tf.draw_augment() for _ in range(N)]
+res2 = {"draw_ms": t(lambda: [tf.draw_augment() for _ in range(N)]), "pack_augment_ms": t(lambda: tf.pack_augment(aug))}
+pool = ThreadPoolExecutor(8)
+ch = [range(k * N // 8, (k + 1) * N // 8) for k in range(8)]
+
+
+def both():
+    fs = [pool.submit(rng_of(pack_n), r) for r in ch]
+    tf.pack_augment(aug)
+    for f in fs:
+        f.result()
+
+
+res2["numpy_8_chunked_with_pack_augment_ms"] = t(both)
+ints, taps = tf.pack_augment(aug)
+ints_d, taps_d = ints.cuda(), taps.cuda()
+out = torch.empty(N, 3, 224, 224, device="cuda")
+
+
+def device_side():
+    d = torch.empty(N * sz, dtype=torch.uint8, device="cuda")
+    d.copy_(stage, non_blocking=True)
+    img = ops.crop_resize_u8(d, desc, 224, max(H, W), filter="bilinear")
+    ops.color_jitter_u8(img, ints_d, out=img)
+    b = ops.gaussian_blur_u8(img, taps_d, 25)
+    ops.flip_rotate_normalize_u8(b, ints_d, IMAGENET_MEAN, IMAGENET_STD, out=out)
+
+
+res2["device_side_ms"] = ev(device_side)
+
+
+def device_and_host():
+    device_side()
+    both()
+
+
+res2["device_side_while_host_packs_ms"] = ev(device_and_host)
+frames_l = frames
+res2["call_predrawn_ms"] = ev(lambda: tf(frames_l, augment=aug, out=out))
+res2["call_with_draws_ms"] = ev(lambda: tf(frames_l, out=out))
+print(json.dumps(res2))

@@ -45,6 +45,7 @@ SIGNATURES = {
     "ssl4p_layernorm_fwd": (i32, [vp, vp, vp, f32, vp, vp, vp, i32, i32, vp]),
     "ssl4p_layernorm_bwd": (i32, [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, vp, sz, vp]),
     "ssl4p_layernorm_bwd_workspace_bytes": (sz, [i32, i32]),
+    "ssl4p_host_pack_rects": (i32, [vp, vp, vp, vp, vp, vp, i32, i32]),
     "ssl4p_layernorm_bwd_static": (i32, [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, vp]),
     "ssl4p_layernorm_bwd_max_static_d": (i32, []),
     "ssl4p_attention_fwd": (i32, [vp, vp, vp, i32, i32, i32, i32, f32, vp]),

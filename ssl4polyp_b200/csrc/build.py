@@ -17,7 +17,7 @@ PKG = os.path.dirname(HERE)
 ROOT = os.path.dirname(PKG)
 OBJ_DIR = os.path.join(HERE, "build")
 LIB_PATH = os.path.join(PKG, "libssl4p.so")
-SOURCES = ["api.cu", "gemm_tcgen05.cu", "tokens.cu", "layernorm.cu", "attention_tc.cu", "loss.cu", "optim.cu", "input_pipeline.cu", "augment.cu"]
+SOURCES = ["api.cu", "gemm_tcgen05.cu", "tokens.cu", "layernorm.cu", "attention_tc.cu", "loss.cu", "optim.cu", "input_pipeline.cu", "augment.cu", "host_pack.cu"]
 HEADERS = [os.path.join(HERE, "common.cuh"), os.path.join(HERE, "attn_common.cuh"), os.path.join(ROOT, "include", "ssl4p.h")]
 # test infrastructure: an independent on-device implementation the product kernels are cross-checked against (tests only)
 CHECK_DIR = os.path.join(ROOT, "tests", "csrc")

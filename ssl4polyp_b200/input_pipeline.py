@@ -67,7 +67,8 @@ class TrainTransform:
         nt = 1 if pack_threads is None else int(pack_threads)      # measured: one thread is fastest (scripts/input_bench.py)
         self._pool = ThreadPoolExecutor(max_workers=nt) if nt > 1 else None
         self._pack_threads = nt
-        self._numpy_pack = False                         # True: pack with numpy slice copies (one core each, GIL released)
+        self._native_pack = False                        # True: one ssl4p_host_pack_rects call per batch (host threads, no GIL)
+        self._pack_exec = None
         self.last_params = []
         self.h2d_bytes = 0
 
@@ -115,22 +116,34 @@ class TrainTransform:
         desc = torch.from_numpy(rows)
         k, stage = self._staging(max(total, 1))
 
-        stage_np = stage.numpy() if self._numpy_pack else None
-
         def pack(i):
             top, left, h, w, _flip = params[i]
             o = int(rows[i, 0])
-            if stage_np is not None:
-                stage_np[o:o + h * w * 3].reshape(h, w, 3)[...] = frames[i][top:top + h, left:left + w]
-            else:
-                stage[o:o + h * w * 3].view(h, w, 3).copy_(torch.from_numpy(frames[i])[top:top + h, left:left + w])
+            stage[o:o + h * w * 3].view(h, w, 3).copy_(torch.from_numpy(frames[i])[top:top + h, left:left + w])
 
         def pack_range(r):
             for i in r:
                 pack(i)
 
         self._overlap_result = None
-        if self._pool is not None and n > 1:               # strided memcpys: the GIL is released inside the copies
+        if self._native_pack and n > 0:
+            # one C call copies every rectangle on `_pack_threads` host threads; it runs on a helper thread (ctypes drops the
+            # GIL for the whole call), so `overlap` - Python-bound - really runs beside the copies
+            frames = [f if (f.strides[2] == 1 and f.strides[1] == 3 and f.strides[0] >= 3 * f.shape[1]) else np.ascontiguousarray(f) for f in frames]
+            src = np.array([f.__array_interface__["data"][0] + p_[0] * f.strides[0] + p_[1] * 3 for f, p_ in zip(frames, params)], np.uint64)
+            pitch = np.array([f.strides[0] for f in frames], np.int64)
+            nrows = np.array([p_[2] for p_ in params], np.int64)
+            row_bytes = np.array([p_[3] * 3 for p_ in params], np.int64)
+            offs = np.ascontiguousarray(rows[:, 0])
+            lib = ops._lib.load()
+            fut = self._pack_exec.submit(lib.ssl4p_host_pack_rects, src.ctypes.data, pitch.ctypes.data, nrows.ctypes.data, row_bytes.ctypes.data,
+                                         stage.data_ptr(), offs.ctypes.data, n, self._pack_threads)
+            try:
+                if overlap is not None:
+                    self._overlap_result = overlap()
+            finally:
+                ops._lib.check(fut.result(), "host_pack_rects")
+        elif self._pool is not None and n > 1:             # strided memcpys: the GIL is released inside the copies
             nt = min(self._pack_threads, n)
             futures = [self._pool.submit(pack_range, range(k * n // nt, (k + 1) * n // nt)) for k in range(nt)]
             try:
@@ -217,15 +230,17 @@ class TrainAugment(EvalTransform):
                  sigma=(0.001, 2.0), degrees=180.0, flip_p: float = 0.5, mean=IMAGENET_MEAN, std=IMAGENET_STD, device=None,
                  pack_threads=None):
         super().__init__(size, mean=mean, std=std, device=device)
-        # Whole frames travel (1.2 MB each at 576x720): numpy slice copies on up to 8 threads (measured on the B200 host, 16
-        # cores, 128 frames: torch copy_ 4.6 ms, numpy x8 2.9 ms), with the parameter draws and their packing - Python-bound -
-        # on the calling thread meanwhile (scripts/augment_host_probe.py).
+        # Whole frames travel (1.2 MB each at 576x720): one ssl4p_host_pack_rects call copies the batch on up to 8 host threads
+        # (measured on the B200 host, 16 cores, 128 frames: torch copy_ 4.6 ms, 8 threads 2.9 ms) while the parameter draws and
+        # their packing - Python-bound - run on the calling thread (scripts/augment_host_probe.py: Python threads around numpy
+        # copies did not overlap with that work, the interpreter lock changed hands once per frame).
         import os
         from concurrent.futures import ThreadPoolExecutor
         nt = min(8, os.cpu_count() or 1) if pack_threads is None else int(pack_threads)
         self._pack_threads = max(1, nt)
-        self._pool = ThreadPoolExecutor(max_workers=self._pack_threads) if self._pack_threads > 1 else None
-        self._numpy_pack = True
+        self._pool = None
+        self._pack_exec = ThreadPoolExecutor(max_workers=1)
+        self._native_pack = True
         if kernel_size % 2 == 0 or kernel_size > ops.AUG_MAX_TAPS:
             raise RuntimeError(f"TrainAugment: kernel_size must be odd and <= {ops.AUG_MAX_TAPS}")
         self.brightness = (max(0.0, 1 - brightness), 1 + brightness)      # ColorJitter._check_input
@@ -234,17 +249,25 @@ class TrainAugment(EvalTransform):
         self.hue = (-hue, hue)
         self.kernel_size, self.sigma, self.degrees, self.flip_p = kernel_size, sigma, float(degrees), flip_p
         self.last_augment = []
+        self._scratch: dict = {}
 
     def draw_augment(self) -> dict:
-        order = [int(v) for v in torch.randperm(4)]                        # ColorJitter.get_params
-        b = float(torch.empty(1).uniform_(self.brightness[0], self.brightness[1]))
-        c = float(torch.empty(1).uniform_(self.contrast[0], self.contrast[1]))
-        s = float(torch.empty(1).uniform_(self.saturation[0], self.saturation[1]))
-        h = float(torch.empty(1).uniform_(self.hue[0], self.hue[1]))
-        sg = torch.empty(1).uniform_(self.sigma[0], self.sigma[1]).item()    # GaussianBlur.get_params
-        hflip = bool(torch.rand(1) < self.flip_p)
-        vflip = bool(torch.rand(1) < self.flip_p)
-        angle = float(torch.empty(1).uniform_(-self.degrees, self.degrees).item())   # RandomRotation.get_params
+        # torchvision draws every scalar as torch.empty(1).uniform_(lo, hi) / torch.rand(1): a one-element tensor of the default
+        # dtype filled from the global generator.  The same fill on one reused scratch tensor consumes the generator identically
+        # and yields the same value (rand(1) is uniform_(0, 1)); it saves ~1400 tensor allocations per batch of 128.
+        u = self._scratch.get(torch.get_default_dtype())
+        if u is None:
+            u = self._scratch[torch.get_default_dtype()] = torch.empty(1)
+            self._flip_thr = float(torch.tensor(self.flip_p, dtype=u.dtype))      # `rand(1) < p` compares in the tensor's dtype
+        order = torch.randperm(4).tolist()                                 # ColorJitter.get_params
+        b = u.uniform_(self.brightness[0], self.brightness[1]).item()
+        c = u.uniform_(self.contrast[0], self.contrast[1]).item()
+        s = u.uniform_(self.saturation[0], self.saturation[1]).item()
+        h = u.uniform_(self.hue[0], self.hue[1]).item()
+        sg = u.uniform_(self.sigma[0], self.sigma[1]).item()               # GaussianBlur.get_params
+        hflip = u.uniform_(0.0, 1.0).item() < self._flip_thr
+        vflip = u.uniform_(0.0, 1.0).item() < self._flip_thr
+        angle = u.uniform_(-self.degrees, self.degrees).item()             # RandomRotation.get_params
         return dict(order=order, brightness=b, contrast=c, saturation=s, hue=h, sigma=sg, hflip=hflip, vflip=vflip, angle=angle)
 
     def pack_augment(self, aug: list):

@@ -595,3 +595,43 @@ def test_augment_oracle_matches_torchvision_golden():
     assert np.array_equal(IO.rotate_nearest(img, 90.0), np.rot90(img, 1))
     assert np.array_equal(IO.gaussian_blur_u8(img, IO.gaussian_kernel1d(25, 0.001)), img)          # delta kernel
     assert np.array_equal(IO.adjust_brightness(img, 1.0), img) and np.array_equal(IO.adjust_saturation(img, 1.0), img)
+
+
+def test_host_pack_rects_matches_numpy_slices_on_every_thread_count():
+    """ssl4p_host_pack_rects (the host side of the frame upload, no CUDA): ragged crop rectangles of ragged frames, offset
+    views, one-row and one-column boxes, byte-balanced over 1..16 threads, against numpy slicing."""
+    import numpy as np
+    from ssl4polyp_b200 import _lib
+    lib = _lib.load()
+    rng = np.random.default_rng(5)
+    frames = [rng.integers(0, 256, (int(rng.integers(200, 600)), int(rng.integers(200, 700)), 3), dtype=np.uint8) for _ in range(24)]
+    frames[2] = frames[2][7:, :]                                   # a view that does not start at its buffer
+    params = []
+    for fr in frames:
+        H, W = fr.shape[:2]
+        h, w = int(rng.integers(1, H + 1)), int(rng.integers(1, W + 1))
+        params.append((int(rng.integers(0, H - h + 1)), int(rng.integers(0, W - w + 1)), h, w))
+    params[0] = (0, 0) + frames[0].shape[:2]                       # a whole frame: one memcpy
+    params[1] = (3, 5, 1, frames[1].shape[1] - 5)                  # one row
+    params[4] = (0, 9, frames[4].shape[0], 1)                      # one column
+    sizes = [p[2] * p[3] * 3 for p in params]
+    offs = np.cumsum([0] + sizes).astype(np.int64)
+    total = int(offs[-1])
+    assert total > (1 << 20)                                       # beyond the single-thread cut-off
+    want = np.concatenate([fr[t:t + h, l:l + w].reshape(-1) for fr, (t, l, h, w) in zip(frames, params)])
+    src = np.array([fr.__array_interface__["data"][0] + t * fr.strides[0] + l * 3 for fr, (t, l, h, w) in zip(frames, params)], np.uint64)
+    pitch = np.array([fr.strides[0] for fr in frames], np.int64)
+    nrows = np.array([p[2] for p in params], np.int64)
+    row_bytes = np.array([p[3] * 3 for p in params], np.int64)
+    o = np.ascontiguousarray(offs[:-1])
+    for threads in (1, 2, 3, 7, 8, 16):
+        dst = np.full(total + 64, 7, np.uint8)
+        rc = lib.ssl4p_host_pack_rects(src.ctypes.data, pitch.ctypes.data, nrows.ctypes.data, row_bytes.ctypes.data, dst.ctypes.data,
+                                       o.ctypes.data, len(frames), threads)
+        assert rc == 0, lib.ssl4p_last_error()
+        assert np.array_equal(dst[:total], want), threads
+        assert (dst[total:] == 7).all()
+    assert lib.ssl4p_host_pack_rects(src.ctypes.data, pitch.ctypes.data, nrows.ctypes.data, row_bytes.ctypes.data, dst.ctypes.data,
+                                     o.ctypes.data, 0, 4) == 0     # empty batch
+    assert lib.ssl4p_host_pack_rects(None, pitch.ctypes.data, nrows.ctypes.data, row_bytes.ctypes.data, dst.ctypes.data,
+                                     o.ctypes.data, 3, 4) != 0     # null pointer: an error, not a crash
