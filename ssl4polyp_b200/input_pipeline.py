@@ -64,11 +64,11 @@ class TrainTransform:
         self.filter = "bicubic"                          # RandomResizedCrop(interpolation=3)
         import os
         from concurrent.futures import ThreadPoolExecutor
-        nt = 1 if pack_threads is None else int(pack_threads)      # measured: one thread is fastest (scripts/input_bench.py)
-        self._pool = ThreadPoolExecutor(max_workers=nt) if nt > 1 else None
-        self._pack_threads = nt
-        self._native_pack = False                        # True: one ssl4p_host_pack_rects call per batch (host threads, no GIL)
-        self._pack_exec = None
+        # The crop rectangles are copied into the staging buffer by ONE native call per batch (ssl4p_host_pack_rects, memcpy on
+        # `pack_threads` host threads) issued from a helper thread: ctypes drops the interpreter lock for the whole call.
+        nt = min(8, os.cpu_count() or 1) if pack_threads is None else int(pack_threads)
+        self._pack_threads = max(1, nt)
+        self._pack_exec = ThreadPoolExecutor(max_workers=1)
         self.last_params = []
         self.h2d_bytes = 0
 
@@ -97,7 +97,7 @@ class TrainTransform:
     def _upload(self, frames, params=None, overlap=None):
         """Draw (or take) the crop parameters, pack the crop rectangles into a pinned buffer, one H2D copy.
         -> (device bytes, device descriptors int64 [N,8], largest crop extent, N).  `overlap`: a callable run on the calling
-        thread while the pool threads copy (the copies release the GIL); its result is left in `self._overlap_result`."""
+        thread while the native copy runs on its helper thread; its result is left in `self._overlap_result`."""
         frames = [f.numpy() if isinstance(f, torch.Tensor) else np.asarray(f) for f in frames]
         for f in frames:
             if f.dtype != np.uint8 or f.ndim != 3 or f.shape[2] != 3:
@@ -116,19 +116,8 @@ class TrainTransform:
         desc = torch.from_numpy(rows)
         k, stage = self._staging(max(total, 1))
 
-        def pack(i):
-            top, left, h, w, _flip = params[i]
-            o = int(rows[i, 0])
-            stage[o:o + h * w * 3].view(h, w, 3).copy_(torch.from_numpy(frames[i])[top:top + h, left:left + w])
-
-        def pack_range(r):
-            for i in r:
-                pack(i)
-
         self._overlap_result = None
-        if self._native_pack and n > 0:
-            # one C call copies every rectangle on `_pack_threads` host threads; it runs on a helper thread (ctypes drops the
-            # GIL for the whole call), so `overlap` - Python-bound - really runs beside the copies
+        if n > 0:
             frames = [f if (f.strides[2] == 1 and f.strides[1] == 3 and f.strides[0] >= 3 * f.shape[1]) else np.ascontiguousarray(f) for f in frames]
             src = np.array([f.__array_interface__["data"][0] + p_[0] * f.strides[0] + p_[1] * 3 for f, p_ in zip(frames, params)], np.uint64)
             pitch = np.array([f.strides[0] for f in frames], np.int64)
@@ -136,26 +125,22 @@ class TrainTransform:
             row_bytes = np.array([p_[3] * 3 for p_ in params], np.int64)
             offs = np.ascontiguousarray(rows[:, 0])
             lib = ops._lib.load()
-            fut = self._pack_exec.submit(lib.ssl4p_host_pack_rects, src.ctypes.data, pitch.ctypes.data, nrows.ctypes.data, row_bytes.ctypes.data,
-                                         stage.data_ptr(), offs.ctypes.data, n, self._pack_threads)
+
+            def copy_all():                              # the error text is thread-local: read it on the thread that made the call
+                rc = lib.ssl4p_host_pack_rects(src.ctypes.data, pitch.ctypes.data, nrows.ctypes.data, row_bytes.ctypes.data,
+                                               stage.data_ptr(), offs.ctypes.data, n, self._pack_threads)
+                return rc, (lib.ssl4p_last_error().decode("utf-8", "replace") if rc else "")
+
+            fut = self._pack_exec.submit(copy_all)
             try:
-                if overlap is not None:
+                if overlap is not None:                  # Python-bound work of the same batch runs beside the copies
                     self._overlap_result = overlap()
             finally:
-                ops._lib.check(fut.result(), "host_pack_rects")
-        elif self._pool is not None and n > 1:             # strided memcpys: the GIL is released inside the copies
-            nt = min(self._pack_threads, n)
-            futures = [self._pool.submit(pack_range, range(k * n // nt, (k + 1) * n // nt)) for k in range(nt)]
-            try:
-                if overlap is not None:
-                    self._overlap_result = overlap()
-            finally:
-                for f in futures:
-                    f.result()
-        else:
-            pack_range(range(n))
-            if overlap is not None:
-                self._overlap_result = overlap()
+                rc, msg = fut.result()
+            if rc:
+                raise RuntimeError(f"host_pack_rects failed (code {rc}): {msg}")
+        elif overlap is not None:
+            self._overlap_result = overlap()
         dev = torch.empty(max(total, 1), dtype=torch.uint8, device=self.device)
         dev.copy_(stage[:max(total, 1)], non_blocking=True)
         desc_dev = desc.pin_memory().to(self.device, non_blocking=True)
@@ -171,8 +156,8 @@ class EvalTransform(TrainTransform):
     """The fine-tune script's val / test transform (classification/data/transforms.py:233-258 with augmentations off):
     T.Resize((size, size)) - PIL BILINEAR over the whole frame - then ToTensor and Normalize; no randomness."""
 
-    def __init__(self, size: int = 224, mean=IMAGENET_MEAN, std=IMAGENET_STD, device=None):
-        super().__init__(size, mean=mean, std=std, device=device)
+    def __init__(self, size: int = 224, mean=IMAGENET_MEAN, std=IMAGENET_STD, device=None, pack_threads=None):
+        super().__init__(size, mean=mean, std=std, device=device, pack_threads=pack_threads)
         self.filter = "bilinear"
 
     def draw(self, height: int, width: int):
@@ -229,18 +214,11 @@ class TrainAugment(EvalTransform):
     def __init__(self, size: int = 224, brightness=0.4, contrast=0.5, saturation=0.25, hue=0.01, kernel_size=25,
                  sigma=(0.001, 2.0), degrees=180.0, flip_p: float = 0.5, mean=IMAGENET_MEAN, std=IMAGENET_STD, device=None,
                  pack_threads=None):
-        super().__init__(size, mean=mean, std=std, device=device)
-        # Whole frames travel (1.2 MB each at 576x720): one ssl4p_host_pack_rects call copies the batch on up to 8 host threads
-        # (measured on the B200 host, 16 cores, 128 frames: torch copy_ 4.6 ms, 8 threads 2.9 ms) while the parameter draws and
-        # their packing - Python-bound - run on the calling thread (scripts/augment_host_probe.py: Python threads around numpy
-        # copies did not overlap with that work, the interpreter lock changed hands once per frame).
-        import os
-        from concurrent.futures import ThreadPoolExecutor
-        nt = min(8, os.cpu_count() or 1) if pack_threads is None else int(pack_threads)
-        self._pack_threads = max(1, nt)
-        self._pool = None
-        self._pack_exec = ThreadPoolExecutor(max_workers=1)
-        self._native_pack = True
+        super().__init__(size, mean=mean, std=std, device=device, pack_threads=pack_threads)
+        # Whole frames travel (1.2 MB each at 576x720).  Measured on the B200 host (16 cores, 128 frames): torch copy_ 4.6 ms,
+        # 8 native threads 2.9 ms, beside which the parameter draws and their packing - Python-bound - run on the calling thread
+        # (scripts/augment_host_probe.py; Python threads around numpy copies did not overlap with that work: the interpreter
+        # lock changed hands once per frame).
         if kernel_size % 2 == 0 or kernel_size > ops.AUG_MAX_TAPS:
             raise RuntimeError(f"TrainAugment: kernel_size must be odd and <= {ops.AUG_MAX_TAPS}")
         self.brightness = (max(0.0, 1 - brightness), 1 + brightness)      # ColorJitter._check_input
