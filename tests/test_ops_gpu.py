@@ -304,7 +304,7 @@ def test_decoder_unshuffle_fwd_bwd():
 
 
 # ---------------------------------------------------------------------------------------------- LayerNorm
-@pytest.mark.parametrize("M,D", [(100, 768), (394, 512), (50, 1024), (37, 64), (20, 32), (5000, 512)])
+@pytest.mark.parametrize("M,D", [(100, 768), (394, 512), (50, 1024), (37, 64), (20, 32), (5000, 512), (12803, 768), (6401, 1024)])
 def test_layernorm_fwd_bwd(M, D):
     from ssl4polyp_b200 import ops
     x = (torch.randn(M, D) * 2 + 0.5).requires_grad_(True)
