@@ -18,6 +18,7 @@ What `engine_pretrain.train_one_epoch` does per iteration in the reference
 from __future__ import annotations
 
 import contextlib
+import gc
 import math
 import os
 
@@ -230,10 +231,20 @@ class TrainEngine:
             if self._graph_warm < 2:                          # lazy attribute / NCCL / workspace initialisation happens
                 self._graph_warm += 1                         # in ordinary eager steps on the caller's own batches
                 return eager_step(*static, lr=lr)
+            # Python's cyclic collector must not run during the capture: if it frees a CUDAGraph / pinned buffer of an engine
+            # that went out of use earlier (cudaGraphExecDestroy, cudaFreeHost), the capture is invalidated
+            # (cudaErrorStreamCaptureInvalidated; torch.cuda.graph no longer collects on entry).  Collect now, then hold it off.
+            gc.collect()
             torch.cuda.synchronize()
-            g = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(g):
-                self._static_out = eager_step(*static, lr=lr)   # lr is read from self.hyper on the device when replayed
+            gc_was_enabled = gc.isenabled()
+            gc.disable()
+            try:
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g):
+                    self._static_out = eager_step(*static, lr=lr)   # lr is read from self.hyper on the device when replayed
+            finally:
+                if gc_was_enabled:
+                    gc.enable()
             self._graph = g
         self._graph.replay()
         self.t += 1

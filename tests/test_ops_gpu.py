@@ -189,8 +189,14 @@ def test_gemm_dynamic_tile_scheduler_slots_reset_themselves():
         s.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(s):
             ops.gemm(a, w, ops.GEMM_NT, ops.EPI_BIAS_BF16, out=out)       # warm-up outside the capture
-            with torch.cuda.graph(g, stream=s):
-                ops.gemm(a, w, ops.GEMM_NT, ops.EPI_BIAS_BF16, out=out)
+            import gc
+            gc.collect()                                                   # a graph of an earlier test freed mid-capture would
+            gc.disable()                                                   # invalidate this one (see engine._replay)
+            try:
+                with torch.cuda.graph(g, stream=s):
+                    ops.gemm(a, w, ops.GEMM_NT, ops.EPI_BIAS_BF16, out=out)
+            finally:
+                gc.enable()
         torch.cuda.current_stream().wait_stream(s)
         for _ in range(3):
             out.zero_()
