@@ -240,7 +240,9 @@ class TrainEngine:
             gc.disable()
             try:
                 g = torch.cuda.CUDAGraph()
-                with torch.cuda.graph(g):
+                # thread_local: CUDA calls of OTHER threads (a DataLoader's pin-memory thread allocating, NCCL's watchdog) do
+                # not touch this capture; in the default global mode any cudaHostAlloc elsewhere invalidates it
+                with torch.cuda.graph(g, capture_error_mode="thread_local"):
                     self._static_out = eager_step(*static, lr=lr)   # lr is read from self.hyper on the device when replayed
             finally:
                 if gc_was_enabled:

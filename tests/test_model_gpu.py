@@ -438,6 +438,35 @@ def test_engine_graph_replay_matches_eager_steps():
     assert len({round(x, 6) for x in own[3:]}) > 1           # replays do advance the noise stream
 
 
+def test_graph_capture_survives_pinned_allocations_on_another_thread():
+    """A DataLoader's pin-memory thread calls cudaHostAlloc whenever it likes (main_pretrain.py:139 `pin_memory=args.pin_mem`);
+    the capture of the step must not be invalidated by it (capture_error_mode thread_local), and the captured step must still
+    train."""
+    import threading
+    from ssl4polyp_b200.engine import PretrainEngine
+    stop = threading.Event()
+    made = []
+
+    def pin_loop():
+        i = 0
+        while not stop.is_set():
+            made.append(torch.empty((1 << 16) + 4096 * (i % 7), dtype=torch.uint8).pin_memory())      # new sizes: real cudaHostAlloc calls
+            if len(made) > 8:
+                made.pop(0)
+            i += 1
+
+    th = threading.Thread(target=pin_loop, daemon=True)
+    th.start()
+    try:
+        imgs = synth_imgs(4, 0, 64).to(dev())
+        eng = PretrainEngine(_small_mae(0), lr=1e-3, weight_decay=0.05)
+        losses = [float(eng.step(imgs, graph=True).item()) for _ in range(8)]
+    finally:
+        stop.set()
+        th.join()
+    assert eng._graph is not None and all(x == x for x in losses) and losses[-1] < losses[0]
+
+
 def test_engine_step_matches_oracle_adamw_step():
     """One engine step == the reference's step restated on the CPU oracle (engine_pretrain.py:50-72 with fp32,
     torch.optim.AdamW over timm's weight-decay groups): updated weights agree (bf16 operand noise only)."""
