@@ -488,8 +488,8 @@ attention_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_
     uint8_t* sDO = smem + 6 * kTileBytes;
     uint8_t* sPT = smem + 8 * kTileBytes;                        // [128 keys] x 2 chunks of 64 queries
     uint8_t* sDS = smem + 10 * kTileBytes;
-    float* sL = reinterpret_cast<float*>(smem + 12 * kTileBytes);   // [HP][256] lse * log2e (+inf for q >= T)
-    float* sD = sL + HP * 256;                                      // [HP][256] D * scale
+    float* sL = reinterpret_cast<float*>(smem + 12 * kTileBytes);   // [HP][256] -lse * log2e (-inf for q >= T)
+    float* sD = sL + HP * 256;                                      // [HP][256] -D * scale
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 12 * kTileBytes + 4096);
     uint64_t* in_full = bars;                                    // [2] operand stages: one-tile sequences (T <= 128) use the two
     uint64_t* in_empty = bars + 2;                               // [2] tiles of every operand buffer as a 2-deep ring of items
@@ -797,7 +797,7 @@ attention_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_
                 }
                 named_bar_sync(1, 256);                          // every thread is done reading the previous item's statistics
 #pragma unroll
-                for (int hh = 0; hh < HP; ++hh) { sts32f(sLa + (hh * 256 + q) * 4, lv[hh]); sts32f(sDa + (hh * 256 + q) * 4, dv[hh]); }
+                for (int hh = 0; hh < HP; ++hh) { sts32f(sLa + (hh * 256 + q) * 4, -lv[hh]); sts32f(sDa + (hh * 256 + q) * 4, -dv[hh]); }   // stored NEGATED: addends of the packed FMAs below
                 named_bar_sync(1, 256);
             }
 
@@ -825,21 +825,27 @@ attention_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_
                                 const int q0 = qt * 128 + h * 64 + c;                // slot of the first query in the statistics arrays
                                 const uint32_t la = sLa + (hh * 256 + q0) * 4, da = sDa + (hh * 256 + q0) * 4;
                                 tmem_ld_wait();
-                                // Padding QUERIES need no masking: their statistics slot holds lse = +inf, so p = exp2(-inf) = 0
+                                // Padding QUERIES need no masking: their statistics slot holds -lse = -inf, so p = exp2(-inf) = 0
                                 // and dS = 0 * finite = 0.  Padding KEYS (zero K rows: s = 0, p = exp2(-lse) != 0) do; the select
                                 // is only compiled into the path taken by warps that own such rows.
+                                // two elements per FFMA2 / FMUL2: (s * scale*log2e - lse*log2e), (dP * scale - D*scale) and their product
+                                const f32x2 sl2v = f2_splat(sl2), scv = f2_splat(p.scale);
                                 auto body = [&](auto mask_keys) {
 #pragma unroll
                                     for (int jj = 0; jj < 32; jj += 4) {
                                         const float4 l4 = lds_v4f(la + jj * 4);      // warp-uniform address: one broadcast wavefront
-                                        const float4 d4 = lds_v4f(da + jj * 4);
-                                        const float lq[4] = {l4.x, l4.y, l4.z, l4.w}, dq_[4] = {d4.x, d4.y, d4.z, d4.w};
+                                        const float4 d4 = lds_v4f(da + jj * 4);      // (both arrays hold the NEGATED statistics)
+                                        const float nl[4] = {l4.x, l4.y, l4.z, l4.w}, nd[4] = {d4.x, d4.y, d4.z, d4.w};
                                         float pv[4], ev[4];
 #pragma unroll
-                                        for (int u = 0; u < 4; ++u) {
-                                            pv[u] = ABLATE(4) ? fmaf(__uint_as_float(rs[jj + u]), sl2, -lq[u]) : fast_exp2(fmaf(__uint_as_float(rs[jj + u]), sl2, -lq[u]));
-                                            ev[u] = pv[u] * fmaf(__uint_as_float(rd[jj + u]), p.scale, -dq_[u]);
-                                            if (decltype(mask_keys)::value && !key_ok) { pv[u] = 0.f; ev[u] = 0.f; }
+                                        for (int u = 0; u < 4; u += 2) {
+                                            float a0, a1;
+                                            f2_unpack(f2_fma(f2_pack(__uint_as_float(rs[jj + u]), __uint_as_float(rs[jj + u + 1])), sl2v, f2_pack(nl[u], nl[u + 1])), a0, a1);
+                                            pv[u] = ABLATE(4) ? a0 : fast_exp2(a0);
+                                            pv[u + 1] = ABLATE(4) ? a1 : fast_exp2(a1);
+                                            const f32x2 t = f2_fma(f2_pack(__uint_as_float(rd[jj + u]), __uint_as_float(rd[jj + u + 1])), scv, f2_pack(nd[u], nd[u + 1]));
+                                            f2_unpack(f2_mul(f2_pack(pv[u], pv[u + 1]), t), ev[u], ev[u + 1]);
+                                            if (decltype(mask_keys)::value && !key_ok) { pv[u] = 0.f; pv[u + 1] = 0.f; ev[u] = 0.f; ev[u + 1] = 0.f; }
                                         }
                                         pw[(jj >> 1)] = pack_bf16(pv[0], pv[1]); pw[(jj >> 1) + 1] = pack_bf16(pv[2], pv[3]);
                                         dw[(jj >> 1)] = pack_bf16(ev[0], ev[1]); dw[(jj >> 1) + 1] = pack_bf16(ev[2], ev[3]);
