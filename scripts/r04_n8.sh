@@ -1,0 +1,14 @@
+# usage: bash scripts/r04_n8.sh TAG : the driver's launch line at N = 8 on the final code (NCCL all-reduces inside the thread_local capture)
+cd $GRAFT_REPO_ROOT
+T=${1:-r04k}
+timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29541 bench.py --gpus 8 --steps 20 --warmup 5 --extra none --no-cpu-baseline > gpurun_out/${T}_bench_n8.json 2> gpurun_out/${T}_bench_n8.err; echo "bench n8 rc=$?"
+python - <<PY
+import json
+try:
+    d=json.loads(open('gpurun_out/${T}_bench_n8.json').read().strip().splitlines()[-1])
+    print(round(d['value']), round(d['ms_per_step'],2), 'e2e', round(d['e2e']['value']), d['clocks']['sm_mhz'], d['dp_check'])
+except Exception as e:
+    print('FAILED', e); print(open('gpurun_out/${T}_bench_n8.err').read()[-3000:])
+PY
+timeout 300 python bench.py --gpus 1 --steps 20 --warmup 5 --extra none --no-cpu-baseline > gpurun_out/${T}_bench_n1_same_box.json 2>/dev/null; python -c "
+import json; d=json.loads(open('gpurun_out/${T}_bench_n1_same_box.json').read().strip().splitlines()[-1]); print('n1 same box', round(d['value']), round(d['ms_per_step'],2), d['clocks']['sm_mhz'])"
