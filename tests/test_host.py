@@ -635,3 +635,28 @@ def test_host_pack_rects_matches_numpy_slices_on_every_thread_count():
                                      o.ctypes.data, 0, 4) == 0     # empty batch
     assert lib.ssl4p_host_pack_rects(None, pitch.ctypes.data, nrows.ctypes.data, row_bytes.ctypes.data, dst.ctypes.data,
                                      o.ctypes.data, 3, 4) != 0     # null pointer: an error, not a crash
+
+
+def test_train_augment_draws_follow_torchvision_call_for_call():
+    """TrainAugment.draw_augment (one reused scratch tensor, .tolist()) against the installed torchvision transforms drawing
+    in the Compose's order under the same seed (classification/data/transforms.py:236-244): identical values, identical
+    generator consumption (the state after 500 images is the same)."""
+    import types
+    import torchvision.transforms as T
+    from ssl4polyp_b200 import input_pipeline as ip
+    me = types.SimpleNamespace(brightness=(0.6, 1.4), contrast=(0.5, 1.5), saturation=(0.75, 1.25), hue=(-0.01, 0.01),
+                               sigma=(0.001, 2.0), degrees=180.0, flip_p=0.5, _scratch={})
+    torch.manual_seed(77)
+    mine = [ip.TrainAugment.draw_augment(me) for _ in range(500)]
+    state_mine = torch.get_rng_state()
+    cj = T.ColorJitter(brightness=0.4, contrast=0.5, saturation=0.25, hue=0.01)
+    torch.manual_seed(77)
+    for a in mine:
+        order, b, c, s, h = T.ColorJitter.get_params(cj.brightness, cj.contrast, cj.saturation, cj.hue)
+        sigma = T.GaussianBlur.get_params(0.001, 2.0)
+        hflip = bool(torch.rand(1) < 0.5)                        # RandomHorizontalFlip.forward
+        vflip = bool(torch.rand(1) < 0.5)                        # RandomVerticalFlip.forward
+        angle = T.RandomRotation.get_params([-180.0, 180.0])
+        assert a == dict(order=order.tolist(), brightness=b, contrast=c, saturation=s, hue=h, sigma=sigma, hflip=hflip, vflip=vflip,
+                         angle=angle)
+    assert torch.equal(torch.get_rng_state(), state_mine)
