@@ -179,7 +179,9 @@ size_t ssl4p_layernorm_bwd_workspace_bytes(int M, int D);
  * operators for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops).  Same arguments and results
  * minus the workspace: the [grid][3*D] partial sums live in a file-scope device array (3.47 MiB per GPU that loads the
  * library, held until exit).  Limit: D <= ssl4p_layernorm_bwd_max_static_d() (1024); larger D returns SSL4P_ERR_ARG.
- * Calls no cudaMalloc/cudaFree.  All calls share the array: calls that overlap on the GPU (different streams) race. */
+ * Calls no cudaMalloc/cudaFree.  All calls share the array: calls that overlap on the GPU (different streams) race.
+ * The first call on a device resolves the array's device address (cudaGetSymbolAddress, checked, cached per device):
+ * make one call per device during set-up, before any stream capture. */
 int ssl4p_layernorm_bwd_static(const void* dy_bf16, const float* x, const float* mean, const float* rstd, const float* gamma,
                                const float* residual_grad, float* dx_out, void* dxb_bf16, float* dgamma, float* dbeta,
                                float* dx_colsum, int M, int D, int accumulate, int accumulate_colsum, void* stream);
